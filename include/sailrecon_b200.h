@@ -1,0 +1,136 @@
+/* libsailrecon_b200.so — C-ABI of the B200 (sm_100a) hot path of SAIL-Recon.
+ *
+ * The reference (ShngJZ/self-supervise-sfm) has no FFI of its own: its "plugin API" for this path is
+ * the nn.Module surface of sailrecon/layers/{attention,block,rope,mlp,layer_scale}.py,
+ * sailrecon/models/aggregator.py and sailrecon/heads/camera_head.py, whose math lands in PyTorch library
+ * calls.  Each entry point below replaces one of those library call sites (reference file:line cited);
+ * the Python mirror of the module surface (package `sailrecon_b200`) binds them through ctypes.
+ *
+ * Conventions: plain C types only; all pointers are DEVICE pointers unless said otherwise; every launch is
+ * asynchronous on `stream` (a cudaStream_t passed as void*); nothing is allocated, owned or freed by the
+ * library; return value 0 = SR_OK, otherwise an SR_ERR_* code with a message in sr_last_error().
+ * There is no CPU fallback: on a device that is not compute capability 10.x every compute call returns
+ * SR_ERR_ARCH.
+ */
+#ifndef SAILRECON_B200_H_
+#define SAILRECON_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SR_OK 0
+#define SR_ERR_SHAPE 1 /* bad shape / alignment / argument                  */
+#define SR_ERR_ARCH 2  /* device is not sm_100                              */
+#define SR_ERR_CUDA 3  /* a CUDA runtime / driver call failed               */
+
+/* ---- library ---------------------------------------------------------------------------------------- */
+int sr_version(void);               /* 10000*major + 100*minor + patch                                       */
+const char* sr_last_error(void);    /* thread-local message of the last failing call                          */
+int sr_arch_check(void);            /* SR_OK iff current device is compute capability 10.x                    */
+int sr_num_kernel_launches(void);   /* kernels launched by this library since load (bench.py gpu_launches)    */
+
+/* ---- LayerNorm: nn.LayerNorm at block.py:50,70 (norm1/norm2), camera_head.py:64,65,77 ------------------
+ * x fp32 [rows, C] (row stride ldx), weight/bias fp32 [C] (NULL = no affine, camera_head.py:77 adaln_norm).
+ * out: bf16 (out_bf16=1; the cast autocast applies before the next Linear) or fp32, row stride ldo.       */
+int sr_layernorm_fwd(const float* x, int64_t ldx, const float* weight, const float* bias, void* out, int out_bf16,
+                     int64_t ldo, int64_t rows, int64_t C, float eps, void* stream);
+/* Same with a fused row gather: out[r] = LN(x[idx[r]]) (idx int32 [rows], NULL = identity).  Replaces the
+ * scene-token gather of aggregator.py:617-625 followed by global_reloc_blocks[i].norm1 (block.py:87).       */
+int sr_layernorm_gather_fwd(const float* x, int64_t ldx, const int32_t* idx, const float* weight, const float* bias,
+                            void* out, int out_bf16, int64_t ldo, int64_t rows, int64_t C, float eps, void* stream);
+
+/* ---- GEMM + fused epilogue: nn.Linear at attention.py:73 (qkv), :120 (proj), mlp.py:35,38 (fc1, fc2) ----
+ * out[M,N] = epilogue(A[M,K] @ W[N,K]^T + bias).  W is nn.Linear.weight as stored ([out,in], row-major). */
+#define SR_EPI_BIAS 0          /* y = acc + bias                                 (proj of a plain Linear)   */
+#define SR_EPI_BIAS_GELU 1     /* y = gelu_erf(round(acc + bias))                (mlp.py:35-36)             */
+#define SR_EPI_LS_RESIDUAL 2   /* out = resid + gamma * round(acc + bias)        (block.py:110-111, fp32)   */
+#define SR_EPI_QKV 3           /* bias, then per-head LayerNorm(d) on q,k (attention.py:78) and 2D RoPE
+                                  (attention.py:80-82, rope.py:165-207); v = bias only                     */
+typedef struct sr_epilogue {
+  int32_t kind;          /* SR_EPI_*                                                                        */
+  int32_t out_bf16;      /* 1: out is bf16 (tensor-core path rounds here exactly where autocast does)       */
+  void* out;             /* [M, N], row stride ldo (elements)                                               */
+  int64_t ldo;
+  const float* bias;     /* [N] or NULL                                                                     */
+  const float* gamma;    /* LS_RESIDUAL: LayerScale gamma [N] (NULL = 1)                                    */
+  const float* resid;    /* LS_RESIDUAL: fp32 [M, N], row stride ldr; may alias out                         */
+  int64_t ldr;
+  /* QKV epilogue */
+  int64_t qkv_dim;       /* C: columns [0,C) are q, [C,2C) k, [2C,3C) v of the full qkv Linear              */
+  int64_t col_offset;    /* column of the full [3C] output that local column 0 corresponds to               */
+  int32_t head_dim;      /* 64                                                                              */
+  int32_t qk_norm;       /* apply LayerNorm(head_dim) to q and k                                            */
+  const float* qn_w;     /* q_norm.weight/bias, k_norm.weight/bias, fp32 [head_dim]                         */
+  const float* qn_b;
+  const float* kn_w;
+  const float* kn_b;
+  float qk_eps;
+  int32_t rope;          /* apply 2D RoPE to q and k                                                        */
+  const float* rope_cos; /* fp32 [rope_max_pos, head_dim/4] (rope.py:110-123 without the duplication)       */
+  const float* rope_sin;
+  int32_t rope_max_pos;
+  const int32_t* pos;    /* int32 [M, 2] (y, x) positions (rope.py:25-66 + aggregator.py:319-328)           */
+} sr_epilogue_t;
+
+/* bf16 tensor-core path (tcgen05.mma, TMA-fed): A bf16 [M,K] row stride lda, W bf16 [N,K] row stride ldw.
+ * Requirements: K % 64 == 0, N % 128 == 0, lda/ldw multiples of 8, 16-byte aligned pointers.              */
+int sr_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int64_t M, int64_t N, int64_t K,
+                 const sr_epilogue_t* epi, void* stream);
+/* fp32 SIMT path (fp32-check mode and the autocast-disabled camera head, sail_recon.py:119): no rounding.  */
+int sr_gemm_f32(const float* A, int64_t lda, const float* W, int64_t ldw, int64_t M, int64_t N, int64_t K,
+                const sr_epilogue_t* epi, void* stream);
+
+/* ---- Attention: F.scaled_dot_product_attention at attention.py:103-109 --------------------------------
+ * Structured instead of dense-masked.  `batch` independent segments; query rows of segment b are
+ * [b*q_batch_stride, b*q_batch_stride + q_len) of q, they attend to the shared prefix rows [0, prefix_len)
+ * of (pk, pv) followed by the segment's own rows [b*kv_batch_stride, +kv_len) of (k, v).
+ *   frame blocks   (aggregator.py:643-670): batch = S, q_len = kv_len = P, no prefix
+ *   global blocks  (aggregator.py:743-769): batch = 1, q_len = kv_len = Na*P
+ *   reloc blocks   (aggregator.py:672-741 + mask :302-311,:832-851): batch = Nq, own frame + scene prefix
+ *   camera trunk   (camera_head.py:163-166 + build_lr_mask :197-228): anchors = 1 segment; queries = Nq
+ *                   segments of length 1 with the anchors as prefix
+ * Head h of a row lives at columns [h*head_dim, (h+1)*head_dim).  out has the layout the proj Linear
+ * consumes (attention.py:119): [rows, num_heads*head_dim].                                               */
+typedef struct sr_attn {
+  const void* q;  int64_t ldq;
+  const void* k;  const void* v;  int64_t ldkv;
+  const void* pk; const void* pv; int64_t ldp; int64_t prefix_len;   /* pk == NULL or prefix_len == 0: none */
+  void* out;      int64_t ldo;
+  int32_t num_heads, head_dim;
+  int32_t batch;
+  int64_t q_len, q_batch_stride;
+  int64_t kv_len, kv_batch_stride;
+  float scale;           /* head_dim^-0.5                                                                  */
+  /* ring / split-KV carry (global attention sharded over ranks; all NULL for a self-contained call):
+   * running row max m and row sum l in the log2 domain, fp32 [num_heads, total_q_rows], and the
+   * un-normalised fp32 accumulator acc [total_q_rows, num_heads*head_dim].                               */
+  float* carry_m; float* carry_l; float* carry_acc;
+  int32_t carry_in;      /* 1: start from the carried state instead of (-inf, 0, 0)                        */
+  int32_t carry_out;     /* 1: write the state back and skip the final normalisation + out store           */
+} sr_attn_t;
+
+int sr_attn_fwd_bf16(const sr_attn_t* p, void* stream);  /* tcgen05 flash attention, head_dim 64           */
+int sr_attn_fwd_f32(const sr_attn_t* p, void* stream);   /* fp32 SIMT, head_dim <= 128 (check mode, camera) */
+
+/* ---- token re-layout (aggregator.py:355-357,393-399,406-423,603-625) ----------------------------------- */
+/* dst[i, :] = src[idx[i], :] for i < n; fp32 rows of C elements; idx int32 (scene-token selection).       */
+int sr_gather_rows_f32(const float* src, int64_t lds, const int32_t* idx, float* dst, int64_t ldd, int64_t n,
+                       int64_t C, void* stream);
+/* dst[r, col_off : col_off + C] = src[r, :] — writes one half of the [.., 2C] concat outputs.             */
+int sr_copy_cols_f32(const float* src, int64_t lds, float* dst, int64_t ldd, int64_t col_off, int64_t rows,
+                     int64_t C, void* stream);
+/* fp32 -> bf16 cast of a [rows, C] matrix (weights, once).                                                */
+int sr_cast_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, int64_t rows, int64_t C,
+                        void* stream);
+/* camera_head.py:157-160: out = gate * (LN_noaffine(x) * (1 + scale) + shift) + x, all fp32 [rows, C];
+ * mod = [rows, 3C] holding (shift | scale | gate).                                                         */
+int sr_adaln_modulate_f32(const float* x, const float* mod, float* out, int64_t rows, int64_t C, float eps,
+                          void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SAILRECON_B200_H_ */

@@ -1,0 +1,79 @@
+"""Generates tests/golden/*.npz by running the UNMODIFIED reference (imported from /root/reference) on seeded
+inputs.  Runs only in the build container; the fixtures travel, the reference does not.
+
+    python oracle/make_golden.py            # rewrites every case in oracle/golden_common.GOLDEN_CASES
+
+Each .npz stores: output_dict[-1] and the intermediate layers, cam_token_last_layer, the four camera-head pose
+encodings, the scene-token indices the reference drew (bit-exact check), the token positions, and the parameter
+shapes (values are regenerated from the seed by golden_common.make_params).
+"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, "/root/reference")
+from golden_common import GOLDEN_CASES, make_images, make_params  # noqa: E402
+
+from sailrecon.heads.camera_head import CameraHead  # noqa: E402
+from sailrecon.models.aggregator import Aggregator  # noqa: E402
+
+
+def run_case(name, case):
+    torch.manual_seed(0)
+    agg = Aggregator(**case["agg"]).eval()
+    head = CameraHead(**case["head"]).eval()
+    sd = {"agg." + k: v for k, v in agg.state_dict().items()}
+    sd.update({"head." + k: v for k, v in head.state_dict().items()})
+    shapes = {k: list(v.shape) for k, v in sd.items()}
+    params = make_params(shapes, case["seed"])
+    agg.load_state_dict({k[4:]: v for k, v in params.items() if k.startswith("agg.")})
+    head.load_state_dict({k[5:]: v for k, v in params.items() if k.startswith("head.")})
+    S, Na = case["S"], case["Na"]
+    if name == "tiny_clamp":                      # anchors are frames 0, 2, 3; the query is frame 1
+        nrl, rl = [0, 2, 3], [1]
+    else:
+        nrl, rl = list(range(Na)), list(range(Na, S))
+    images = make_images(S, case["H"], case["W"], case["seed"] + 100)
+
+    # record the indices the reference draws (aggregator.py:617-621) by wrapping torch.randperm
+    drawn = []
+    orig = torch.randperm
+
+    def spy(n, *a, **k):
+        r = orig(n, *a, **k)
+        drawn.append(r.clone())
+        return r
+
+    torch.randperm = spy
+    try:
+        with torch.no_grad():
+            agg.generator.manual_seed(1234)
+            out, psi, cam = agg(images, nrl, rl, fix_rank=case["fix_rank"])
+            poses = head(out, cam)
+    finally:
+        torch.randperm = orig
+    rank = agg.rank
+    sel = torch.stack([d[:rank] for d in drawn]).reshape(case["agg"]["depth"], len(nrl), rank)
+    arrays = {f"out_{k}": v.numpy() for k, v in out.items()}
+    arrays["cam_token_last_layer"] = cam.numpy()
+    for i, pz in enumerate(poses):
+        arrays[f"pose_{i}"] = pz.numpy()
+    arrays["scene_idx"] = sel.numpy().astype(np.int64)
+    arrays["positions"] = agg.position_getter(1, case["H"] // 14, case["W"] // 14, "cpu")[0].numpy()
+    arrays["meta"] = np.frombuffer(json.dumps(dict(shapes=shapes, no_reloc_list=nrl, reloc_list=rl, rank=rank,
+                                                    patch_start_idx=psi)).encode(), dtype=np.uint8)
+    path = os.path.join(os.path.dirname(HERE), "tests", "golden", name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(name, {k: v.shape for k, v in arrays.items() if k != "meta"}, os.path.getsize(path), "bytes")
+
+
+if __name__ == "__main__":
+    for n, c in GOLDEN_CASES.items():
+        if len(sys.argv) > 1 and n not in sys.argv[1:]:
+            continue
+        run_case(n, c)

@@ -1,0 +1,104 @@
+"""ctypes binding of libsailrecon_b200.so — the C-ABI declared in include/sailrecon_b200.h.
+
+There is deliberately no fallback: if the shared library is missing, or a compute entry point is called on a
+machine without an sm_100 device, a RuntimeError is raised.  Signatures carry only plain C types (device
+pointers as void*, sizes as int64, cudaStream_t as void*).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+SR_OK, SR_ERR_SHAPE, SR_ERR_ARCH, SR_ERR_CUDA = 0, 1, 2, 3
+SR_EPI_BIAS, SR_EPI_BIAS_GELU, SR_EPI_LS_RESIDUAL, SR_EPI_QKV = 0, 1, 2, 3
+
+_vp, _i64, _i32, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_float
+
+
+class SrEpilogue(C.Structure):
+    """struct sr_epilogue (include/sailrecon_b200.h)."""
+
+    _fields_ = [
+        ("kind", _i32), ("out_bf16", _i32), ("out", _vp), ("ldo", _i64),
+        ("bias", _vp), ("gamma", _vp), ("resid", _vp), ("ldr", _i64),
+        ("qkv_dim", _i64), ("col_offset", _i64), ("head_dim", _i32), ("qk_norm", _i32),
+        ("qn_w", _vp), ("qn_b", _vp), ("kn_w", _vp), ("kn_b", _vp), ("qk_eps", _f32),
+        ("rope", _i32), ("rope_cos", _vp), ("rope_sin", _vp), ("rope_max_pos", _i32), ("pos", _vp),
+    ]
+
+
+class SrAttn(C.Structure):
+    """struct sr_attn (include/sailrecon_b200.h)."""
+
+    _fields_ = [
+        ("q", _vp), ("ldq", _i64),
+        ("k", _vp), ("v", _vp), ("ldkv", _i64),
+        ("pk", _vp), ("pv", _vp), ("ldp", _i64), ("prefix_len", _i64),
+        ("out", _vp), ("ldo", _i64),
+        ("num_heads", _i32), ("head_dim", _i32), ("batch", _i32),
+        ("q_len", _i64), ("q_batch_stride", _i64), ("kv_len", _i64), ("kv_batch_stride", _i64),
+        ("scale", _f32),
+        ("carry_m", _vp), ("carry_l", _vp), ("carry_acc", _vp), ("carry_in", _i32), ("carry_out", _i32),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/sailrecon_b200.h declares
+SIGNATURES = {
+    "sr_version": (C.c_int, []),
+    "sr_last_error": (C.c_char_p, []),
+    "sr_arch_check": (C.c_int, []),
+    "sr_num_kernel_launches": (C.c_int, []),
+    "sr_layernorm_fwd": (C.c_int, [_vp, _i64, _vp, _vp, _vp, C.c_int, _i64, _i64, _i64, _f32, _vp]),
+    "sr_layernorm_gather_fwd": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, C.c_int, _i64, _i64, _i64, _f32, _vp]),
+    "sr_gemm_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, C.POINTER(SrEpilogue), _vp]),
+    "sr_gemm_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, C.POINTER(SrEpilogue), _vp]),
+    "sr_attn_fwd_bf16": (C.c_int, [C.POINTER(SrAttn), _vp]),
+    "sr_attn_fwd_f32": (C.c_int, [C.POINTER(SrAttn), _vp]),
+    "sr_gather_rows_f32": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _vp]),
+    "sr_copy_cols_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp]),
+    "sr_cast_f32_to_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _vp]),
+    "sr_adaln_modulate_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _f32, _vp]),
+}
+
+_lib = None
+
+
+def lib_path() -> str:
+    return os.environ.get("SAILRECON_B200_LIB", _build.LIB_PATH)
+
+
+def load():
+    """dlopen the library (building it first if nvcc is available and it is stale) and bind every symbol."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if path == _build.LIB_PATH and not _build.is_current():
+        try:
+            _build.build_library()
+        except Exception as e:  # no nvcc on this machine
+            if not os.path.exists(path):
+                raise RuntimeError(
+                    f"libsailrecon_b200.so is not built and could not be built ({e}); "
+                    "sailrecon_b200 has no CPU or PyTorch fallback") from e
+    if not os.path.exists(path):
+        raise RuntimeError(f"{path} not found; sailrecon_b200 has no CPU or PyTorch fallback")
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc == SR_OK:
+        return
+    msg = load().sr_last_error().decode(errors="replace")
+    kind = {SR_ERR_SHAPE: "bad argument", SR_ERR_ARCH: "unsupported device", SR_ERR_CUDA: "CUDA error"}.get(rc, "error")
+    if rc == SR_ERR_SHAPE:
+        raise ValueError(f"sailrecon_b200 {what}: {kind}: {msg}")
+    raise RuntimeError(f"sailrecon_b200 {what}: {kind}: {msg}")

@@ -1,0 +1,410 @@
+// bf16 GEMM on tcgen05 tensor cores with fused epilogues (sm_100a).
+//
+//   out[M,N] = epilogue(A[M,K] @ W[N,K]^T + bias)
+//
+// Replaces the cuBLASLt calls behind nn.Linear at sailrecon/layers/attention.py:73 (qkv), :120 (proj) and
+// sailrecon/layers/mlp.py:35,38 (fc1, fc2) and folds in what the reference runs as separate ATen kernels:
+// bias, exact-erf GELU (mlp.py:36), LayerScale*x + residual (layer_scale.py:23, block.py:110-111) and, for
+// the qkv projection, the per-head LayerNorm on q,k (attention.py:78) plus 2D RoPE (rope.py:165-207).
+//
+// Design (one persistent CTA per SM, 384 threads):
+//   warp 0      TMA producer: A tile 128x64 and W tile BNx64 (SWIZZLE_128B) into a 4-stage smem ring
+//   warp 1      MMA issuer: one thread issues tcgen05.mma (M=128, N=BN, K=16) x4 per stage; accumulators
+//               live in TMEM, double buffered (2 x BN columns) so the epilogue of tile i overlaps tile i+1
+//   warp 2      TMEM allocator
+//   warps 4-11  epilogue: tcgen05.ld gives each thread one output row x 32 columns; warps w and w+4 share a
+//               lane quarter and split the BN columns.  A thread holding a whole 64-wide head makes the
+//               q/k LayerNorm + RoPE a purely in-register computation (no shuffles).
+// Rounding points reproduce CUDA autocast (SURVEY.md §5 "precision policy"): acc+bias is rounded to bf16
+// where the reference's Linear returns bf16, before GELU / LayerScale / LayerNorm consume it.
+#include "common.cuh"
+#include "sr_internal.h"
+
+namespace sr {
+
+constexpr int kBM = 128;
+constexpr int kBK = 64;
+constexpr int kGemmThreads = 384;
+constexpr int kEpiWarp0 = 4;
+constexpr int kNumEpiWarps = 8;
+
+struct GemmParams {
+  int M, N, K;
+  sr_epilogue_t e;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kABytes = kBM * kBK * 2;
+  static constexpr int kBBytes = BN * kBK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // +1024: manual 1 KB alignment
+  static constexpr int kTmemCols = 2 * BN;                         // double-buffered accumulator
+};
+
+// ---------------------------------------------------------------------------------------------- epilogues
+// v[32] = raw fp32 accumulators of row `row`, columns [col, col+32) of the output.
+template <int EPI, bool OUT_BF16>
+__device__ __forceinline__ void epi_store32(const GemmParams& p, int row, int col, uint32_t (&v)[32]) {
+  const sr_epilogue_t& e = p.e;
+  float x[32];
+#pragma unroll
+  for (int i = 0; i < 32; i += 4) {
+    float4 b = e.bias ? __ldg(reinterpret_cast<const float4*>(e.bias + col + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    x[i + 0] = __uint_as_float(v[i + 0]) + b.x;
+    x[i + 1] = __uint_as_float(v[i + 1]) + b.y;
+    x[i + 2] = __uint_as_float(v[i + 2]) + b.z;
+    x[i + 3] = __uint_as_float(v[i + 3]) + b.w;
+  }
+  if (EPI == SR_EPI_BIAS_GELU) {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) x[i] = gelu_erf(bf16_round(x[i]));
+  }
+  if (EPI == SR_EPI_LS_RESIDUAL) {
+    const float* r = e.resid + static_cast<int64_t>(row) * e.ldr + col;
+    float* o = reinterpret_cast<float*>(e.out) + static_cast<int64_t>(row) * e.ldo + col;
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      float4 rr = *reinterpret_cast<const float4*>(r + i);
+      float4 g = e.gamma ? __ldg(reinterpret_cast<const float4*>(e.gamma + col + i)) : make_float4(1.f, 1.f, 1.f, 1.f);
+      float4 y;
+      y.x = rr.x + g.x * bf16_round(x[i + 0]);
+      y.y = rr.y + g.y * bf16_round(x[i + 1]);
+      y.z = rr.z + g.z * bf16_round(x[i + 2]);
+      y.w = rr.w + g.w * bf16_round(x[i + 3]);
+      *reinterpret_cast<float4*>(o + i) = y;
+    }
+    return;
+  }
+  if (OUT_BF16) {
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + static_cast<int64_t>(row) * e.ldo + col;
+#pragma unroll
+    for (int i = 0; i < 32; i += 8) {
+      uint4 w;
+      w.x = pack_bf16x2(x[i + 0], x[i + 1]);
+      w.y = pack_bf16x2(x[i + 2], x[i + 3]);
+      w.z = pack_bf16x2(x[i + 4], x[i + 5]);
+      w.w = pack_bf16x2(x[i + 6], x[i + 7]);
+      *reinterpret_cast<uint4*>(o + i) = w;
+    }
+  } else {
+    float* o = reinterpret_cast<float*>(e.out) + static_cast<int64_t>(row) * e.ldo + col;
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) *reinterpret_cast<float4*>(o + i) = make_float4(x[i], x[i + 1], x[i + 2], x[i + 3]);
+  }
+}
+
+// One 64-wide head of q or k for one token: bias -> bf16 round -> LayerNorm(64) -> 2D RoPE -> bf16 store.
+// `which` = 0 (q) / 1 (k) / 2 (v: bias + store only).
+__device__ __forceinline__ void epi_qkv_head(const GemmParams& p, int row, int col, int which, uint32_t (&v0)[32],
+                                             uint32_t (&v1)[32]) {
+  const sr_epilogue_t& e = p.e;
+  float x[64];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    x[i] = __uint_as_float(v0[i]);
+    x[32 + i] = __uint_as_float(v1[i]);
+  }
+  if (e.bias) {
+#pragma unroll
+    for (int i = 0; i < 64; i += 4) {
+      float4 b = __ldg(reinterpret_cast<const float4*>(e.bias + col + i));
+      x[i] += b.x; x[i + 1] += b.y; x[i + 2] += b.z; x[i + 3] += b.w;
+    }
+  }
+  if (which < 2 && (e.qk_norm || e.rope)) {
+    // the reference's Linear returned bf16; LayerNorm / RoPE then run in fp32 on that rounded value
+#pragma unroll
+    for (int i = 0; i < 64; ++i) x[i] = bf16_round(x[i]);
+    if (e.qk_norm) {
+      float mean = 0.f;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) mean += x[i];
+      mean *= (1.0f / 64.0f);
+      float var = 0.f;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { float d = x[i] - mean; var += d * d; }
+      float rstd = rsqrtf(var * (1.0f / 64.0f) + e.qk_eps);
+      const float* w = which == 0 ? e.qn_w : e.kn_w;
+      const float* b = which == 0 ? e.qn_b : e.kn_b;
+#pragma unroll
+      for (int i = 0; i < 64; i += 4) {
+        float4 ww = __ldg(reinterpret_cast<const float4*>(w + i));
+        float4 bb = __ldg(reinterpret_cast<const float4*>(b + i));
+        x[i + 0] = (x[i + 0] - mean) * rstd * ww.x + bb.x;
+        x[i + 1] = (x[i + 1] - mean) * rstd * ww.y + bb.y;
+        x[i + 2] = (x[i + 2] - mean) * rstd * ww.z + bb.z;
+        x[i + 3] = (x[i + 3] - mean) * rstd * ww.w + bb.w;
+      }
+    }
+    if (e.rope) {
+      // rope.py:196-207: first 32 features rotate with the y position, last 32 with x; inside each half the
+      // pairs are (i, i+16) (rotate-half, rope.py:136-138) and both members share frequency i (rope.py:119).
+      int2 yx = __ldg(reinterpret_cast<const int2*>(e.pos) + row);
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        int ppos = half == 0 ? yx.x : yx.y;
+        const float* ct = e.rope_cos + static_cast<int64_t>(ppos) * 16;
+        const float* st = e.rope_sin + static_cast<int64_t>(ppos) * 16;
+#pragma unroll
+        for (int i = 0; i < 16; i += 4) {
+          float4 c = __ldg(reinterpret_cast<const float4*>(ct + i));
+          float4 s = __ldg(reinterpret_cast<const float4*>(st + i));
+          float cc[4] = {c.x, c.y, c.z, c.w}, ss[4] = {s.x, s.y, s.z, s.w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            float a = x[half * 32 + i + j], b = x[half * 32 + 16 + i + j];
+            x[half * 32 + i + j] = a * cc[j] - b * ss[j];
+            x[half * 32 + 16 + i + j] = b * cc[j] + a * ss[j];
+          }
+        }
+      }
+    }
+  }
+  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + static_cast<int64_t>(row) * e.ldo + col;
+#pragma unroll
+  for (int i = 0; i < 64; i += 8) {
+    uint4 w;
+    w.x = pack_bf16x2(x[i + 0], x[i + 1]);
+    w.y = pack_bf16x2(x[i + 2], x[i + 3]);
+    w.z = pack_bf16x2(x[i + 4], x[i + 5]);
+    w.w = pack_bf16x2(x[i + 6], x[i + 7]);
+    *reinterpret_cast<uint4*>(o + i) = w;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- kernel
+template <int BN, int EPI, bool OUT_BF16>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+               const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t full_bar[Cfg::kStages];
+  __shared__ __align__(8) uint64_t empty_bar[Cfg::kStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_slot;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+
+  const int num_m = (p.M + kBM - 1) / kBM;
+  const int num_n = p.N / BN;
+  const int num_tiles = num_m * num_n;
+  const int num_kb = p.K / kBK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < Cfg::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full_bar[s], 1);
+      mbar_init(&tmem_empty_bar[s], kNumEpiWarps);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<Cfg::kTmemCols>(&tmem_base_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_slot;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const int m_blk = t / num_n, n_blk = t % num_n;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * Cfg::kStageBytes;
+          uint8_t* sb = sa + Cfg::kABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
+          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kBK, n_blk * BN);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+        const int as = it & 1;
+        mbar_wait(&tmem_empty_bar[as], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + as * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sb = sa + Cfg::kABytes;
+          const uint64_t da = umma_desc_sw128(sa, 16, 1024);
+          const uint64_t db = umma_desc_sw128(sb, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            // +32 bytes per K=16 slice inside the 128B swizzle atom -> +2 in the (addr >> 4) field
+            umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tmem_full_bar[as]);
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    // ------------------------------------------------------------------ epilogue
+    const int ew = warp - kEpiWarp0;
+    const int quarter = warp & 3;          // TMEM lane quarter this warp may access
+    const int half = ew >> 2;              // which half of the BN columns
+    constexpr int kColsPerWarp = BN / 2;
+    int it = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      const int m_blk = t / num_n, n_blk = t % num_n;
+      const int as = it & 1;
+      mbar_wait(&tmem_full_bar[as], (it >> 1) & 1);
+      tc_fence_after();
+      const int row = m_blk * kBM + quarter * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN + half * kColsPerWarp;
+      const int col_base = n_blk * BN + half * kColsPerWarp;
+      if (EPI == SR_EPI_QKV) {
+#pragma unroll 1
+        for (int c = 0; c < kColsPerWarp; c += 64) {
+          uint32_t v0[32], v1[32];
+          tmem_ld32(taddr + c, v0);
+          tmem_ld32(taddr + c + 32, v1);
+          tmem_ld_wait();
+          if (row < p.M) {
+            const int col = col_base + c;
+            const int which = static_cast<int>((p.e.col_offset + col) / p.e.qkv_dim);
+            epi_qkv_head(p, row, col, which, v0, v1);
+          }
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < kColsPerWarp; c += 32) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c, v);
+          tmem_ld_wait();
+          if (row < p.M) epi_store32<EPI, OUT_BF16>(p, row, col_base + c, v);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[as]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- host
+extern int g_launch_count;
+
+template <int BN, int EPI, bool OUT_BF16>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+  using Cfg = GemmCfg<BN>;
+  auto kern = gemm_tc_kernel<BN, EPI, OUT_BF16>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    SR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    configured = true;
+  }
+  const int num_tiles = ((p.M + kBM - 1) / kBM) * (p.N / BN);
+  const int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(ta, tb, p);
+  ++g_launch_count;
+  SR_CHECK_CUDA(cudaGetLastError());
+  return SR_OK;
+}
+
+template <int BN>
+static int dispatch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+  const sr_epilogue_t& e = p.e;
+  switch (e.kind) {
+    case SR_EPI_BIAS:
+      return e.out_bf16 ? launch_gemm<BN, SR_EPI_BIAS, true>(ta, tb, p, st)
+                        : launch_gemm<BN, SR_EPI_BIAS, false>(ta, tb, p, st);
+    case SR_EPI_BIAS_GELU:
+      return e.out_bf16 ? launch_gemm<BN, SR_EPI_BIAS_GELU, true>(ta, tb, p, st)
+                        : launch_gemm<BN, SR_EPI_BIAS_GELU, false>(ta, tb, p, st);
+    case SR_EPI_LS_RESIDUAL:
+      return launch_gemm<BN, SR_EPI_LS_RESIDUAL, false>(ta, tb, p, st);
+    case SR_EPI_QKV:
+      return launch_gemm<BN, SR_EPI_QKV, true>(ta, tb, p, st);
+  }
+  return fail(SR_ERR_SHAPE, "sr_gemm_bf16: unknown epilogue kind %d", e.kind);
+}
+
+}  // namespace sr
+
+extern "C" int sr_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int64_t M, int64_t N, int64_t K,
+                            const sr_epilogue_t* epi, void* stream) {
+  using namespace sr;
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(A && W && epi && epi->out, "sr_gemm_bf16: null pointer");
+  SR_REQUIRE(M > 0 && N > 0 && K > 0, "sr_gemm_bf16: empty problem M=%lld N=%lld K=%lld", (long long)M, (long long)N,
+             (long long)K);
+  SR_REQUIRE(K % kBK == 0, "sr_gemm_bf16: K=%lld must be a multiple of 64", (long long)K);
+  SR_REQUIRE(N % 128 == 0, "sr_gemm_bf16: N=%lld must be a multiple of 128", (long long)N);
+  SR_REQUIRE(lda % 8 == 0 && ldw % 8 == 0 && lda >= K && ldw >= K, "sr_gemm_bf16: lda/ldw must be >= K and multiples of 8");
+  SR_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0,
+             "sr_gemm_bf16: A and W must be 16-byte aligned");
+  SR_REQUIRE(M < (1ll << 31) && N < (1ll << 31), "sr_gemm_bf16: M, N must fit int32");
+  const sr_epilogue_t& e = *epi;
+  const int out_elt = (e.kind == SR_EPI_LS_RESIDUAL || !e.out_bf16) ? 4 : 2;
+  SR_REQUIRE((reinterpret_cast<uintptr_t>(e.out) & 15) == 0 && (e.ldo * out_elt) % 16 == 0 && e.ldo >= N,
+             "sr_gemm_bf16: out must be 16-byte aligned with a 16-byte multiple row stride >= N");
+  if (e.kind == SR_EPI_LS_RESIDUAL) {
+    SR_REQUIRE(e.resid && (reinterpret_cast<uintptr_t>(e.resid) & 15) == 0 && e.ldr % 4 == 0,
+               "sr_gemm_bf16: LS_RESIDUAL needs a 16-byte aligned fp32 residual");
+  }
+  if (e.kind == SR_EPI_QKV) {
+    SR_REQUIRE(e.head_dim == 64, "sr_gemm_bf16: QKV epilogue supports head_dim 64 (got %d)", e.head_dim);
+    SR_REQUIRE(e.out_bf16, "sr_gemm_bf16: QKV epilogue writes bf16");
+    SR_REQUIRE(e.qkv_dim > 0 && e.qkv_dim % 64 == 0 && e.col_offset % 64 == 0 && e.col_offset + N <= 3 * e.qkv_dim,
+               "sr_gemm_bf16: QKV epilogue column mapping out of range");
+    if (e.qk_norm) SR_REQUIRE(e.qn_w && e.qn_b && e.kn_w && e.kn_b, "sr_gemm_bf16: qk_norm needs q/k norm parameters");
+    if (e.rope) SR_REQUIRE(e.rope_cos && e.rope_sin && e.pos, "sr_gemm_bf16: rope needs tables and positions");
+  }
+
+  CUtensorMap ta, tb;
+  const int BN = (N % 256 == 0) ? 256 : 128;
+  {
+    uint64_t dims[2] = {static_cast<uint64_t>(K), static_cast<uint64_t>(M)};
+    uint64_t strides[1] = {static_cast<uint64_t>(lda) * 2};
+    uint32_t box[2] = {kBK, kBM};
+    if (int rc = make_tmap_bf16(&ta, A, 2, dims, strides, box)) return rc;
+  }
+  {
+    uint64_t dims[2] = {static_cast<uint64_t>(K), static_cast<uint64_t>(N)};
+    uint64_t strides[1] = {static_cast<uint64_t>(ldw) * 2};
+    uint32_t box[2] = {kBK, static_cast<uint32_t>(BN)};
+    if (int rc = make_tmap_bf16(&tb, W, 2, dims, strides, box)) return rc;
+  }
+  GemmParams p;
+  p.M = static_cast<int>(M);
+  p.N = static_cast<int>(N);
+  p.K = static_cast<int>(K);
+  p.e = e;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  return BN == 256 ? dispatch_gemm<256>(ta, tb, p, st) : dispatch_gemm<128>(ta, tb, p, st);
+}

@@ -1,0 +1,226 @@
+"""Thin torch-tensor wrappers over the C-ABI (include/sailrecon_b200.h).
+
+PyTorch is only the plumbing here: it owns device memory and the stream.  Every function below hands raw
+device pointers, row strides and the current CUDA stream to libsailrecon_b200.so and raises if the call fails.
+Nothing in this module computes with torch ops; there is no fallback path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import SR_EPI_BIAS, SR_EPI_BIAS_GELU, SR_EPI_LS_RESIDUAL, SR_EPI_QKV, SrAttn, SrEpilogue
+
+__all__ = [
+    "layernorm", "gemm", "attention", "gather_rows", "copy_cols", "cast_bf16", "adaln_modulate",
+    "QkvEpilogue", "num_kernel_launches",
+]
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _rows2d(t: torch.Tensor, dtype, name: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"sailrecon_b200: {name} must be a CUDA tensor (no CPU fallback)")
+    if t.dtype != dtype:
+        raise TypeError(f"sailrecon_b200: {name} must be {dtype}, got {t.dtype}")
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"sailrecon_b200: {name} must be 2-D with unit inner stride, got {tuple(t.shape)} {t.stride()}")
+
+
+def _vec(t: Optional[torch.Tensor], n: int, name: str) -> None:
+    if t is None:
+        return
+    if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == n):
+        raise ValueError(f"sailrecon_b200: {name} must be a contiguous fp32 CUDA vector of {n} elements")
+
+
+def num_kernel_launches() -> int:
+    return int(_lib.load().sr_num_kernel_launches())
+
+
+# ------------------------------------------------------------------------------------------------ LayerNorm
+def layernorm(x: torch.Tensor, weight: Optional[torch.Tensor], bias: Optional[torch.Tensor], eps: float,
+              out: torch.Tensor, idx: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """out[r] = LayerNorm(x[idx[r]] if idx is not None else x[r]); out dtype bf16 or fp32 picks the store."""
+    _rows2d(x, torch.float32, "x")
+    rows = out.shape[0]
+    Cdim = x.shape[1]
+    _rows2d(out, out.dtype, "out")
+    if out.dtype not in (torch.bfloat16, torch.float32) or out.shape[1] != Cdim:
+        raise ValueError("sailrecon_b200: layernorm out must be bf16/fp32 [rows, C]")
+    _vec(weight, Cdim, "weight")
+    _vec(bias, Cdim, "bias")
+    if idx is not None:
+        if not (idx.is_cuda and idx.dtype == torch.int32 and idx.is_contiguous() and idx.numel() == rows):
+            raise ValueError("sailrecon_b200: idx must be a contiguous int32 CUDA vector with one entry per output row")
+    elif x.shape[0] != rows:
+        raise ValueError("sailrecon_b200: layernorm x/out row mismatch")
+    lib = _lib.load()
+    _lib.check(lib.sr_layernorm_gather_fwd(x.data_ptr(), x.stride(0), _ptr(idx), _ptr(weight), _ptr(bias), out.data_ptr(),
+                                           int(out.dtype == torch.bfloat16), out.stride(0), rows, Cdim, float(eps),
+                                           _stream()), "layernorm")
+    return out
+
+
+def adaln_modulate(x: torch.Tensor, mod: torch.Tensor, eps: float, out: torch.Tensor) -> torch.Tensor:
+    """camera_head.py:157-160: gate * (LN_noaffine(x) * (1 + scale) + shift) + x with mod = [shift|scale|gate]."""
+    _rows2d(x, torch.float32, "x")
+    _rows2d(mod, torch.float32, "mod")
+    _rows2d(out, torch.float32, "out")
+    rows, Cdim = x.shape
+    if not (x.is_contiguous() and mod.is_contiguous() and out.is_contiguous() and mod.shape == (rows, 3 * Cdim)
+            and out.shape == x.shape):
+        raise ValueError("sailrecon_b200: adaln_modulate needs contiguous x [R,C], mod [R,3C], out [R,C]")
+    _lib.check(_lib.load().sr_adaln_modulate_f32(x.data_ptr(), mod.data_ptr(), out.data_ptr(), rows, Cdim, float(eps),
+                                                 _stream()), "adaln_modulate")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ GEMM
+class QkvEpilogue:
+    """Arguments of the fused q/k LayerNorm + 2D-RoPE epilogue (attention.py:78-82)."""
+
+    def __init__(self, qkv_dim: int, col_offset: int = 0, head_dim: int = 64, q_norm=None, k_norm=None, qk_eps: float = 1e-5,
+                 rope_cos: Optional[torch.Tensor] = None, rope_sin: Optional[torch.Tensor] = None,
+                 pos: Optional[torch.Tensor] = None):
+        self.qkv_dim, self.col_offset, self.head_dim = qkv_dim, col_offset, head_dim
+        self.q_norm, self.k_norm, self.qk_eps = q_norm, k_norm, qk_eps      # (weight, bias) pairs or None
+        self.rope_cos, self.rope_sin, self.pos = rope_cos, rope_sin, pos
+
+
+def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor, kind: int = SR_EPI_BIAS,
+         gamma: Optional[torch.Tensor] = None, resid: Optional[torch.Tensor] = None,
+         qkv: Optional[QkvEpilogue] = None) -> torch.Tensor:
+    """out = epilogue(a @ w.T + bias).  a/w both bf16 -> tcgen05 path; both fp32 -> SIMT fp32 path."""
+    if a.dtype != w.dtype or a.dtype not in (torch.bfloat16, torch.float32):
+        raise TypeError(f"sailrecon_b200: gemm operands must both be bf16 or both fp32, got {a.dtype} / {w.dtype}")
+    _rows2d(a, a.dtype, "a")
+    _rows2d(w, w.dtype, "w")
+    _rows2d(out, out.dtype, "out")
+    M, K = a.shape
+    N = w.shape[0]
+    if w.shape[1] != K or out.shape != (M, N):
+        raise ValueError(f"sailrecon_b200: gemm shape mismatch a{tuple(a.shape)} w{tuple(w.shape)} out{tuple(out.shape)}")
+    _vec(bias, N, "bias")
+    _vec(gamma, N, "gamma")
+    e = SrEpilogue()
+    e.kind, e.out_bf16 = kind, int(out.dtype == torch.bfloat16)
+    e.out, e.ldo = out.data_ptr(), out.stride(0)
+    e.bias, e.gamma = _ptr(bias), _ptr(gamma)
+    if kind == SR_EPI_LS_RESIDUAL:
+        if resid is None or out.dtype != torch.float32:
+            raise ValueError("sailrecon_b200: LS_RESIDUAL needs an fp32 residual and fp32 out")
+        _rows2d(resid, torch.float32, "resid")
+        if resid.shape != (M, N):
+            raise ValueError("sailrecon_b200: residual shape mismatch")
+        e.resid, e.ldr = resid.data_ptr(), resid.stride(0)
+    keep = []
+    if kind == SR_EPI_QKV:
+        if qkv is None:
+            raise ValueError("sailrecon_b200: QKV epilogue arguments missing")
+        e.qkv_dim, e.col_offset, e.head_dim = qkv.qkv_dim, qkv.col_offset, qkv.head_dim
+        e.qk_norm = int(qkv.q_norm is not None)
+        if qkv.q_norm is not None:
+            for t in (*qkv.q_norm, *qkv.k_norm):
+                _vec(t, qkv.head_dim, "q/k norm parameter")
+            e.qn_w, e.qn_b = qkv.q_norm[0].data_ptr(), qkv.q_norm[1].data_ptr()
+            e.kn_w, e.kn_b = qkv.k_norm[0].data_ptr(), qkv.k_norm[1].data_ptr()
+        e.qk_eps = float(qkv.qk_eps)
+        e.rope = int(qkv.rope_cos is not None)
+        if qkv.rope_cos is not None:
+            cos, sin, pos = qkv.rope_cos, qkv.rope_sin, qkv.pos
+            if not (cos.is_cuda and cos.dtype == torch.float32 and cos.is_contiguous() and cos.shape == sin.shape
+                    and cos.dim() == 2 and cos.shape[1] == qkv.head_dim // 4):
+                raise ValueError("sailrecon_b200: rope tables must be fp32 [max_pos, head_dim/4]")
+            if not (pos.is_cuda and pos.dtype == torch.int32 and pos.is_contiguous() and pos.shape == (M, 2)):
+                raise ValueError("sailrecon_b200: rope positions must be int32 [M, 2]")
+            e.rope_cos, e.rope_sin, e.rope_max_pos, e.pos = cos.data_ptr(), sin.data_ptr(), cos.shape[0], pos.data_ptr()
+            keep += [cos, sin, pos]
+    lib = _lib.load()
+    fn = lib.sr_gemm_bf16 if a.dtype == torch.bfloat16 else lib.sr_gemm_f32
+    _lib.check(fn(a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), M, N, K, C.byref(e), _stream()), "gemm")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ attention
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[torch.Tensor], num_heads: int,
+              head_dim: int, batch: int, q_len: int, kv_len: int, q_batch_stride: int = 0, kv_batch_stride: int = 0,
+              prefix_k: Optional[torch.Tensor] = None, prefix_v: Optional[torch.Tensor] = None, prefix_len: int = 0,
+              scale: Optional[float] = None, carry=None, carry_in: bool = False, carry_out: bool = False):
+    """Structured attention (see sr_attn in the header).  q/k/v are 2-D row views [rows, >= heads*head_dim]
+    (column slices of the fused qkv buffer are fine); bf16 -> tcgen05 flash kernel, fp32 -> SIMT kernel."""
+    dt = q.dtype
+    for name, t in (("q", q), ("k", k), ("v", v)):
+        _rows2d(t, dt, name)
+    if k.stride(0) != v.stride(0):
+        raise ValueError("sailrecon_b200: k and v must share a row stride")
+    a = SrAttn()
+    a.q, a.ldq = q.data_ptr(), q.stride(0)
+    a.k, a.v, a.ldkv = k.data_ptr(), v.data_ptr(), k.stride(0)
+    if prefix_k is not None and prefix_len > 0:
+        _rows2d(prefix_k, dt, "prefix_k")
+        _rows2d(prefix_v, dt, "prefix_v")
+        if prefix_k.stride(0) != prefix_v.stride(0) or prefix_k.shape[0] < prefix_len:
+            raise ValueError("sailrecon_b200: bad prefix K/V")
+        a.pk, a.pv, a.ldp, a.prefix_len = prefix_k.data_ptr(), prefix_v.data_ptr(), prefix_k.stride(0), prefix_len
+    if out is not None:
+        _rows2d(out, dt, "out")
+        a.out, a.ldo = out.data_ptr(), out.stride(0)
+    a.num_heads, a.head_dim, a.batch = num_heads, head_dim, batch
+    a.q_len, a.q_batch_stride = q_len, q_batch_stride or q_len
+    a.kv_len, a.kv_batch_stride = kv_len, kv_batch_stride or kv_len
+    need_q = (batch - 1) * a.q_batch_stride + q_len
+    need_kv = (batch - 1) * a.kv_batch_stride + kv_len
+    if q.shape[0] < need_q or k.shape[0] < need_kv or v.shape[0] < need_kv or (out is not None and out.shape[0] < need_q):
+        raise ValueError("sailrecon_b200: attention row ranges exceed the tensors")
+    a.scale = float(scale if scale is not None else head_dim ** -0.5)
+    if carry is not None:
+        m, l, acc = carry
+        a.carry_m, a.carry_l, a.carry_acc = m.data_ptr(), l.data_ptr(), acc.data_ptr()
+    a.carry_in, a.carry_out = int(carry_in), int(carry_out)
+    lib = _lib.load()
+    fn = lib.sr_attn_fwd_bf16 if dt == torch.bfloat16 else lib.sr_attn_fwd_f32
+    _lib.check(fn(C.byref(a), _stream()), "attention")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ re-layout
+def gather_rows(src: torch.Tensor, idx: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    _rows2d(src, torch.float32, "src")
+    _rows2d(out, torch.float32, "out")
+    if not (idx.is_cuda and idx.dtype == torch.int32 and idx.is_contiguous() and idx.numel() == out.shape[0]):
+        raise ValueError("sailrecon_b200: idx must be contiguous int32 CUDA, one per output row")
+    _lib.check(_lib.load().sr_gather_rows_f32(src.data_ptr(), src.stride(0), idx.data_ptr(), out.data_ptr(), out.stride(0),
+                                              out.shape[0], src.shape[1], _stream()), "gather_rows")
+    return out
+
+
+def copy_cols(src: torch.Tensor, dst: torch.Tensor, col_off: int) -> torch.Tensor:
+    """dst[:, col_off:col_off+C] = src (one half of the [.., 2C] concat outputs)."""
+    _rows2d(src, torch.float32, "src")
+    _rows2d(dst, torch.float32, "dst")
+    if src.shape[0] != dst.shape[0] or col_off + src.shape[1] > dst.shape[1]:
+        raise ValueError("sailrecon_b200: copy_cols shape mismatch")
+    _lib.check(_lib.load().sr_copy_cols_f32(src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0), col_off,
+                                            src.shape[0], src.shape[1], _stream()), "copy_cols")
+    return dst
+
+
+def cast_bf16(src: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _rows2d(src, torch.float32, "src")
+    if out is None:
+        out = torch.empty(src.shape, dtype=torch.bfloat16, device=src.device)
+    _rows2d(out, torch.bfloat16, "out")
+    _lib.check(_lib.load().sr_cast_f32_to_bf16(src.data_ptr(), src.stride(0), out.data_ptr(), out.stride(0), src.shape[0],
+                                               src.shape[1], _stream()), "cast_bf16")
+    return out
