@@ -35,6 +35,8 @@ NVCC_FLAGS = [
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr",
+    # mbarrier waits are bounded: a pipeline-protocol bug traps (CUDA error through the C-ABI) instead of hanging the GPU
+    "-DSR_DEBUG_HANG_TRAP",
 ]
 
 

@@ -1,0 +1,269 @@
+"""GPU parity of every C-ABI entry point against the CPU oracle (oracle/sailrecon_oracle.py) on seeded inputs.
+
+Tolerances: fp32 paths 1e-5 relative L2 (summation order only); bf16 tensor-core paths are compared with the
+oracle's bf16-rounding emulation and must agree to 4e-3 relative L2 (one bf16 ulp = 3.9e-3; the end-to-end budget
+of north_star is 2e-2).  Integer / copy kernels: bit-exact.
+"""
+import math
+
+import pytest
+import torch
+
+import sailrecon_oracle as O
+from golden_common import rel_l2
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda"
+
+
+def _ops():
+    from sailrecon_b200 import ops
+    return ops
+
+
+def _g(seed):
+    return torch.Generator().manual_seed(seed)
+
+
+def bf(x):
+    return x.to(torch.bfloat16)
+
+
+# ------------------------------------------------------------------------------------------------ LayerNorm
+@pytest.mark.parametrize("C,rows", [(1024, 1374 * 2 + 3), (2048, 37), (64, 100), (128, 25)])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_layernorm(C, rows, out_dtype):
+    ops = _ops()
+    g = _g(1)
+    x = torch.randn(rows, C, generator=g) * 3 + 0.5
+    w, b = 1 + 0.1 * torch.randn(C, generator=g), 0.1 * torch.randn(C, generator=g)
+    ref = O.layer_norm(x, w, b, 1e-5)
+    out = torch.empty(rows, C, dtype=out_dtype, device=DEV)
+    ops.layernorm(x.to(DEV), w.to(DEV), b.to(DEV), 1e-5, out)
+    if out_dtype == torch.bfloat16:
+        assert torch.equal(out.cpu(), bf(ref)) or rel_l2(out.cpu().float(), bf(ref).float()) < 1e-3
+    else:
+        assert rel_l2(out.cpu(), ref) < 1e-6
+
+
+def test_layernorm_gather_and_noaffine():
+    ops = _ops()
+    g = _g(2)
+    x = torch.randn(500, 1024, generator=g)
+    idx = torch.randperm(500, generator=g)[:123].to(torch.int32)
+    out = torch.empty(123, 1024, dtype=torch.float32, device=DEV)
+    ops.layernorm(x.to(DEV), None, None, 1e-6, out, idx=idx.to(DEV))
+    assert rel_l2(out.cpu(), O.layer_norm(x[idx.long()], None, None, 1e-6)) < 1e-6
+
+
+def test_adaln_modulate():
+    ops = _ops()
+    g = _g(3)
+    x, mod = torch.randn(37, 2048, generator=g), torch.randn(37, 3 * 2048, generator=g)
+    shift, scale, gate = mod.chunk(3, dim=-1)
+    ref = gate * (O.layer_norm(x, None, None, 1e-6) * (1 + scale) + shift) + x
+    out = torch.empty(37, 2048, device=DEV)
+    ops.adaln_modulate(x.to(DEV), mod.to(DEV), 1e-6, out)
+    assert rel_l2(out.cpu(), ref) < 1e-6
+
+
+# ------------------------------------------------------------------------------------------------ re-layout
+def test_gather_copy_cast_bit_exact():
+    ops = _ops()
+    g = _g(4)
+    src = torch.randn(300, 1024, generator=g)
+    idx = torch.randint(0, 300, (77,), generator=g).to(torch.int32)
+    out = torch.empty(77, 1024, device=DEV)
+    ops.gather_rows(src.to(DEV), idx.to(DEV), out)
+    assert torch.equal(out.cpu(), src[idx.long()])
+    dst = torch.zeros(300, 2048, device=DEV)
+    ops.copy_cols(src.to(DEV), dst, 1024)
+    assert torch.equal(dst.cpu()[:, 1024:], src) and float(dst[:, :1024].abs().sum()) == 0.0
+    assert torch.equal(ops.cast_bf16(src.to(DEV)).cpu(), bf(src))
+
+
+# ------------------------------------------------------------------------------------------------ GEMM
+def _gemm_inputs(M, N, K, seed):
+    g = _g(seed)
+    a = torch.randn(M, K, generator=g)
+    w = torch.randn(N, K, generator=g) / math.sqrt(K)
+    b = 0.1 * torch.randn(N, generator=g)
+    return a, w, b
+
+
+@pytest.mark.parametrize("M,N,K", [(1374 * 2, 1024, 1024), (300, 4096, 1024), (129, 1024, 4096), (1374, 3072, 1024),
+                                   (64, 128, 64)])
+def test_gemm_bf16_bias(M, N, K):
+    ops = _ops()
+    a, w, b = _gemm_inputs(M, N, K, 5)
+    ref = O.linear(a, w, b, True)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    ops.gemm(bf(a).to(DEV), bf(w).to(DEV), bf(b).float().to(DEV), out)
+    assert rel_l2(out.cpu().float(), ref) < 4e-3
+    out32 = torch.empty(M, N, dtype=torch.float32, device=DEV)
+    ops.gemm(bf(a).to(DEV), bf(w).to(DEV), bf(b).float().to(DEV), out32)
+    exact = bf(a).double() @ bf(w).double().t() + bf(b).double()
+    assert rel_l2(out32.cpu(), exact) < 1e-5
+
+
+def test_gemm_bf16_gelu_and_ls_residual():
+    ops = _ops()
+    from sailrecon_b200._lib import SR_EPI_BIAS_GELU, SR_EPI_LS_RESIDUAL
+    M, N, K = 1000, 4096, 1024
+    a, w, b = _gemm_inputs(M, N, K, 6)
+    ref = bf(O.gelu_erf(O.linear(a, w, b, True))).float()
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    ops.gemm(bf(a).to(DEV), bf(w).to(DEV), bf(b).float().to(DEV), out, kind=SR_EPI_BIAS_GELU)
+    assert rel_l2(out.cpu().float(), ref) < 4e-3
+    # LayerScale + residual, in place on the fp32 residual stream
+    M, N, K = 777, 1024, 4096
+    a, w, b = _gemm_inputs(M, N, K, 7)
+    g = _g(8)
+    gamma, resid = 0.5 + torch.rand(N, generator=g), torch.randn(M, N, generator=g)
+    ref = resid + gamma * O.linear(a, w, b, True)
+    x = resid.clone().to(DEV)
+    ops.gemm(bf(a).to(DEV), bf(w).to(DEV), bf(b).float().to(DEV), x, kind=SR_EPI_LS_RESIDUAL, gamma=gamma.to(DEV), resid=x)
+    assert rel_l2(x.cpu(), ref) < 2e-3
+
+
+def _rope_tables_dev(max_pos):
+    cos, sin = O.rope_tables(max_pos, 32, 100.0)
+    return cos[:, :16].contiguous().to(DEV), sin[:, :16].contiguous().to(DEV)
+
+
+@pytest.mark.parametrize("M,col_offset", [(1374, 0), (305 * 2, 1024)])
+def test_gemm_qkv_epilogue(M, col_offset):
+    """bias -> bf16 -> LayerNorm(64) on q,k -> 2D RoPE -> bf16, v untouched (attention.py:71-82)."""
+    ops = _ops()
+    from sailrecon_b200._lib import SR_EPI_QKV
+    Cm, H = 1024, 16
+    g = _g(9)
+    x = torch.randn(M, Cm, generator=g)
+    p = {"qkv.weight": torch.randn(3 * Cm, Cm, generator=g) / 32, "qkv.bias": 0.1 * torch.randn(3 * Cm, generator=g),
+         "q_norm.weight": 1 + 0.1 * torch.randn(64, generator=g), "q_norm.bias": 0.1 * torch.randn(64, generator=g),
+         "k_norm.weight": 1 + 0.1 * torch.randn(64, generator=g), "k_norm.bias": 0.1 * torch.randn(64, generator=g)}
+    pos = torch.stack([torch.randint(0, 38, (M,), generator=g), torch.randint(0, 38, (M,), generator=g)], dim=-1)
+    q, k, v = O.qkv_heads(x, p, "", H, pos, True, True, True)
+    ref = torch.cat([t.transpose(0, 1).reshape(M, Cm) for t in (q, k, v)], dim=1)            # [M, 3C] fp32
+    ref = bf(ref).float()[:, col_offset:]
+    N = 3 * Cm - col_offset
+    out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    cos, sin = _rope_tables_dev(38)
+    dv = lambda t: t.to(DEV)
+    epi = ops.QkvEpilogue(Cm, col_offset, 64, (dv(p["q_norm.weight"]), dv(p["q_norm.bias"])),
+                          (dv(p["k_norm.weight"]), dv(p["k_norm.bias"])), 1e-5, cos, sin, pos.to(torch.int32).to(DEV))
+    ops.gemm(bf(x).to(DEV), bf(p["qkv.weight"][col_offset:]).to(DEV), bf(p["qkv.bias"][col_offset:]).float().to(DEV), out,
+             kind=SR_EPI_QKV, qkv=epi)
+    assert rel_l2(out.cpu().float(), ref) < 6e-3
+
+
+def test_gemm_f32_all_epilogues():
+    ops = _ops()
+    from sailrecon_b200._lib import SR_EPI_BIAS_GELU, SR_EPI_LS_RESIDUAL
+    for (M, N, K) in [(37, 9, 1024), (37, 2048, 9), (100, 300, 130)]:
+        a, w, b = _gemm_inputs(M, N, K, 10)
+        out = torch.empty(M, N, device=DEV)
+        ops.gemm(a.to(DEV), w.to(DEV), b.to(DEV), out)
+        assert rel_l2(out.cpu(), O.linear(a, w, b, False)) < 1e-5
+        ops.gemm(a.to(DEV), w.to(DEV), b.to(DEV), out, kind=SR_EPI_BIAS_GELU)
+        assert rel_l2(out.cpu(), O.gelu_erf(O.linear(a, w, b, False))) < 1e-5
+        g = _g(11)
+        gamma, resid = torch.rand(N, generator=g), torch.randn(M, N, generator=g)
+        x = resid.clone().to(DEV)
+        ops.gemm(a.to(DEV), w.to(DEV), b.to(DEV), x, kind=SR_EPI_LS_RESIDUAL, gamma=gamma.to(DEV), resid=x)
+        assert rel_l2(x.cpu(), resid + gamma * O.linear(a, w, b, False)) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------------ attention
+def _attn_ref(q, k, v, H, d, segs, prefix=None, bf16=True):
+    """q,k,v [rows, H*d]; segs = list of (q0, q_len, k0, kv_len); prefix = (pk, pv, len)."""
+    out = torch.zeros(q.shape[0], H * d)
+    hv = lambda t: t.reshape(t.shape[0], H, d).transpose(0, 1)
+    for (q0, ql, k0, kl) in segs:
+        kk, vv = k[k0:k0 + kl], v[k0:k0 + kl]
+        if prefix is not None:
+            kk, vv = torch.cat([prefix[0][:prefix[2]], kk]), torch.cat([prefix[1][:prefix[2]], vv])
+        o = O.sdpa(hv(q[q0:q0 + ql]), hv(kk), hv(vv), None, bf16)
+        out[q0:q0 + ql] = o.transpose(0, 1).reshape(ql, H * d)
+    return out
+
+
+@pytest.mark.parametrize("batch,L", [(3, 1374), (1, 2 * 1374), (2, 130), (1, 128), (4, 25)])
+def test_attention_bf16_segments(batch, L):
+    ops = _ops()
+    H, d = 16, 64
+    g = _g(12)
+    qkv = torch.randn(batch * L, 3 * H * d, generator=g)
+    qkv[:, : 2 * H * d] *= 1.5
+    qkv_d = bf(qkv).to(DEV)
+    q, k, v = (qkv_d[:, i * H * d:(i + 1) * H * d] for i in range(3))
+    out = torch.empty(batch * L, H * d, dtype=torch.bfloat16, device=DEV)
+    ops.attention(q, k, v, out, H, d, batch, L, L, L, L)
+    qc, kc, vc = (bf(qkv[:, i * H * d:(i + 1) * H * d]).float() for i in range(3))
+    ref = _attn_ref(qc, kc, vc, H, d, [(b * L, L, b * L, L) for b in range(batch)])
+    assert rel_l2(out.cpu().float(), ref) < 6e-3
+
+
+@pytest.mark.parametrize("Nq,P,prefix_len", [(3, 1374, 2 * 305), (2, 25, 22), (1, 300, 128)])
+def test_attention_bf16_prefix(Nq, P, prefix_len):
+    """reloc structure: each query frame attends to [scene prefix ; itself] (aggregator.py:302-311, 672-741)."""
+    ops = _ops()
+    H, d = 16, 64
+    g = _g(13)
+    qkv = torch.randn(Nq * P, 3 * H * d, generator=g)
+    pkv = torch.randn(prefix_len, 2 * H * d, generator=g)
+    qkv_d, pkv_d = bf(qkv).to(DEV), bf(pkv).to(DEV)
+    q, k, v = (qkv_d[:, i * H * d:(i + 1) * H * d] for i in range(3))
+    out = torch.empty(Nq * P, H * d, dtype=torch.bfloat16, device=DEV)
+    ops.attention(q, k, v, out, H, d, Nq, P, P, P, P, prefix_k=pkv_d[:, :H * d], prefix_v=pkv_d[:, H * d:], prefix_len=prefix_len)
+    qc, kc, vc = (bf(qkv[:, i * H * d:(i + 1) * H * d]).float() for i in range(3))
+    pk, pv = bf(pkv[:, :H * d]).float(), bf(pkv[:, H * d:]).float()
+    ref = _attn_ref(qc, kc, vc, H, d, [(b * P, P, b * P, P) for b in range(Nq)], prefix=(pk, pv, prefix_len))
+    assert rel_l2(out.cpu().float(), ref) < 6e-3
+
+
+def test_attention_bf16_carry_equals_single_pass():
+    """Ring / split-KV carry: attending to K/V in two halves with (m, l, acc) carried == one pass."""
+    ops = _ops()
+    H, d, L = 16, 64, 700
+    g = _g(14)
+    qkv = bf(torch.randn(L, 3 * H * d, generator=g)).to(DEV)
+    q, k, v = (qkv[:, i * H * d:(i + 1) * H * d] for i in range(3))
+    one = torch.empty(L, H * d, dtype=torch.bfloat16, device=DEV)
+    ops.attention(q, k, v, one, H, d, 1, L, L)
+    m = torch.empty(H, L, device=DEV)
+    l = torch.empty(H, L, device=DEV)
+    acc = torch.empty(L, H * d, device=DEV)
+    two = torch.empty(L, H * d, dtype=torch.bfloat16, device=DEV)
+    half = 333
+    ops.attention(q, k[:half], v[:half], None, H, d, 1, L, half, carry=(m, l, acc), carry_out=True)
+    ops.attention(q, k[half:], v[half:], two, H, d, 1, L, L - half, carry=(m, l, acc), carry_in=True)
+    assert rel_l2(two.float().cpu(), one.float().cpu()) < 4e-3
+
+
+@pytest.mark.parametrize("d,H", [(128, 16), (64, 2)])
+def test_attention_f32(d, H):
+    ops = _ops()
+    g = _g(15)
+    Na, Nq = 5, 7
+    x = torch.randn(Na + Nq, 3 * H * d, generator=g)
+    xd = x.to(DEV)
+    q, k, v = (xd[:, i * H * d:(i + 1) * H * d] for i in range(3))
+    out = torch.empty(Na + Nq, H * d, device=DEV)
+    ops.attention(q, k, v, out, H, d, 1, Na, Na)                                              # anchors see anchors
+    ops.attention(q[Na:], k[Na:], v[Na:], out[Na:], H, d, Nq, 1, 1, 1, 1, prefix_k=k, prefix_v=v, prefix_len=Na)
+    qc, kc, vc = (x[:, i * H * d:(i + 1) * H * d] for i in range(3))
+    hv = lambda t: t.reshape(t.shape[0], H, d).transpose(0, 1)
+    ref = O.sdpa(hv(qc), hv(kc), hv(vc), O.camera_mask(Na, Nq), False).transpose(0, 1).reshape(Na + Nq, H * d)
+    assert rel_l2(out.cpu(), ref) < 1e-5
+
+
+def test_errors_are_loud():
+    ops = _ops()
+    with pytest.raises(RuntimeError):
+        ops.layernorm(torch.zeros(4, 64), None, None, 1e-5, torch.zeros(4, 64))       # CPU tensor: no fallback
+    a = torch.zeros(8, 100, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(ValueError):
+        ops.gemm(a, torch.zeros(128, 100, dtype=torch.bfloat16, device=DEV), None,
+                 torch.zeros(8, 128, dtype=torch.bfloat16, device=DEV))               # K % 64 != 0
