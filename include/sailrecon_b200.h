@@ -47,6 +47,8 @@ int sr_layernorm_gather_fwd(const float* x, int64_t ldx, const int32_t* idx, con
 #define SR_EPI_BIAS 0          /* y = acc + bias                                 (proj of a plain Linear)   */
 #define SR_EPI_BIAS_GELU 1     /* y = gelu_erf(round(acc + bias))                (mlp.py:35-36)             */
 #define SR_EPI_LS_RESIDUAL 2   /* out = resid + gamma * round(acc + bias)        (block.py:110-111, fp32)   */
+#define SR_EPI_BIAS_SILU 4     /* y = silu(acc + bias): embed_pose feeding poseLN_modulation's SiLU
+                                  (camera_head.py:72-74,146-155); fp32 path only                           */
 #define SR_EPI_QKV 3           /* bias, then per-head LayerNorm(d) on q,k (attention.py:78) and 2D RoPE
                                   (attention.py:80-82, rope.py:165-207); v = bias only                     */
 typedef struct sr_epilogue {
@@ -129,6 +131,31 @@ int sr_cast_f32_to_bf16(const float* src, int64_t lds, void* dst, int64_t ldd, i
  * mod = [rows, 3C] holding (shift | scale | gate).                                                         */
 int sr_adaln_modulate_f32(const float* x, const float* mod, float* out, int64_t rows, int64_t C, float eps,
                           void* stream);
+
+
+/* LayerScale.forward on its own (layer_scale.py:23): out[r, c] = x[r, c] * gamma[c]; contiguous fp32 (inside a
+ * Block the scale is folded into the GEMM epilogue instead).                                                  */
+int sr_scale_cols_f32(const float* x, const float* gamma, float* out, int64_t rows, int64_t C, void* stream);
+
+/* ---- 2D RoPE (rope.py:69-207) --------------------------------------------------------------------------- */
+/* cos/sin fp32 [max_pos, quarter_dim]: entry (p, f) = cos/sin(p * frequency^(-f/quarter_dim)) (rope.py:107-123
+ * before the duplication of :119; the kernels index the duplicate by f mod quarter_dim).                    */
+int sr_rope_table_build(float* cos_out, float* sin_out, int32_t max_pos, int32_t quarter_dim, float frequency,
+                        void* stream);
+/* RotaryPositionEmbedding2D.forward (rope.py:165-207): x, out fp32 [B, H, N, d] contiguous; pos int32 [B, N, 2]. */
+int sr_rope2d_f32(const float* x, float* out, const int32_t* pos, const float* rope_cos, const float* rope_sin,
+                  int32_t max_pos, int64_t B, int64_t H, int64_t N, int64_t d, void* stream);
+
+/* ---- patch-embed front end (aggregator.py:267-271, patch_embed.py:62-84) --------------------------------- */
+/* out[(s*h + py)*w + px, (c*patch + ky)*patch + kx] = (images[s, c, py*patch+ky, px*patch+kx] - mean[c]) / std[c];
+ * columns [3*patch*patch, ldo) are zero-filled (K padding for the tensor-core GEMM).  images fp32 [S,3,H,W];
+ * out bf16 or fp32 [S*h*w, ldo]; mean3/std3 are HOST pointers to 3 floats.                                    */
+int sr_patchify(const float* images, void* out, int out_bf16, int64_t ldo, int64_t S, int64_t H, int64_t W,
+                int32_t patch, const float* mean3, const float* std3, void* stream);
+
+/* ---- camera head pose accumulation (camera_head.py:172-184, head_act.py:12-37) -----------------------------
+ * pred = first ? delta : pred + delta; activated = [pred[:, :7], relu(pred[:, 7:9])]; all fp32 [rows, 9].     */
+int sr_pose_update(float* pred, const float* delta, float* activated, int64_t rows, int32_t first, void* stream);
 
 #ifdef __cplusplus
 }

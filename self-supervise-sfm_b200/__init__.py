@@ -6,8 +6,9 @@ the shim ``sailrecon_b200.py`` at the repository root, which loads this package 
 Layout:
   csrc/      hand-written CUDA kernels + the C-ABI (include/sailrecon_b200.h) -> lib/libsailrecon_b200.so
   _lib.py    ctypes binding;  ops.py  torch-tensor wrappers (pointers + strides + stream, nothing else)
-  layers/    Block / Attention / Mlp / LayerScale / RotaryPositionEmbedding2D / PositionGetter   (sailrecon/layers)
-  models/    Aggregator (+ DINOv2 patch embed)                                                    (sailrecon/models)
+  engine.py  the fused per-block launch schedule and the structured-attention description
+  layers/    Block / Attention / Mlp / LayerScale / RotaryPositionEmbedding2D / PositionGetter / DINOv2 ViT  (sailrecon/layers)
+  models/    Aggregator                                                                           (sailrecon/models)
   heads/     CameraHead                                                                           (sailrecon/heads)
   parallel.py  frame-sharded (sequence-parallel) global attention with ring K/V exchange
 """

@@ -12,7 +12,7 @@ import os
 from . import build as _build
 
 SR_OK, SR_ERR_SHAPE, SR_ERR_ARCH, SR_ERR_CUDA = 0, 1, 2, 3
-SR_EPI_BIAS, SR_EPI_BIAS_GELU, SR_EPI_LS_RESIDUAL, SR_EPI_QKV = 0, 1, 2, 3
+SR_EPI_BIAS, SR_EPI_BIAS_GELU, SR_EPI_LS_RESIDUAL, SR_EPI_QKV, SR_EPI_BIAS_SILU = 0, 1, 2, 3, 4
 
 _vp, _i64, _i32, _f32 = C.c_void_p, C.c_int64, C.c_int32, C.c_float
 
@@ -60,6 +60,11 @@ SIGNATURES = {
     "sr_copy_cols_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp]),
     "sr_cast_f32_to_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _vp]),
     "sr_adaln_modulate_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _f32, _vp]),
+    "sr_scale_cols_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _vp]),
+    "sr_rope_table_build": (C.c_int, [_vp, _vp, _i32, _i32, _f32, _vp]),
+    "sr_rope2d_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i64, _i64, _i64, _i64, _vp]),
+    "sr_patchify": (C.c_int, [_vp, _vp, C.c_int, _i64, _i64, _i64, _i64, _i32, C.POINTER(_f32), C.POINTER(_f32), _vp]),
+    "sr_pose_update": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
 }
 
 _lib = None

@@ -24,6 +24,7 @@ SOURCES = [
     "sr_api.cu",
     "layernorm.cu",
     "relayout.cu",
+    "misc.cu",
     "gemm_f32.cu",
     "attn_f32.cu",
     "gemm_tc.cu",

@@ -71,6 +71,7 @@ gemm_f32_kernel(const GemmF32Params p) {
       if (gn >= p.N) continue;
       float y = acc[i][j] + (e.bias ? __ldg(e.bias + gn) : 0.f);
       if (EPI == SR_EPI_BIAS_GELU) y = gelu_erf(y);
+      if (EPI == SR_EPI_BIAS_SILU) y = y / (1.f + expf(-y));
       if (EPI == SR_EPI_LS_RESIDUAL) {
         const float g = e.gamma ? __ldg(e.gamma + gn) : 1.f;
         y = e.resid[static_cast<int64_t>(gm) * e.ldr + gn] + g * y;
@@ -140,6 +141,7 @@ extern "C" int sr_gemm_f32(const float* A, int64_t lda, const float* W, int64_t 
     case SR_EPI_BIAS: gemm_f32_kernel<SR_EPI_BIAS><<<grid, 256, 0, st>>>(p); break;
     case SR_EPI_BIAS_GELU: gemm_f32_kernel<SR_EPI_BIAS_GELU><<<grid, 256, 0, st>>>(p); break;
     case SR_EPI_LS_RESIDUAL: gemm_f32_kernel<SR_EPI_LS_RESIDUAL><<<grid, 256, 0, st>>>(p); break;
+    case SR_EPI_BIAS_SILU: gemm_f32_kernel<SR_EPI_BIAS_SILU><<<grid, 256, 0, st>>>(p); break;
     default: return fail(SR_ERR_SHAPE, "sr_gemm_f32: unknown epilogue kind %d", epi->kind);
   }
   ++g_launch_count;

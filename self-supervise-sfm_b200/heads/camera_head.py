@@ -1,0 +1,108 @@
+"""CameraHead — API mirror of sailrecon/heads/camera_head.py (CameraHead :19-186, modulate :189-194,
+build_lr_mask :197-228) on the B200 kernel library.
+
+Runs in fp32, as the reference does (SailRecon disables autocast around the heads, sail_recon.py:119-121).  The
+boolean mask of build_lr_mask is consumed structurally: anchors attend to anchors; every query camera token attends
+to the anchors and to itself — two launches of the structured attention kernel instead of a dense masked SDPA.
+Per refinement iteration: embed_pose+SiLU (one GEMM epilogue), the 2048->6144 modulation GEMM, one fused
+adaLN-modulate-gate-residual kernel, 4 trunk blocks (7 launches each), trunk_norm, pose_branch (2 GEMMs) and one
+accumulate+activate kernel.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from .. import engine, ops
+from .._lib import SR_EPI_BIAS, SR_EPI_BIAS_GELU, SR_EPI_BIAS_SILU
+from ..layers import Mlp
+from ..layers.block import Block
+
+
+class CameraHead(nn.Module):
+    def __init__(self, dim_in: int = 2048, trunk_depth: int = 4, pose_encoding_type: str = "absT_quaR_FoV",
+                 num_heads: int = 16, mlp_ratio: int = 4, init_values: float = 0.01, trans_act: str = "linear",
+                 quat_act: str = "linear", fl_act: str = "relu"):
+        super().__init__()
+        if pose_encoding_type == "absT_quaR_FoV":
+            self.target_dim = 9
+        else:
+            raise ValueError(f"Unsupported camera encoding type: {pose_encoding_type}")    # camera_head.py:43
+        if (trans_act, quat_act, fl_act) != ("linear", "linear", "relu"):
+            raise NotImplementedError("sailrecon_b200: CameraHead implements the activations SAIL-Recon configures "
+                                      "(trans/quat 'linear', FoV 'relu')")
+        self.trans_act, self.quat_act, self.fl_act = trans_act, quat_act, fl_act
+        self.trunk_depth = trunk_depth
+        self.trunk = nn.Sequential(*[Block(dim=dim_in, num_heads=num_heads, mlp_ratio=mlp_ratio, init_values=init_values)
+                                     for _ in range(trunk_depth)])
+        self.token_norm = nn.LayerNorm(dim_in)
+        self.trunk_norm = nn.LayerNorm(dim_in)
+        self.empty_pose_tokens = nn.Parameter(torch.zeros(1, 1, self.target_dim))
+        self.embed_pose = nn.Linear(self.target_dim, dim_in)
+        self.poseLN_modulation = nn.Sequential(nn.SiLU(), nn.Linear(dim_in, 3 * dim_in, bias=True))
+        self.adaln_norm = nn.LayerNorm(dim_in, elementwise_affine=False, eps=1e-6)
+        self.pose_branch = Mlp(in_features=dim_in, hidden_features=dim_in // 2, out_features=self.target_dim, drop=0)
+
+    def forward(self, aggregated_tokens_list, cam_token_last_layer: torch.Tensor, num_iterations: int = 4) -> list:
+        tokens = aggregated_tokens_list[-1]                                                # camera_head.py:103-109
+        pose_q = tokens[:, :, 0]
+        if pose_q.shape[0] != 1:
+            raise NotImplementedError("sailrecon_b200: batch size 1")
+        engine.require_cuda_f32(pose_q, "aggregated tokens")
+        engine.require_cuda_f32(cam_token_last_layer, "cam_token_last_layer")
+        Na, Nq = cam_token_last_layer.shape[1], pose_q.shape[1]
+        x_in = torch.cat([cam_token_last_layer[0], pose_q[0]], dim=0).contiguous()          # [T, C]
+        T, C = x_in.shape
+        dev = x_in.device
+        mode = "f32"
+        w, b, eps = engine.ln_params(self.token_norm)
+        x = torch.empty_like(x_in)
+        ops.layernorm(x_in, w, b, eps, x)                                                  # :110
+        # ~build_lr_mask (:112-116, :197-228) as structure: anchors | each query behind the anchors
+        calls = engine.MaskStructure(Na, 1, Nq).calls()
+        f32 = dict(dtype=torch.float32, device=dev)
+        emb = torch.empty(T, C, **f32)
+        mod = torch.empty(T, 3 * C, **f32)
+        y = torch.empty(T, C, **f32)
+        yn = torch.empty(T, C, **f32)
+        hid = torch.empty(T, self.pose_branch.fc1.weight.shape[0], **f32)
+        delta = torch.empty(T, self.target_dim, **f32)
+        pred = torch.empty(T, self.target_dim, **f32)
+        empty = self.empty_pose_tokens.detach()[0].expand(T, -1).contiguous()
+        tw, tb, teps = engine.ln_params(self.trunk_norm)
+        out = []
+        for it in range(num_iterations):                                                   # trunk_fn :143-184
+            inp = empty if it == 0 else pred
+            engine.linear_rows(self.embed_pose, inp, emb, mode, SR_EPI_BIAS_SILU)          # embed_pose + the SiLU of :72-74
+            engine.linear_rows(self.poseLN_modulation[1], emb, mod, mode, SR_EPI_BIAS)     # shift | scale | gate
+            ops.adaln_modulate(x, mod, float(self.adaln_norm.eps), y)                      # :157-161
+            for blk in self.trunk:
+                engine.run_block(blk, y, calls, None, mode, tag="cam.")                   # :163-166
+            ops.layernorm(y, tw, tb, teps, yn)
+            engine.linear_rows(self.pose_branch.fc1, yn, hid, mode, SR_EPI_BIAS_GELU)      # :168-170
+            engine.linear_rows(self.pose_branch.fc2, hid, delta, mode, SR_EPI_BIAS)
+            act = torch.empty(T, self.target_dim, **f32)
+            ops.pose_update(pred, delta, act, it == 0)                                     # :172-184
+            out.append(act[None, Na:])                                                     # query rows only, :118-121
+        return out
+
+    def trunk_fn(self, pose_tokens: torch.Tensor, attention_mask: torch.Tensor, num_iterations: int) -> list:
+        raise NotImplementedError("sailrecon_b200: call CameraHead.forward (trunk_fn is internal to the reference)")
+
+
+def modulate(x: torch.Tensor, shift: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
+    raise NotImplementedError("sailrecon_b200: modulate is fused into sr_adaln_modulate_f32 (CameraHead.forward)")
+
+
+def build_lr_mask(S: int, no_reloc_list, device="cpu"):
+    """camera_head.py:197-228 (True = masked).  Kept for API parity; the head itself uses the structure directly."""
+    r = [i for i in range(S) if i not in no_reloc_list]
+    mask = torch.zeros(S, S, dtype=torch.bool, device=device)
+    l_idx = torch.as_tensor(sorted(set(no_reloc_list)), dtype=torch.long, device=device)
+    r_idx = torch.tensor(r, dtype=torch.long, device=device)
+    if l_idx.numel() and r_idx.numel():
+        mask[l_idx[:, None], r_idx[None, :]] = True
+    if r_idx.numel() > 1:
+        mask[r_idx[:, None], r_idx[None, :]] = True
+        mask[r_idx, r_idx] = False
+    return mask.unsqueeze(0).unsqueeze(0)

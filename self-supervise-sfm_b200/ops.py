@@ -12,11 +12,12 @@ from typing import Optional
 import torch
 
 from . import _lib
-from ._lib import SR_EPI_BIAS, SR_EPI_BIAS_GELU, SR_EPI_LS_RESIDUAL, SR_EPI_QKV, SrAttn, SrEpilogue
+from ._lib import (SR_EPI_BIAS, SR_EPI_BIAS_GELU, SR_EPI_BIAS_SILU, SR_EPI_LS_RESIDUAL, SR_EPI_QKV, SrAttn,
+                   SrEpilogue)
 
 __all__ = [
     "layernorm", "gemm", "attention", "gather_rows", "copy_cols", "cast_bf16", "adaln_modulate",
-    "QkvEpilogue", "num_kernel_launches",
+    "QkvEpilogue", "num_kernel_launches", "rope_tables", "rope2d", "patchify", "pose_update", "scale_cols",
 ]
 
 
@@ -223,4 +224,64 @@ def cast_bf16(src: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
     _rows2d(out, torch.bfloat16, "out")
     _lib.check(_lib.load().sr_cast_f32_to_bf16(src.data_ptr(), src.stride(0), out.data_ptr(), out.stride(0), src.shape[0],
                                                src.shape[1], _stream()), "cast_bf16")
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ RoPE / front end / pose
+def rope_tables(max_pos: int, quarter_dim: int, frequency: float, device) -> tuple:
+    """cos / sin fp32 [max_pos, quarter_dim] (rope.py:107-123), built on the device by the library."""
+    cos = torch.empty(max_pos, quarter_dim, dtype=torch.float32, device=device)
+    sin = torch.empty_like(cos)
+    _lib.check(_lib.load().sr_rope_table_build(cos.data_ptr(), sin.data_ptr(), max_pos, quarter_dim, float(frequency),
+                                               _stream()), "rope_tables")
+    return cos, sin
+
+
+def rope2d(x: torch.Tensor, pos: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
+    """RotaryPositionEmbedding2D.forward on fp32 [B, H, N, d] with int32 positions [B, N, 2]."""
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.is_contiguous()):
+        raise ValueError("sailrecon_b200: rope2d needs a contiguous fp32 CUDA tensor [B, H, N, d]")
+    B, H, N, d = x.shape
+    if not (pos.is_cuda and pos.dtype == torch.int32 and pos.is_contiguous() and tuple(pos.shape) == (B, N, 2)):
+        raise ValueError("sailrecon_b200: rope2d positions must be contiguous int32 [B, N, 2]")
+    if cos.shape[1] != d // 4:
+        raise ValueError("sailrecon_b200: rope tables do not match the feature dimension")
+    out = torch.empty_like(x)
+    _lib.check(_lib.load().sr_rope2d_f32(x.data_ptr(), out.data_ptr(), pos.data_ptr(), cos.data_ptr(), sin.data_ptr(),
+                                         cos.shape[0], B, H, N, d, _stream()), "rope2d")
+    return out
+
+
+def patchify(images: torch.Tensor, out: torch.Tensor, patch: int, mean, std) -> torch.Tensor:
+    """images fp32 [S, 3, H, W] -> out [S*h*w, ldo] (bf16 or fp32): normalised im2col rows, zero padded to ldo columns."""
+    if not (images.is_cuda and images.dtype == torch.float32 and images.dim() == 4 and images.is_contiguous()
+            and images.shape[1] == 3):
+        raise ValueError("sailrecon_b200: patchify needs contiguous fp32 CUDA images [S, 3, H, W]")
+    S, _, H, W = images.shape
+    _rows2d(out, out.dtype, "out")
+    if out.dtype not in (torch.bfloat16, torch.float32) or not out.is_contiguous() or out.shape[0] != S * (H // patch) * (W // patch):
+        raise ValueError("sailrecon_b200: patchify out must be contiguous bf16/fp32 [S*h*w, Kpad]")
+    m = (C.c_float * 3)(*[float(v) for v in mean])
+    sd = (C.c_float * 3)(*[float(v) for v in std])
+    _lib.check(_lib.load().sr_patchify(images.data_ptr(), out.data_ptr(), int(out.dtype == torch.bfloat16), out.shape[1], S, H, W,
+                                       patch, m, sd, _stream()), "patchify")
+    return out
+
+
+def pose_update(pred: torch.Tensor, delta: torch.Tensor, activated: torch.Tensor, first: bool) -> None:
+    for t in (pred, delta, activated):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.shape[-1] == 9 and t.shape == pred.shape):
+            raise ValueError("sailrecon_b200: pose_update needs contiguous fp32 CUDA tensors [rows, 9]")
+    _lib.check(_lib.load().sr_pose_update(pred.data_ptr(), delta.data_ptr(), activated.data_ptr(), pred.numel() // 9,
+                                          int(first), _stream()), "pose_update")
+
+
+def scale_cols(x: torch.Tensor, gamma: torch.Tensor) -> torch.Tensor:
+    """LayerScale on its own: x [..., C] fp32 contiguous times gamma [C]."""
+    if not (x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()):
+        raise ValueError("sailrecon_b200: scale_cols needs a contiguous fp32 CUDA tensor")
+    _vec(gamma, x.shape[-1], "gamma")
+    out = torch.empty_like(x)
+    _lib.check(_lib.load().sr_scale_cols_f32(x.data_ptr(), gamma.data_ptr(), out.data_ptr(), x.numel() // x.shape[-1],
+                                             x.shape[-1], _stream()), "scale_cols")
     return out
