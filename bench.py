@@ -1,0 +1,348 @@
+#!/usr/bin/env python
+"""bench.py — SAIL-Recon hot path on B200: aggregator + camera head, frames/s (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload agg32|ring]
+
+Workload "agg32" (default, BASELINE.json configs[1]): 32 frames of 518x518 = 16 anchors + 16 query frames
+(the train/demo_imc_forward.py duplication), full-size model (DINOv2 ViT-L patch embed + 3 x 24 blocks + camera head),
+random-init weights, autocast(bf16) around the aggregator and fp32 camera head exactly like sail_recon.py:101,119-121.
+One "step" = one aggregator + camera-head forward over one synthetic 32-frame scene.
+  value  frames/s with the images already resident in HBM (CUDA events, max over ranks)
+  e2e    frames/s through the public module API with the images in pinned HOST memory: H2D copy of the scene and D2H
+         read of the pose encodings inside the timed region
+N > 1 (torchrun): one process per GPU, one independent scene per rank (the reference's own DDP decomposition,
+train/train_imc.py:494-504) — no data-path collective, weak scaling.
+Workload "ring" (BASELINE.json configs[3]): the sequence-sharded global-attention stack, see parallel.py.
+
+--impl reference: the reference's CPU path restated by the oracle (oracle/sailrecon_oracle.py; the Python reference
+itself cannot travel to the GPU box) timed on the host cores on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "aggregator+camera-head frames/s at N=32 (518px)"
+UNIT = "frames/s"
+C, HEADS, PATCH, DEPTH, PSI = 1024, 16, 14, 24, 5
+
+
+# ------------------------------------------------------------------------------------------------ algorithmic work
+def algorithmic_flops(Na: int, Nq: int, H: int, W: int, rank: int = 300, depth: int = DEPTH, vit_depth: int = 24) -> dict:
+    """multiply-add = 2 flops; softmax / LN / GELU / RoPE excluded; dead scene-row work excluded."""
+    P = PSI + (H // PATCH) * (W // PATCH)
+    Pp = min(rank, P - PSI) + PSI
+    S = Na + Nq
+    blk = 24 * C * C                                                   # per token per block (qkv + proj + fc1 + fc2)
+    f = {}
+    f["dino"] = vit_depth * S * (P * blk + 4 * P * P * C)
+    f["frame"] = depth * S * (P * blk + 4 * P * P * C)
+    Lg = Na * P
+    f["global"] = depth * (Lg * blk + 4 * Lg * Lg * C)
+    f["reloc"] = depth * (Nq * P * blk + Na * Pp * 2 * C * 2 * C + Nq * 4 * P * (Na * Pp + P) * C) if Nq else 0
+    T, Ch = S, 2 * C
+    f["camera"] = 4 * (4 * (T * 24 * Ch * Ch + 4 * T * T * Ch) + T * 2 * (9 * Ch + 3 * Ch * Ch + Ch * Ch // 2 + 9 * Ch // 2))
+    f["total"] = sum(f.values())
+    return f
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=lambda: self.lines.extend(self.proc.stdout), daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1])); pw.append(float(p[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU (reference) arm
+def cpu_sample(Na: int, Nq: int, H: int, W: int, threads: int) -> dict:
+    """Oracle port of the reference CPU path (fp32, no autocast — BASELINE.json configs[0] arithmetic) on a bounded
+    sample of the agg32 workload: ALL 32 frames through ONE DINOv2 block, ONE aggregator layer (frame + global + reloc
+    blocks) and ONE of the 4 camera-head refinement iterations; every layer / iteration costs the same, so the full
+    forward is the sample scaled by the counts (24 layers, 4 iterations).  Returns seconds for the scaled full forward."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import sailrecon_oracle as O
+    from golden_common import make_images, make_params
+    torch.set_num_threads(threads)
+    st = cpu_sample.__dict__.setdefault("state", {})
+    if not st:
+        hw = (H // PATCH) * (W // PATCH)
+        shapes = {}
+        for stack in ("frame_blocks", "global_blocks", "global_reloc_blocks", "patch_embed.blocks"):
+            pre = f"{stack}.0."
+            shapes.update({pre + "norm1.weight": [C], pre + "norm1.bias": [C], pre + "attn.qkv.weight": [3 * C, C],
+                           pre + "attn.qkv.bias": [3 * C], pre + "attn.proj.weight": [C, C], pre + "attn.proj.bias": [C],
+                           pre + "ls1.gamma": [C], pre + "norm2.weight": [C], pre + "norm2.bias": [C],
+                           pre + "mlp.fc1.weight": [4 * C, C], pre + "mlp.fc1.bias": [4 * C], pre + "mlp.fc2.weight": [C, 4 * C],
+                           pre + "mlp.fc2.bias": [C], pre + "ls2.gamma": [C]})
+            if stack != "patch_embed.blocks":
+                for n in ("q_norm", "k_norm"):
+                    shapes.update({pre + f"attn.{n}.weight": [64], pre + f"attn.{n}.bias": [64]})
+        shapes.update({"patch_embed.patch_embed.proj.weight": [C, 3, PATCH, PATCH], "patch_embed.patch_embed.proj.bias": [C],
+                       "patch_embed.cls_token": [1, 1, C], "patch_embed.pos_embed": [1, 1 + 37 * 37, C],
+                       "patch_embed.register_tokens": [1, 4, C], "patch_embed.norm.weight": [C], "patch_embed.norm.bias": [C],
+                       "camera_token": [1, 2, 1, C], "register_token": [1, 2, 4, C], "camera_token_reloc": [1, 1, 1, C],
+                       "register_token_reloc": [1, 1, 4, C]})
+        Ch = 2 * C
+        hs = {"token_norm.weight": [Ch], "token_norm.bias": [Ch], "trunk_norm.weight": [Ch], "trunk_norm.bias": [Ch],
+              "empty_pose_tokens": [1, 1, 9], "embed_pose.weight": [Ch, 9], "embed_pose.bias": [Ch],
+              "poseLN_modulation.1.weight": [3 * Ch, Ch], "poseLN_modulation.1.bias": [3 * Ch],
+              "pose_branch.fc1.weight": [Ch // 2, Ch], "pose_branch.fc1.bias": [Ch // 2], "pose_branch.fc2.weight": [9, Ch // 2],
+              "pose_branch.fc2.bias": [9]}
+        for b in range(4):
+            pre = f"trunk.{b}."
+            hs.update({pre + "norm1.weight": [Ch], pre + "norm1.bias": [Ch], pre + "attn.qkv.weight": [3 * Ch, Ch],
+                       pre + "attn.qkv.bias": [3 * Ch], pre + "attn.proj.weight": [Ch, Ch], pre + "attn.proj.bias": [Ch],
+                       pre + "ls1.gamma": [Ch], pre + "norm2.weight": [Ch], pre + "norm2.bias": [Ch],
+                       pre + "mlp.fc1.weight": [4 * Ch, Ch], pre + "mlp.fc1.bias": [4 * Ch], pre + "mlp.fc2.weight": [Ch, 4 * Ch],
+                       pre + "mlp.fc2.bias": [Ch], pre + "ls2.gamma": [Ch]})
+        st["agg"] = make_params(shapes, 1)
+        st["head"] = make_params(hs, 2)
+        st["images"] = make_images(Na + Nq, H, W, 3)
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        out, _, cam = O.aggregator_forward(st["images"], st["agg"], list(range(Na)), list(range(Na, Na + Nq)), 300,
+                                           torch.Generator().manual_seed(1234), depth=1, vit_depth=1,
+                                           intermediate_layer_idx=(0,), bf16=False)
+        t1 = time.perf_counter()
+        O.camera_head_forward(out[-1][:, :, 0], cam, st["head"], 1, 16, 4)
+        t2 = time.perf_counter()
+    return {"layer_s": t1 - t0, "head_s": t2 - t1, "full_forward_s": DEPTH * (t1 - t0) + 4 * (t2 - t1)}
+
+
+def run_reference_arm(args, rank: int, world: int) -> None:
+    if rank != 0:
+        return
+    Na = Nq = args.frames // 2
+    threads = os.cpu_count() or 1
+    for _ in range(args.warmup):
+        cpu_sample(Na, Nq, args.size, args.size, threads)
+    ts = []
+    for _ in range(args.steps):
+        ts.append(cpu_sample(Na, Nq, args.size, args.size, threads)["full_forward_s"])
+    t = sum(ts) / len(ts)
+    v = args.frames / t
+    sample = ("oracle port (fp32): all %d frames through 1 of 24 DINOv2 blocks + 1 of 24 aggregator layers "
+              "(frame+global+reloc) + 1 of 4 camera-head iterations per step; step time scaled by 24 / 4" % args.frames)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"agg{args.frames}: {Na} anchors + {Nq} queries, {args.size}x{args.size}, fix_rank 300, "
+                                   "random-init weights, CPU"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def build_models(device):
+    """Full-size SAIL-Recon aggregator + camera head with the reference's default constructor arguments
+    (sail_recon.py:38-45) and random init, created directly on the device."""
+    from sailrecon_b200.heads import CameraHead
+    from sailrecon_b200.models import Aggregator
+    torch.manual_seed(0)
+    with torch.device(device):
+        agg = Aggregator().eval()
+        head = CameraHead(dim_in=2 * C).eval()
+    return agg, head
+
+
+def forward_scene(agg, head, images, Na, Nq):
+    """train/demo_imc_forward.py:92-101 + sail_recon.py:101,119-121."""
+    with torch.no_grad():
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out, psi, cam = agg(images, list(range(Na)), list(range(Na, Na + Nq)), fix_rank=300)
+        with torch.autocast("cuda", enabled=False):
+            poses = head(out, cam)
+    return poses
+
+
+def summarize_profile(records) -> dict:
+    """Per kernel class: launches, summed CUDA-event time, algorithmic flops / bytes (ops._Timed)."""
+    agg = {}
+    for label, flops, nbytes, e0, e1 in records:
+        d = agg.setdefault(label, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+        d["launches"] += 1
+        d["ms"] += e0.elapsed_time(e1)
+        d["flops"] += flops
+        d["bytes"] += nbytes
+    return agg
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="agg32", choices=["agg32", "ring"])
+    ap.add_argument("--frames", type=int, default=32)
+    ap.add_argument("--size", type=int, default=518)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+    if args.workload == "ring":
+        from sailrecon_b200 import parallel
+        parallel.bench_ring(args, rank, world, local)
+        return
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a B200: sailrecon_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from sailrecon_b200 import ops
+
+    Na = Nq = args.frames // 2
+    S, H, W = Na + Nq, args.size, args.size
+    agg, head = build_models(dev)
+    host_images = torch.rand(1, S, 3, H, W, generator=torch.Generator().manual_seed(1 + rank)).pin_memory()
+    images = host_images.to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput
+    for _ in range(args.warmup):
+        agg.generator.manual_seed(1234)
+        forward_scene(agg, head, images, Na, Nq)
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    ops.PROFILE = []
+    launches0 = ops.num_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        agg.generator.manual_seed(1234)
+        poses = forward_scene(agg, head, images, Na, Nq)
+    e1.record()
+    barrier()
+    launches = ops.num_kernel_launches() - launches0
+    records, ops.PROFILE = ops.PROFILE, None
+    clk = clocks.stop()
+    ms = e0.elapsed_time(e1)
+    finite = bool(torch.isfinite(poses[-1]).all())
+
+    # ---- end to end through the public API: host images in, pose encodings out
+    barrier()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(args.steps):
+        agg.generator.manual_seed(1234)
+        dimg = host_images.to(dev, non_blocking=True)
+        poses = forward_scene(agg, head, dimg, Na, Nq)
+        host_poses = torch.stack(poses).cpu()
+    t1.record()
+    barrier()
+    ms_e2e = t0.elapsed_time(t1)
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(tt[0]), float(tt[1])
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak_tf = peaks.get("bf16_tflops_sustained", 1400.0)
+        peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if peaks else "fallback (B200_PROFILING.md sustained ~1.4 PF)"
+        prof = summarize_profile(records)
+        top = max((k for k in prof if prof[k]["flops"] > 0), key=lambda k: prof[k]["ms"])
+        d = prof[top]
+        achieved = d["flops"] / (d["ms"] * 1e-3) / 1e12
+        kern = {k: {"launches_per_step": v["launches"] // args.steps, "ms_per_step": v["ms"] / args.steps,
+                    "tflops": (v["flops"] / (v["ms"] * 1e-3) / 1e12) if v["flops"] else None,
+                    "gbs": v["bytes"] / (v["ms"] * 1e-3) / 1e9} for k, v in prof.items()}
+        fl = algorithmic_flops(Na, Nq, H, W)
+        step_s = ms * 1e-3 / args.steps
+        line = {
+            "metric": METRIC, "value": world * S / step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": f"agg{S}: {Na} anchors + {Nq} queries, {H}x{W}, fix_rank 300, DINOv2 ViT-L patch embed + "
+                                   "24x(frame, global, reloc) blocks + camera head, random-init weights, one scene per GPU",
+                       "l2": "activations per layer (>= 180 MB residual + 270 MB qkv + 360 MB MLP hidden) exceed the 126 MB L2; "
+                             "no flush needed"},
+            "e2e": {"value": world * S / (ms_e2e * 1e-3 / args.steps), "unit": UNIT,
+                    "h2d_bytes_per_step": host_images.numel() * 4, "d2h_bytes_per_step": host_poses.numel() * 4},
+            "gpu_launches": launches,
+            "clocks": clk,
+            "roofline": {"bound": "tensor", "kernel": top, "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
+                         "frac": achieved / peak_tf, "traffic": None, "peak_source": peak_src,
+                         "launches_per_step": d["launches"] // args.steps},
+            "kernels": kern,
+            "algorithmic_tflop_per_step": fl["total"] / 1e12,
+            "tensor_frac_whole_step": fl["total"] / step_s / 1e12 / peak_tf,
+            "outputs_finite": finite,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            cs = cpu_sample(Na, Nq, H, W, threads)
+            line["cpu_baseline"] = {"value": S / cs["full_forward_s"], "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": f"oracle port (fp32) on {threads} host threads: all {S} frames through 1 of 24 DINOv2 "
+                                              f"blocks + 1 of 24 aggregator layers ({cs['layer_s']:.1f} s) + 1 of 4 camera-head "
+                                              f"iterations ({cs['head_s']:.2f} s); scaled by 24 / 4"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -100,10 +100,16 @@ def rope_2d(x: Tensor, pos: Tensor, frequency: float = 100.0) -> Tensor:
 def sdpa(q: Tensor, k: Tensor, v: Tensor, mask: Optional[Tensor], bf16: bool) -> Tensor:
     """F.scaled_dot_product_attention (layers/attention.py:103-109); mask True = attend.  q,k,v [H, N, d]."""
     q, k, v = _r(q, bf16), _r(k, bf16), _r(v, bf16)
-    s = (q @ k.transpose(-1, -2)) * (q.shape[-1] ** -0.5)
-    if mask is not None:
-        s = s.masked_fill(~mask, float("-inf"))
-    return _r(torch.softmax(s, dim=-1) @ v, bf16)
+    scale = q.shape[-1] ** -0.5
+    n_q, n_k = q.shape[-2], k.shape[-2]
+    chunk = n_q if n_q * n_k <= (1 << 24) else max(1, (1 << 24) // n_k)      # rows are independent: bound the score matrix
+    outs = []
+    for r0 in range(0, n_q, chunk):
+        s = (q[..., r0:r0 + chunk, :] @ k.transpose(-1, -2)) * scale
+        if mask is not None:
+            s = s.masked_fill(~mask[..., r0:r0 + chunk, :], float("-inf"))
+        outs.append(torch.softmax(s, dim=-1) @ v)
+    return _r(outs[0] if len(outs) == 1 else torch.cat(outs, dim=-2), bf16)
 
 
 def qkv_heads(x: Tensor, p: Params, pre: str, num_heads: int, pos: Optional[Tensor], qk_norm: bool, rope: bool,

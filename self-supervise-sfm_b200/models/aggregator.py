@@ -70,7 +70,7 @@ class Aggregator(nn.Module):
         for t in (self.camera_token, self.register_token, self.camera_token_reloc, self.register_token_reloc):
             nn.init.normal_(t, std=1e-6)
         for name, value in (("_resnet_mean", _RESNET_MEAN), ("_resnet_std", _RESNET_STD)):
-            self.register_buffer(name, torch.FloatTensor(value).view(1, 1, 3, 1, 1), persistent=False)
+            self.register_buffer(name, torch.tensor(value, dtype=torch.float32).view(1, 1, 3, 1, 1), persistent=False)
         self.use_reentrant = False
         self.generator = self._generate_per_rank_generator()
         self.num_recon = 0
@@ -97,7 +97,7 @@ class Aggregator(nn.Module):
         """aggregator.py:628-641: CPU generator seeded from the global RNG plus the distributed rank."""
         per_forward_pass_seed = torch.randint(0, 2 ** 32, (1,)).item()
         world_rank = torch.distributed.get_rank() if torch.distributed.is_initialized() else 0
-        g = torch.Generator()
+        g = torch.Generator(device="cpu")
         g.manual_seed(per_forward_pass_seed + world_rank)
         return g
 

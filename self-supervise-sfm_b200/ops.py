@@ -21,6 +21,28 @@ __all__ = [
 ]
 
 
+# Optional per-launch timing (bench.py): when `PROFILE` is a list, every wrapper below brackets its launch with CUDA
+# events on the launching stream and appends (kernel class, algorithmic flops, algorithmic bytes, start, end).
+PROFILE = None
+
+
+class _Timed:
+    __slots__ = ("rec",)
+
+    def __init__(self, label: str, flops: float, nbytes: float):
+        self.rec = None
+        if PROFILE is not None:
+            e0 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            self.rec = (label, flops, nbytes, e0)
+
+    def done(self):
+        if self.rec is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            PROFILE.append((*self.rec, e1))
+
+
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -67,9 +89,11 @@ def layernorm(x: torch.Tensor, weight: Optional[torch.Tensor], bias: Optional[to
     elif x.shape[0] != rows:
         raise ValueError("sailrecon_b200: layernorm x/out row mismatch")
     lib = _lib.load()
+    t = _Timed("layernorm", 0.0, rows * Cdim * (4 + out.element_size()))
     _lib.check(lib.sr_layernorm_gather_fwd(x.data_ptr(), x.stride(0), _ptr(idx), _ptr(weight), _ptr(bias), out.data_ptr(),
                                            int(out.dtype == torch.bfloat16), out.stride(0), rows, Cdim, float(eps),
                                            _stream()), "layernorm")
+    t.done()
     return out
 
 
@@ -149,7 +173,10 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: to
             keep += [cos, sin, pos]
     lib = _lib.load()
     fn = lib.sr_gemm_bf16 if a.dtype == torch.bfloat16 else lib.sr_gemm_f32
+    t = _Timed("gemm_tc" if a.dtype == torch.bfloat16 else "gemm_f32", 2.0 * M * N * K,
+               (M * K + N * K) * a.element_size() + M * N * out.element_size())
     _lib.check(fn(a.data_ptr(), a.stride(0), w.data_ptr(), w.stride(0), M, N, K, C.byref(e), _stream()), "gemm")
+    t.done()
     return out
 
 
@@ -191,7 +218,11 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[t
     a.carry_in, a.carry_out = int(carry_in), int(carry_out)
     lib = _lib.load()
     fn = lib.sr_attn_fwd_bf16 if dt == torch.bfloat16 else lib.sr_attn_fwd_f32
+    hd = num_heads * head_dim
+    t = _Timed("attn_tc" if dt == torch.bfloat16 else "attn_f32", 4.0 * batch * q_len * (prefix_len + kv_len) * hd,
+               (2 * batch * q_len + 2 * batch * kv_len + 2 * prefix_len) * hd * q.element_size())
     _lib.check(fn(C.byref(a), _stream()), "attention")
+    t.done()
     return out
 
 
