@@ -5,16 +5,20 @@
 // boolean mask (aggregator.py:302-311, build_allow_block :832-847) is never materialised: its structure is
 // "shared scene prefix + own frame", which this kernel walks as two K/V tile ranges.
 //
-// One CTA = one head x NQ=2 query tiles of 128 rows.  384 threads:
-//   warp 0        TMA producer: Q tiles once, then K/V tiles (128 x 64, SWIZZLE_128B) through a 3-stage ring
-//   warp 1        MMA issuer (one thread):  S_q = Q_q K^T   (tcgen05.mma SS, M=128 N=128 K=16 x4)  -> TMEM
-//                                           O_q += P_q V    (tcgen05.mma SS, M=128 N=64  K=16 x8)  -> TMEM
-//                 S_q(j+1) is issued before P_q(j)V(j) so the tensor pipe works under the softmax
-//   warp 2        TMEM allocator (S: 2 x 128 columns, O: 2 x 64 columns)
+// One CTA = one head x 2 query tiles of 128 rows.  384 threads:
+//   warp 0        TMA producer: Q tiles once, then K/V tiles (128 x 64, SWIZZLE_128B) through a kAtStages ring
+//   warp 1, 3     MMA issuers, one per query tile q (one thread each), each an independent in-order pipeline:
+//                     S_q(j+1) = Q_q K(j+1)^T   tcgen05.mma SS, M=128 N=128 K=16 x4 -> TMEM   as soon as the softmax
+//                                               warpgroup has pulled S_q(j) into registers (s_free)
+//                     O_q     += P_q(j) V(j)    tcgen05.mma TS (A = P from TMEM), M=128 N=64 K=16 x8 -> TMEM
+//   warp 2        TMEM allocator: S0 S1 (128 cols each) | O0 O1 (64 each) | P0 P1 (64 each: 128 bf16) = 512 columns
 //   warps 4-7     softmax warpgroup of Q tile 0, warps 8-11 of Q tile 1: one thread = one query row
 //                 (tcgen05.ld 32x32b), online softmax in the log2 domain with lazy rescale of O
-//                 (rescale only when the row max grows by more than 2^8), P written as bf16 into a
-//                 K-major SWIZZLE_128B smem tile that the second MMA consumes.
+//                 (rescale only when the row max grows by more than 2^8), P written back to TMEM as packed bf16
+//                 (tcgen05.st) so the second MMA reads it from TMEM and shared memory only carries Q, K, V.
+// The softmax inner loop is written for instruction count (it is the critical resource at head_dim 64, where one
+// 128x128 tile costs 16K exponentials against 512 tensor-core cycles): FMNMX3 row max, FFMA2 / FADD2 packed fp32,
+// MUFU.EX2 without range wrappers, F2FP packed conversion.
 // Optional carry of (m, l, un-normalised O) in/out turns one call into a step of ring attention
 // (global blocks sharded over ranks).
 #include "common.cuh"
@@ -24,14 +28,13 @@ namespace sr {
 extern int g_launch_count;
 
 constexpr int kAtNQ = 2;
-constexpr int kAtStages = 3;
+constexpr int kAtStages = 4;
 constexpr int kAtTile = 128 * 64 * 2;                 // 16 KB: one 128 x 64 bf16 tile
 constexpr int kAtThreads = 128 + kAtNQ * 128;
 constexpr int kAtSmem = kAtNQ * kAtTile               // Q
-                        + kAtNQ * 2 * kAtTile         // P (128 x 128 bf16 = two K-major 64-wide sub-tiles)
                         + kAtStages * 2 * kAtTile     // K, V ring
                         + 1024;
-constexpr int kAtTmemCols = 512;                      // S0 S1 (128 each) | O0 O1 (64 each) -> 384, pow2 = 512
+constexpr int kAtTmemCols = 512;                      // S0 S1 (128 each) | O0 O1 (64 each) | P0 P1 (64 each)
 constexpr float kLazyRescaleLog2 = 8.0f;
 
 struct AttnParams {
@@ -50,6 +53,41 @@ struct AttnParams {
   float scale_log2;
 };
 
+// ---- packed fp32 helpers (FFMA2 / FADD2 on sm_100) and bare MUFU.EX2
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
 __global__ void __launch_bounds__(kAtThreads, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_pk,
@@ -57,15 +95,14 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t q_full;
   __shared__ __align__(8) uint64_t k_full[kAtStages], k_empty[kAtStages], v_full[kAtStages], v_empty[kAtStages];
-  __shared__ __align__(8) uint64_t s_full[kAtNQ], p_full[kAtNQ], pv_done[kAtNQ];
+  __shared__ __align__(8) uint64_t s_full[kAtNQ], s_free[kAtNQ], p_full[kAtNQ], pv_done[kAtNQ];
   __shared__ uint32_t tmem_base_slot;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
-  uint8_t* sP = sQ + kAtNQ * kAtTile;
-  uint8_t* sK = sP + kAtNQ * 2 * kAtTile;
+  uint8_t* sK = sQ + kAtNQ * kAtTile;
   uint8_t* sV = sK + kAtStages * kAtTile;
 
   const int head = blockIdx.y;
@@ -87,13 +124,14 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     mbar_init(&q_full, 1);
     for (int s = 0; s < kAtStages; ++s) {
       mbar_init(&k_full[s], 1);
-      mbar_init(&k_empty[s], 1);
+      mbar_init(&k_empty[s], nq_valid);      // one tcgen05.commit per MMA issuer
       mbar_init(&v_full[s], 1);
-      mbar_init(&v_empty[s], 1);
+      mbar_init(&v_empty[s], nq_valid);
     }
     for (int q = 0; q < kAtNQ; ++q) {
       mbar_init(&s_full[q], 1);
-      mbar_init(&p_full[q], 128);
+      mbar_init(&s_free[q], 4);              // one elected arrive per softmax warp
+      mbar_init(&p_full[q], 4);
       mbar_init(&pv_done[q], 1);
     }
     fence_mbar_init();
@@ -105,7 +143,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
   const uint32_t tmem_base = tmem_base_slot;
   const uint32_t tmem_S0 = tmem_base;                         // + q * 128
   const uint32_t tmem_O0 = tmem_base + kAtNQ * 128;           // + q * 64
+  const uint32_t tmem_P0 = tmem_O0 + kAtNQ * 64;              // + q * 64   (128 bf16 per row = 64 columns)
 
+  // register re-distribution: the 4 control warps keep 80 registers, the 8 softmax warps (a 128-value fp32 row
+  // fragment per thread) grow to 208:  128 x 80 + 256 x 208 = 63488 <= 65536
+  if (warp < 4) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
@@ -126,55 +169,57 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         else     tma_load_3d(sV + s * kAtTile, &tmap_v, &v_full[s], head * 64, r0, b);
       }
     }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+  } else if (warp == 1 || warp == 3) {
+    // ------------------------------------------------------------------ MMA issuer of query tile q
+    const int q = warp >> 1;
+    if (lane == 0 && q < nq_valid) {
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);   // Q (K-major) x K (K-major)
-      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);    // P (K-major) x V (MN-major: d contiguous)
-      auto issue_s = [&](int q, int stage) {
-        const uint64_t da = umma_desc_sw128(smem_u32(sQ + q * kAtTile), 16, 1024);
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);    // P (TMEM)    x V (MN-major: d contiguous)
+      const uint32_t tS = tmem_S0 + q * 128, tO = tmem_O0 + q * 64, tP = tmem_P0 + q * 64;
+      const uint64_t dq = umma_desc_sw128(smem_u32(sQ + q * kAtTile), 16, 1024);
+      auto issue_s = [&](int stage) {
         const uint64_t db = umma_desc_sw128(smem_u32(sK + stage * kAtTile), 16, 1024);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_ss(tmem_S0 + q * 128, da + 2 * k, db + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+        for (int k = 0; k < 4; ++k) umma_ss(tS, dq + 2 * k, db + 2 * k, idesc_s, k != 0 ? 1u : 0u);
         umma_commit(&s_full[q]);
+        umma_commit(&k_empty[stage]);
       };
-      auto issue_pv = [&](int q, int stage, bool accumulate) {
-        const uint32_t pbase = smem_u32(sP + q * 2 * kAtTile);
+      auto issue_pv = [&](int stage, bool accumulate) {
         const uint32_t vbase = smem_u32(sV + stage * kAtTile);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          // A: P sub-tile k/4 (64 kv columns each), 32 B per K=16 slice inside the swizzle atom
-          const uint64_t da = umma_desc_sw128(pbase + (k >> 2) * kAtTile + (k & 3) * 32, 16, 1024);
+          // A: P columns [8k, 8k+8) hold kv [16k, 16k+16) as packed bf16 pairs
           // B: V rows [16k, 16k+16) = two 8-row swizzle atoms (SBO 1024 B); one 64-wide MN block (LBO unused)
           const uint64_t db = umma_desc_sw128(vbase + k * 2048, 0, 1024);
-          umma_ss(tmem_O0 + q * 64, da, db, idesc_o, (accumulate || k != 0) ? 1u : 0u);
+          umma_ts(tO, tP + k * 8, db, idesc_o, (accumulate || k != 0) ? 1u : 0u);
         }
         umma_commit(&pv_done[q]);
+        umma_commit(&v_empty[stage]);
       };
 
       mbar_wait(&q_full, 0);
       mbar_wait(&k_full[0], 0);
       tc_fence_after();
-      for (int q = 0; q < nq_valid; ++q) issue_s(q, 0);
-      umma_commit(&k_empty[0]);
+      issue_s(0);
       for (int j = 0; j < n_tiles; ++j) {
         const int s = j % kAtStages;
-        const int sn = (j + 1) % kAtStages;
-        const bool has_next = j + 1 < n_tiles;
-        if (has_next) mbar_wait(&k_full[sn], ((j + 1) / kAtStages) & 1);
-        for (int q = 0; q < nq_valid; ++q) {
-          mbar_wait(&p_full[q], j & 1);          // softmax q done with S_q(j); P_q(j) in smem; O_q rescaled
+        if (j + 1 < n_tiles) {
+          const int sn = (j + 1) % kAtStages;
+          mbar_wait(&k_full[sn], ((j + 1) / kAtStages) & 1);
+          mbar_wait(&s_free[q], j & 1);          // softmax q holds S_q(j) in registers
           tc_fence_after();
-          if (has_next) issue_s(q, sn);
-          if (q == 0) { mbar_wait(&v_full[s], (j / kAtStages) & 1); tc_fence_after(); }
-          issue_pv(q, s, p.carry_in != 0 || j > 0);
+          issue_s(sn);
         }
-        if (has_next) umma_commit(&k_empty[sn]);
-        umma_commit(&v_empty[s]);
+        mbar_wait(&v_full[s], (j / kAtStages) & 1);
+        mbar_wait(&p_full[q], j & 1);            // P_q(j) in TMEM, O_q rescaled
+        tc_fence_after();
+        issue_pv(s, p.carry_in != 0 || j > 0);
       }
     }
-  } else if (warp >= 4) {
+  }
+  } else {
     // ------------------------------------------------------------------ softmax warpgroups
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
     const int q = (warp - 4) >> 2;
     if (q < nq_valid) {
       const int quarter = warp & 3;
@@ -185,8 +230,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
       const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
       const uint32_t tS = tmem_S0 + q * 128 + lane_off;
       const uint32_t tO = tmem_O0 + q * 64 + lane_off;
-      uint8_t* myP = sP + q * 2 * kAtTile + (r_tile >> 3) * 1024 + (r_tile & 7) * 128;
-      const int sw = r_tile & 7;
+      const uint32_t tP = tmem_P0 + q * 64 + lane_off;
 
       float m = -INFINITY, l = 0.f;
       if (p.carry_in) {
@@ -206,6 +250,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         tmem_st32(tO + 32, o1);
         tmem_st_wait();
       }
+      const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
 
       for (int j = 0; j < n_tiles; ++j) {
         mbar_wait(&s_full[q], j & 1);
@@ -222,6 +267,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
           tmem_ld32(tS + 96, c3);
           tmem_ld_wait();
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_free[q]);     // S_q may be overwritten by Q_q K(j+1)^T
         // valid kv columns of this tile (only the last tile of the prefix / own range is partial)
         int valid = 128;
         if (j < p.n_prefix_tiles) {
@@ -229,44 +277,61 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         } else if (j == n_tiles - 1) {
           valid = p.kv_len - (j - p.n_prefix_tiles) * 128;
         }
-        float mx = -INFINITY;
         if (valid < 128) {
 #pragma unroll
-          for (int i = 0; i < 128; ++i) {
-            float sv = i < valid ? __uint_as_float(sraw[i]) : -INFINITY;
-            sraw[i] = __float_as_uint(sv);
-            mx = fmaxf(mx, sv);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 128; ++i) mx = fmaxf(mx, __uint_as_float(sraw[i]));
+          for (int i = 0; i < 128; ++i)
+            if (i >= valid) sraw[i] = 0xff800000u;   // -inf
         }
-        mx *= p.scale_log2;
+        float mx0 = max3(__uint_as_float(sraw[0]), __uint_as_float(sraw[1]), __uint_as_float(sraw[2]));
+        float mx1 = max3(__uint_as_float(sraw[3]), __uint_as_float(sraw[4]), __uint_as_float(sraw[5]));
+        float mx2 = max3(__uint_as_float(sraw[6]), __uint_as_float(sraw[7]), __uint_as_float(sraw[8]));
+        float mx3 = max3(__uint_as_float(sraw[9]), __uint_as_float(sraw[10]), __uint_as_float(sraw[11]));
+#pragma unroll
+        for (int i = 12; i < 124; i += 8) {
+          mx0 = max3(mx0, __uint_as_float(sraw[i + 0]), __uint_as_float(sraw[i + 1]));
+          mx1 = max3(mx1, __uint_as_float(sraw[i + 2]), __uint_as_float(sraw[i + 3]));
+          mx2 = max3(mx2, __uint_as_float(sraw[i + 4]), __uint_as_float(sraw[i + 5]));
+          mx3 = max3(mx3, __uint_as_float(sraw[i + 6]), __uint_as_float(sraw[i + 7]));
+        }
+        mx0 = max3(mx0, __uint_as_float(sraw[124]), __uint_as_float(sraw[125]));
+        mx1 = max3(mx1, __uint_as_float(sraw[126]), __uint_as_float(sraw[127]));
+        const float mx = fmaxf(max3(mx0, mx1, mx2), mx3) * p.scale_log2;   // scale > 0
         float m_new = m;
-        if (mx > m + kLazyRescaleLog2 || m == -INFINITY) m_new = fmaxf(mx, m);
-        const float alpha = (m_new != m) ? exp2f(m - m_new) : 1.0f;   // exp2f(-inf) = 0 on the first tile
-        float rowsum = 0.f;
-        const float neg_m = -m_new;
+        if (mx > m + kLazyRescaleLog2) m_new = mx;                         // also the first tile (m = -inf)
+        const float alpha = ex2_approx(m - m_new);                         // 1 when unchanged, 0 on the first tile
+        const uint64_t negm2 = pack2(-m_new, -m_new);
+        uint64_t sum0 = 0, sum1 = 0, sum2 = 0, sum3 = 0;                   // packed (0.f, 0.f)
+        uint32_t pk[64];
 #pragma unroll
-        for (int i = 0; i < 128; ++i) {
-          float pv = exp2f(fmaf(__uint_as_float(sraw[i]), p.scale_log2, neg_m));
-          rowsum += pv;
-          sraw[i] = __float_as_uint(pv);
+        for (int i = 0; i < 128; i += 8) {
+          float e[8];
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const uint64_t x2 = fma2(pack2(__uint_as_float(sraw[i + 2 * t]), __uint_as_float(sraw[i + 2 * t + 1])), scale2, negm2);
+            float x0, x1;
+            unpack2(x2, x0, x1);
+            e[2 * t] = ex2_approx(x0);
+            e[2 * t + 1] = ex2_approx(x1);
+            pk[(i >> 1) + t] = cvt_bf16x2(e[2 * t], e[2 * t + 1]);
+          }
+          sum0 = add2(sum0, pack2(e[0], e[1]));
+          sum1 = add2(sum1, pack2(e[2], e[3]));
+          sum2 = add2(sum2, pack2(e[4], e[5]));
+          sum3 = add2(sum3, pack2(e[6], e[7]));
         }
-        l = l * alpha + rowsum;
+        float r0, r1;
+        unpack2(add2(add2(sum0, sum1), add2(sum2, sum3)), r0, r1);
+        l = l * alpha + (r0 + r1);
 
         if (j > 0) {
-          mbar_wait(&pv_done[q], (j - 1) & 1);     // P_q smem and O_q are no longer in use by the tensor core
+          mbar_wait(&pv_done[q], (j - 1) & 1);     // P_q and O_q are no longer in use by the tensor core
           tc_fence_after();
         }
-#pragma unroll
-        for (int ch = 0; ch < 16; ++ch) {
-          uint4 w;
-          w.x = pack_bf16x2(__uint_as_float(sraw[ch * 8 + 0]), __uint_as_float(sraw[ch * 8 + 1]));
-          w.y = pack_bf16x2(__uint_as_float(sraw[ch * 8 + 2]), __uint_as_float(sraw[ch * 8 + 3]));
-          w.z = pack_bf16x2(__uint_as_float(sraw[ch * 8 + 4]), __uint_as_float(sraw[ch * 8 + 5]));
-          w.w = pack_bf16x2(__uint_as_float(sraw[ch * 8 + 6]), __uint_as_float(sraw[ch * 8 + 7]));
-          *reinterpret_cast<uint4*>(myP + (ch >> 3) * kAtTile + (((ch & 7) ^ sw) << 4)) = w;
+        {
+          uint32_t(&h0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&pk[0]);
+          uint32_t(&h1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&pk[32]);
+          tmem_st32(tP, h0);
+          tmem_st32(tP + 32, h1);
         }
         const bool have_acc = (j > 0) || p.carry_in;
         if (have_acc && __any_sync(0xffffffffu, m_new != m)) {
@@ -279,12 +344,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
             for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
             tmem_st32(tO + hlf * 32, o);
           }
-          tmem_st_wait();
         }
+        tmem_st_wait();
         m = m_new;
-        fence_proxy_async_smem();
         tc_fence_before();
-        mbar_arrive(&p_full[q]);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&p_full[q]);
       }
 
       // ---------------------------------------------------------------- epilogue

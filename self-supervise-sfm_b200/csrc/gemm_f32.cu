@@ -81,6 +81,151 @@ gemm_f32_kernel(const GemmF32Params p) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------- skinny path
+// Few rows (the camera head: M = Na + Nq camera tokens, tens of rows) against big weights (216 M fp32 parameters,
+// camera_head.py:59-83): the work is streaming W once from HBM.  Warp-per-output-column: a warp owns 2 rows of W, its
+// lanes split K in float4s (fully coalesced 512 B per row per step), A[32 rows, 256 k] is staged in shared memory by
+// cp.async (double buffered) and every A float4 read from smem feeds 8 FMAs.  The 2 x 32 per-lane partial sums are
+// reduced with a 31-shuffle transpose-reduce so that lane l ends up owning row m0 + l.  Grid = N/16 x ceil(M/32) CTAs
+// (128 ... 512 CTAs for the camera-head shapes) instead of the 32 ... 128 CTAs of the 64x64 tiling above.
+constexpr int kSkM = 32, kSkKC = 256, kSkWarps = 8, kSkNPerWarp = 2;
+constexpr int kSkSmem = 2 * kSkM * kSkKC * 4;
+
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
+  const int sz = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// lane l of the warp returns sum over lanes of v[l]  (v is consumed)
+__device__ __forceinline__ float warp_transpose_reduce32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool hi = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; ++i) {
+      const float send = hi ? v[i] : v[i + off];
+      const float keep = hi ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kSkWarps * 32, 2)
+gemm_f32_skinny_kernel(const GemmF32Params p) {
+  extern __shared__ __align__(16) uint8_t sk_smem[];
+  float* As = reinterpret_cast<float*>(sk_smem);            // [2][kSkM][kSkKC]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int m0 = blockIdx.y * kSkM;
+  const int n_base = (blockIdx.x * kSkWarps + warp) * kSkNPerWarp;
+  const int num_kc = (p.K + kSkKC - 1) / kSkKC;
+
+  auto stage_a = [&](int kc, int buf) {
+    // 32 rows x 64 float4 = 2048 float4, 256 threads -> 8 each; a warp covers 512 contiguous bytes of one row
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int f = tid + i * 256;
+      const int r = f >> 6, c4 = f & 63;
+      const int gm = m0 + r, gk = kc * kSkKC + c4 * 4;
+      const bool ok = gm < p.M && gk < p.K;
+      const float* src = ok ? p.A + static_cast<int64_t>(gm) * p.lda + gk : p.A;
+      cp_async16_zfill(As + (buf * kSkM + r) * kSkKC + c4 * 4, src, ok);
+    }
+    cp_async_commit();
+  };
+  const float* wrow[kSkNPerWarp];
+  bool wok[kSkNPerWarp];
+#pragma unroll
+  for (int j = 0; j < kSkNPerWarp; ++j) {
+    wok[j] = n_base + j < p.N;
+    wrow[j] = p.W + static_cast<int64_t>(wok[j] ? n_base + j : 0) * p.ldw;
+  }
+  auto load_w = [&](int kc, float4 (&w)[kSkNPerWarp][2]) {
+#pragma unroll
+    for (int j = 0; j < kSkNPerWarp; ++j)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int gk = kc * kSkKC + h * 128 + lane * 4;
+        w[j][h] = (wok[j] && gk < p.K) ? __ldg(reinterpret_cast<const float4*>(wrow[j] + gk)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+  };
+
+  float acc[kSkNPerWarp][kSkM];
+#pragma unroll
+  for (int j = 0; j < kSkNPerWarp; ++j)
+#pragma unroll
+    for (int m = 0; m < kSkM; ++m) acc[j][m] = 0.f;
+
+  float4 wcur[kSkNPerWarp][2], wnext[kSkNPerWarp][2];
+  stage_a(0, 0);
+  load_w(0, wcur);
+  for (int kc = 0; kc < num_kc; ++kc) {
+    const int buf = kc & 1;
+    cp_async_wait<0>();
+    __syncthreads();                       // chunk kc landed for everyone; everyone finished reading buffer buf^1
+    if (kc + 1 < num_kc) {
+      stage_a(kc + 1, buf ^ 1);
+      load_w(kc + 1, wnext);
+    }
+    const float* a_base = As + buf * kSkM * kSkKC + lane * 4;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+#pragma unroll
+      for (int m = 0; m < kSkM; ++m) {
+        const float4 a = *reinterpret_cast<const float4*>(a_base + m * kSkKC + h * 128);
+#pragma unroll
+        for (int j = 0; j < kSkNPerWarp; ++j) {
+          acc[j][m] = fmaf(a.x, wcur[j][h].x, acc[j][m]);
+          acc[j][m] = fmaf(a.y, wcur[j][h].y, acc[j][m]);
+          acc[j][m] = fmaf(a.z, wcur[j][h].z, acc[j][m]);
+          acc[j][m] = fmaf(a.w, wcur[j][h].w, acc[j][m]);
+        }
+      }
+    }
+    if (kc + 1 < num_kc) {
+#pragma unroll
+      for (int j = 0; j < kSkNPerWarp; ++j)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) wcur[j][h] = wnext[j][h];
+    }
+  }
+
+  const sr_epilogue_t& e = p.e;
+  const int gm = m0 + lane;
+#pragma unroll
+  for (int j = 0; j < kSkNPerWarp; ++j) {
+    const float s = warp_transpose_reduce32(acc[j], lane);
+    const int gn = n_base + j;
+    if (gn >= p.N || gm >= p.M) continue;
+    float y = s + (e.bias ? __ldg(e.bias + gn) : 0.f);
+    if (EPI == SR_EPI_BIAS_GELU) y = gelu_erf(y);
+    if (EPI == SR_EPI_BIAS_SILU) y = y / (1.f + expf(-y));
+    if (EPI == SR_EPI_LS_RESIDUAL) {
+      const float g = e.gamma ? __ldg(e.gamma + gn) : 1.f;
+      y = e.resid[static_cast<int64_t>(gm) * e.ldr + gn] + g * y;
+    }
+    reinterpret_cast<float*>(e.out)[static_cast<int64_t>(gm) * e.ldo + gn] = y;
+  }
+}
+
+template <int EPI>
+static int launch_skinny(const GemmF32Params& p, cudaStream_t st) {
+  auto kern = gemm_f32_skinny_kernel<EPI>;
+  static bool configured = false;
+  if (!configured) {
+    SR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSkSmem));
+    configured = true;
+  }
+  dim3 grid(static_cast<unsigned>((p.N + kSkWarps * kSkNPerWarp - 1) / (kSkWarps * kSkNPerWarp)),
+            static_cast<unsigned>((p.M + kSkM - 1) / kSkM));
+  kern<<<grid, kSkWarps * 32, kSkSmem, st>>>(p);
+  return SR_OK;
+}
+
 // In-place q/k LayerNorm(d) + 2D RoPE on an fp32 [M, 3C] qkv buffer (check mode; attention.py:78-82).
 // One warp per (token, head, q|k); head_dim 64: lane holds features lane and lane+32.
 __global__ void __launch_bounds__(256)
@@ -137,12 +282,27 @@ extern "C" int sr_gemm_f32(const float* A, int64_t lda, const float* W, int64_t 
   dim3 grid(static_cast<unsigned>((N + kFBN - 1) / kFBN), static_cast<unsigned>((M + kFBM - 1) / kFBM));
   SR_REQUIRE(grid.y <= 65535, "sr_gemm_f32: M too large for this path");
   const int kind = epi->kind == SR_EPI_QKV ? SR_EPI_BIAS : epi->kind;
-  switch (kind) {
-    case SR_EPI_BIAS: gemm_f32_kernel<SR_EPI_BIAS><<<grid, 256, 0, st>>>(p); break;
-    case SR_EPI_BIAS_GELU: gemm_f32_kernel<SR_EPI_BIAS_GELU><<<grid, 256, 0, st>>>(p); break;
-    case SR_EPI_LS_RESIDUAL: gemm_f32_kernel<SR_EPI_LS_RESIDUAL><<<grid, 256, 0, st>>>(p); break;
-    case SR_EPI_BIAS_SILU: gemm_f32_kernel<SR_EPI_BIAS_SILU><<<grid, 256, 0, st>>>(p); break;
-    default: return fail(SR_ERR_SHAPE, "sr_gemm_f32: unknown epilogue kind %d", epi->kind);
+  // few rows against a big weight matrix (camera head): stream W once, warp-per-output-column
+  const bool skinny = M <= 128 && K >= 256 && K % 4 == 0 && lda % 4 == 0 && ldw % 4 == 0 &&
+                      ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(W)) & 15) == 0;
+  if (skinny) {
+    int rc = SR_OK;
+    switch (kind) {
+      case SR_EPI_BIAS: rc = launch_skinny<SR_EPI_BIAS>(p, st); break;
+      case SR_EPI_BIAS_GELU: rc = launch_skinny<SR_EPI_BIAS_GELU>(p, st); break;
+      case SR_EPI_LS_RESIDUAL: rc = launch_skinny<SR_EPI_LS_RESIDUAL>(p, st); break;
+      case SR_EPI_BIAS_SILU: rc = launch_skinny<SR_EPI_BIAS_SILU>(p, st); break;
+      default: return fail(SR_ERR_SHAPE, "sr_gemm_f32: unknown epilogue kind %d", epi->kind);
+    }
+    if (rc) return rc;
+  } else {
+    switch (kind) {
+      case SR_EPI_BIAS: gemm_f32_kernel<SR_EPI_BIAS><<<grid, 256, 0, st>>>(p); break;
+      case SR_EPI_BIAS_GELU: gemm_f32_kernel<SR_EPI_BIAS_GELU><<<grid, 256, 0, st>>>(p); break;
+      case SR_EPI_LS_RESIDUAL: gemm_f32_kernel<SR_EPI_LS_RESIDUAL><<<grid, 256, 0, st>>>(p); break;
+      case SR_EPI_BIAS_SILU: gemm_f32_kernel<SR_EPI_BIAS_SILU><<<grid, 256, 0, st>>>(p); break;
+      default: return fail(SR_ERR_SHAPE, "sr_gemm_f32: unknown epilogue kind %d", epi->kind);
+    }
   }
   ++g_launch_count;
   SR_CHECK_CUDA(cudaGetLastError());
