@@ -1,0 +1,71 @@
+#!/usr/bin/env python
+"""Per-shape timing of sr_attn_fwd_bf16 on the three aggregator attention shapes of agg32 (+ optional extra shapes).
+CUDA events on the launching stream, 3 warm-up + 10 timed launches per shape; inputs (>= 135 MB for global) rotate over
+4 buffers so that consecutive launches do not hit in L2.  Prints one JSON line per shape."""
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+from sailrecon_b200 import ops
+
+H, D, C = 16, 64, 1024
+dev = "cuda"
+
+
+def bench(name, batch, L, prefix_len=0, iters=10, check=False):
+    T = batch * L
+    g = torch.Generator(device=dev).manual_seed(0)
+    nbuf = 4 if T * 3 * C * 2 < 600e6 else 1
+    qkvs = [(torch.randn(T, 3 * C, device=dev, generator=g) * 1.0).to(torch.bfloat16) for _ in range(nbuf)]
+    pre = None
+    if prefix_len:
+        pre = (torch.randn(prefix_len, 2 * C, device=dev, generator=g)).to(torch.bfloat16)
+    out = torch.empty(T, C, device=dev, dtype=torch.bfloat16)
+
+    def run(i):
+        qkv = qkvs[i % nbuf]
+        ops.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], out, H, D, batch, L, L, L, L,
+                      prefix_k=None if pre is None else pre[:, :C], prefix_v=None if pre is None else pre[:, C:],
+                      prefix_len=prefix_len)
+    for i in range(3):
+        run(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        run(i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    flops = 4.0 * batch * L * (prefix_len + L) * C
+    rec = {"shape": name, "batch": batch, "L": L, "prefix": prefix_len, "ms": round(ms, 4), "tflops": round(flops / ms / 1e9, 1)}
+    if check:
+        # fp32 reference on a few heads / segments (bf16 inputs, fp32 math)
+        qkv = qkvs[(iters - 1) % nbuf].float()
+        errs = []
+        for b in (0, batch - 1):
+            for h in (0, H - 1):
+                q = qkv[b * L:(b + 1) * L, h * D:(h + 1) * D]
+                k = qkv[b * L:(b + 1) * L, C + h * D:C + (h + 1) * D]
+                v = qkv[b * L:(b + 1) * L, 2 * C + h * D:2 * C + (h + 1) * D]
+                if pre is not None:
+                    k = torch.cat([pre[:, h * D:(h + 1) * D].float(), k])
+                    v = torch.cat([pre[:, C + h * D:C + (h + 1) * D].float(), v])
+                rows = slice(0, min(L, 2048))
+                ref = torch.softmax(q[rows] @ k.t() * D ** -0.5, -1) @ v
+                got = out[b * L:(b + 1) * L, h * D:(h + 1) * D].float()[rows]
+                errs.append(float((got - ref).norm() / ref.norm()))
+        rec["rel_l2_max"] = max(errs)
+    print(json.dumps(rec), flush=True)
+
+
+if __name__ == "__main__":
+    check = "--check" in sys.argv
+    bench("global16", 1, 16 * 1374, check=check)
+    bench("frame32", 32, 1374, check=check)
+    bench("reloc16", 16, 1374, prefix_len=16 * 305, check=check)
+    if "--big" in sys.argv:
+        bench("global64", 1, 64 * 1374, iters=3)

@@ -21,6 +21,8 @@
 // MUFU.EX2 without range wrappers, F2FP packed conversion.
 // Optional carry of (m, l, un-normalised O) in/out turns one call into a step of ring attention
 // (global blocks sharded over ranks).
+#include <cstdlib>
+
 #include "common.cuh"
 #include "sr_internal.h"
 
@@ -51,6 +53,7 @@ struct AttnParams {
   int n_prefix_tiles, n_own_tiles;
   int64_t total_q_rows;
   float scale_log2;
+  int lag_ns;                    // start-up lag of the second softmax warpgroup (de-phases the two MUFU streams)
 };
 
 // ---- packed fp32 helpers (FFMA2 / FADD2 on sm_100) and bare MUFU.EX2
@@ -77,6 +80,36 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
 }
+// exp2 of a packed pair on the FMA / ALU pipes instead of the MUFU unit (16 exponentials / clk / SM is the binding
+// resource of this kernel): round-to-nearest split x = i + f via the 1.5 * 2^23 magic add, f in [-0.5, 0.5],
+// degree-3 minimax polynomial for 2^f (max relative error 7.5e-5, far below the bf16 rounding of P that follows), and
+// the integer part added straight into the exponent field.  x is clamped at -126 so the exponent cannot wrap.
+__device__ __forceinline__ void ex2_poly2(uint64_t x2, float& e0, float& e1) {
+  float x0, x1;
+  unpack2(x2, x0, x1);
+  x0 = fmaxf(x0, -126.0f);
+  x1 = fmaxf(x1, -126.0f);
+  const uint64_t xc = pack2(x0, x1);
+  const uint64_t t2 = add2(xc, pack2(12582912.0f, 12582912.0f));
+  const uint64_t i2 = add2(t2, pack2(-12582912.0f, -12582912.0f));
+  const uint64_t f2 = fma2(i2, pack2(-1.0f, -1.0f), xc);
+  uint64_t p2 = fma2(pack2(0.0551716685f, 0.0551716685f), f2, pack2(0.2426111251f, 0.2426111251f));
+  p2 = fma2(p2, f2, pack2(0.6932609677f, 0.6932609677f));
+  p2 = fma2(p2, f2, pack2(0.9999280572f, 0.9999280572f));
+  float t0, t1, p0, p1;
+  unpack2(t2, t0, t1);
+  unpack2(p2, p0, p1);
+  e0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+  e1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
+}
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 __device__ __forceinline__ float max3(float a, float b, float c) {
   float r;
   asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
@@ -88,6 +121,8 @@ __device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
   return r;
 }
 
+// kPoly = how many of every 8 element pairs take the polynomial exp2 (0 = all on MUFU.EX2)
+template <int kPoly>
 __global__ void __launch_bounds__(kAtThreads, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_k,
                const __grid_constant__ CUtensorMap tmap_v, const __grid_constant__ CUtensorMap tmap_pk,
@@ -145,10 +180,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
   const uint32_t tmem_O0 = tmem_base + kAtNQ * 128;           // + q * 64
   const uint32_t tmem_P0 = tmem_O0 + kAtNQ * 64;              // + q * 64   (128 bf16 per row = 64 columns)
 
-  // register re-distribution: the 4 control warps keep 80 registers, the 8 softmax warps (a 128-value fp32 row
-  // fragment per thread) grow to 208:  128 x 80 + 256 x 208 = 63488 <= 65536
+  // register re-distribution: the 4 control warps keep 72 registers, the 8 softmax warps (a 128-value fp32 row
+  // fragment per thread) grow to 216:  128 x 72 + 256 x 216 = 64512 <= 65536
   if (warp < 4) {
-  asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
@@ -219,7 +254,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
   }
   } else {
     // ------------------------------------------------------------------ softmax warpgroups
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 208;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
     const int q = (warp - 4) >> 2;
     if (q < nq_valid) {
       const int quarter = warp & 3;
@@ -252,31 +287,14 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
       }
       const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
 
-      for (int j = 0; j < n_tiles; ++j) {
-        mbar_wait(&s_full[q], j & 1);
-        tc_fence_after();
-        uint32_t sraw[128];
-        {
-          uint32_t(&c0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sraw[0]);
-          uint32_t(&c1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sraw[32]);
-          uint32_t(&c2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sraw[64]);
-          uint32_t(&c3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&sraw[96]);
-          tmem_ld32(tS, c0);
-          tmem_ld32(tS + 32, c1);
-          tmem_ld32(tS + 64, c2);
-          tmem_ld32(tS + 96, c3);
-          tmem_ld_wait();
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&s_free[q]);     // S_q may be overwritten by Q_q K(j+1)^T
-        // valid kv columns of this tile (only the last tile of the prefix / own range is partial)
-        int valid = 128;
-        if (j < p.n_prefix_tiles) {
-          if (j == p.n_prefix_tiles - 1) valid = p.prefix_len - j * 128;
-        } else if (j == n_tiles - 1) {
-          valid = p.kv_len - (j - p.n_prefix_tiles) * 128;
-        }
+      // valid kv columns of tile j (only the last tile of the prefix / own range is partial)
+      auto valid_cols = [&](int j) {
+        if (j < p.n_prefix_tiles) return j == p.n_prefix_tiles - 1 ? p.prefix_len - j * 128 : 128;
+        return j == n_tiles - 1 ? p.kv_len - (j - p.n_prefix_tiles) * 128 : 128;
+      };
+      // row max of sraw (masked to `valid` columns), in raw score units
+      uint32_t sraw[128];
+      auto row_max = [&](int valid) {
         if (valid < 128) {
 #pragma unroll
           for (int i = 0; i < 128; ++i)
@@ -295,7 +313,23 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         }
         mx0 = max3(mx0, __uint_as_float(sraw[124]), __uint_as_float(sraw[125]));
         mx1 = max3(mx1, __uint_as_float(sraw[126]), __uint_as_float(sraw[127]));
-        const float mx = fmaxf(max3(mx0, mx1, mx2), mx3) * p.scale_log2;   // scale > 0
+        return fmaxf(max3(mx0, mx1, mx2), mx3);
+      };
+
+      // Barrier probes: a (non-blocking) mbarrier.test_wait is issued one phase ahead of where its answer is needed,
+      // so the ~60-150 clk of a barrier round trip overlaps the exponentials instead of sitting between two phases.
+      bool s_ready = false;
+      if (q == 1 && p.lag_ns > 0) __nanosleep(p.lag_ns);
+      for (int j = 0; j < n_tiles; ++j) {
+        if (!s_ready) mbar_wait(&s_full[q], j & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
+        tmem_ld_wait();
+        tc_fence_before();
+        if (elect_one()) mbar_arrive(&s_free[q]);   // S_q may be overwritten by Q_q K(j+1)^T (wait::ld is warp-wide)
+        const float mx = row_max(valid_cols(j)) * p.scale_log2;            // scale > 0
+        const bool pv_ready = j > 0 && mbar_test_wait(&pv_done[q], (j - 1) & 1);
         float m_new = m;
         if (mx > m + kLazyRescaleLog2) m_new = mx;                         // also the first tile (m = -inf)
         const float alpha = ex2_approx(m - m_new);                         // 1 when unchanged, 0 on the first tile
@@ -308,10 +342,14 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
 #pragma unroll
           for (int t = 0; t < 4; ++t) {
             const uint64_t x2 = fma2(pack2(__uint_as_float(sraw[i + 2 * t]), __uint_as_float(sraw[i + 2 * t + 1])), scale2, negm2);
-            float x0, x1;
-            unpack2(x2, x0, x1);
-            e[2 * t] = ex2_approx(x0);
-            e[2 * t + 1] = ex2_approx(x1);
+            if ((((i >> 1) + t) & 7) < kPoly) {
+              ex2_poly2(x2, e[2 * t], e[2 * t + 1]);
+            } else {
+              float x0, x1;
+              unpack2(x2, x0, x1);
+              e[2 * t] = ex2_approx(x0);
+              e[2 * t + 1] = ex2_approx(x1);
+            }
             pk[(i >> 1) + t] = cvt_bf16x2(e[2 * t], e[2 * t + 1]);
           }
           sum0 = add2(sum0, pack2(e[0], e[1]));
@@ -323,16 +361,15 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         unpack2(add2(add2(sum0, sum1), add2(sum2, sum3)), r0, r1);
         l = l * alpha + (r0 + r1);
 
-        if (j > 0) {
-          mbar_wait(&pv_done[q], (j - 1) & 1);     // P_q and O_q are no longer in use by the tensor core
-          tc_fence_after();
-        }
+        if (j > 0 && !pv_ready) mbar_wait(&pv_done[q], (j - 1) & 1);   // P_q and O_q no longer in use by the tensor core
+        tc_fence_after();
         {
           uint32_t(&h0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&pk[0]);
           uint32_t(&h1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&pk[32]);
           tmem_st32(tP, h0);
           tmem_st32(tP + 32, h1);
         }
+        s_ready = j + 1 < n_tiles && mbar_test_wait(&s_full[q], (j + 1) & 1);
         const bool have_acc = (j > 0) || p.carry_in;
         if (have_acc && __any_sync(0xffffffffu, m_new != m)) {
           uint32_t o[32];
@@ -348,8 +385,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         tmem_st_wait();
         m = m_new;
         tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&p_full[q]);
+        if (elect_one()) mbar_arrive(&p_full[q]);
       }
 
       // ---------------------------------------------------------------- epilogue
@@ -401,6 +437,23 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
     tc_fence_after();
     tmem_dealloc<kAtTmemCols>(tmem_base);
   }
+}
+
+constexpr int kAtPolyDefault = 0;   // measured on B200: the kernel is latency- not MUFU-throughput-bound; poly does not pay yet
+
+template <int kPoly>
+static int launch_attn(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv,
+                       const CUtensorMap& tpk, const CUtensorMap& tpv, const AttnParams& p) {
+  auto kern = attn_tc_kernel<kPoly>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    SR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmem));
+    configured = true;
+  }
+  kern<<<grid, kAtThreads, kAtSmem, st>>>(tq, tk, tv, tpk, tpv, p);
+  ++g_launch_count;
+  SR_CHECK_CUDA(cudaGetLastError());
+  return SR_OK;
 }
 
 }  // namespace sr
@@ -479,16 +532,20 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
   p.n_own_tiles = (p.kv_len + 127) / 128;
   p.total_q_rows = a->batch > 1 ? static_cast<int64_t>(a->batch - 1) * a->q_batch_stride + a->q_len : a->q_len;
   p.scale_log2 = a->scale * 1.4426950408889634f;
+  p.lag_ns = 0;
+  if (const char* env = getenv("SR_ATTN_LAG_NS")) p.lag_ns = atoi(env);
 
-  static bool configured = false;
-  if (!configured) {
-    SR_CHECK_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAtSmem));
-    configured = true;
-  }
   dim3 grid(static_cast<unsigned>((a->q_len + 128 * kAtNQ - 1) / (128 * kAtNQ)), static_cast<unsigned>(a->num_heads),
             static_cast<unsigned>(a->batch));
-  attn_tc_kernel<<<grid, kAtThreads, kAtSmem, reinterpret_cast<cudaStream_t>(stream)>>>(tq, tk, tv, tpk, tpv, p);
-  ++g_launch_count;
-  SR_CHECK_CUDA(cudaGetLastError());
-  return SR_OK;
+  // tuning knob (profiling only): SR_ATTN_POLY = 0 / 2 / 3 / 4 polynomial-exp2 pairs out of 8; default kAtPolyDefault
+  int poly = kAtPolyDefault;
+  if (const char* env = getenv("SR_ATTN_POLY")) poly = atoi(env);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  switch (poly) {
+    case 0: return launch_attn<0>(grid, st, tq, tk, tv, tpk, tpv, p);
+    case 2: return launch_attn<2>(grid, st, tq, tk, tv, tpk, tpv, p);
+    case 3: return launch_attn<3>(grid, st, tq, tk, tv, tpk, tpv, p);
+    case 4: return launch_attn<4>(grid, st, tq, tk, tv, tpk, tpv, p);
+  }
+  return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16: SR_ATTN_POLY must be 0, 2, 3 or 4 (got %d)", poly);
 }
