@@ -224,6 +224,8 @@ def main():
     ap.add_argument("--frames", type=int, default=32)
     ap.add_argument("--size", type=int, default=518)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ring-frames", type=int, default=512)
+    ap.add_argument("--ring-depth", type=int, default=24)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

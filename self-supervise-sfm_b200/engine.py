@@ -221,7 +221,7 @@ class RowPositions:
 
 # ------------------------------------------------------------------------------------------------ the block schedule
 def qkv_rows(attn: nn.Module, a_in: torch.Tensor, out: torch.Tensor, mode: str, rows_pos: Optional[RowPositions],
-             col_offset: int = 0) -> torch.Tensor:
+             col_offset: int = 0, n_cols: Optional[int] = None) -> torch.Tensor:
     """qkv Linear + per-head q/k LayerNorm + RoPE (attention.py:73-82) on rows.  col_offset = C computes only the
     k|v columns (scene tokens are K/V producers only, aggregator.py:737)."""
     C = attn.qkv.weight.shape[1]
@@ -244,11 +244,12 @@ def qkv_rows(attn: nn.Module, a_in: torch.Tensor, out: torch.Tensor, mode: str, 
         epi_kind = SR_EPI_QKV
         epi = ops.QkvEpilogue(C, col_offset, d, qn, kn, attn.q_norm.eps if qn is not None else 1e-5, cos, sin, pos32)
     if mode == "bf16":
-        w = weight_bf16(attn.qkv)[col_offset:]
+        end = 3 * C if n_cols is None else col_offset + n_cols        # n_cols: only a column window (ring attention: q, then k|v)
+        w = weight_bf16(attn.qkv)[col_offset:end]
         b = bias_for(attn.qkv, mode)
-        ops.gemm(a_in, w, None if b is None else b[col_offset:], out, kind=epi_kind, qkv=epi)
+        ops.gemm(a_in, w, None if b is None else b[col_offset:end], out, kind=epi_kind, qkv=epi)
     else:
-        if col_offset:
+        if col_offset or n_cols is not None:
             raise ValueError("sailrecon_b200: the fp32 path computes the full qkv projection")
         ops.gemm(a_in, weight_f32(attn.qkv), bias_for(attn.qkv, mode), out, kind=epi_kind, qkv=epi)
     return out
@@ -290,6 +291,18 @@ def run_block(blk: nn.Module, x: torch.Tensor, calls: Sequence[AttnCall], rows_p
         qkv = WS.get(tag + "qkv", (T, 3 * C), act, dev)
         qkv_rows(attn, a, qkv, mode, rows_pos)
         attention_rows(attn, qkv, a, calls)              # `a` is free again: reuse it for the attention output
+    block_tail(blk, x, a, mode, tag, attn_zero)
+    return x
+
+
+def block_tail(blk: nn.Module, x: torch.Tensor, a: torch.Tensor, mode: str, tag: str = "", attn_zero: bool = False) -> torch.Tensor:
+    """Everything of Block.forward after the attention core: x += g1 * proj(a); x += g2 * mlp(LN2(x)) (block.py:110-111).
+    `a` [T, C] holds the attention output on entry and is reused as scratch."""
+    T, C = x.shape
+    dev = x.device
+    act = torch.bfloat16 if mode == "bf16" else torch.float32
+    attn, mlp = blk.attn, blk.mlp
+    if not attn_zero:
         wp = weight_bf16(attn.proj) if mode == "bf16" else weight_f32(attn.proj)
         ops.gemm(a, wp, bias_for(attn.proj, mode), x, kind=SR_EPI_LS_RESIDUAL, gamma=gamma_of(blk.ls1), resid=x)
     w2, b2, eps2 = ln_params(blk.norm2)

@@ -1,0 +1,290 @@
+"""Frame-sharded (sequence-parallel) global attention with ring K/V exchange — SURVEY.md §8(e), BASELINE.json configs[3].
+
+The reference has no sequence parallelism (DP only, train/train_imc.py:472); its global blocks
+(sailrecon/models/aggregator.py:743-769) run one SDPA over all Na*P anchor tokens on one GPU.  Here the anchor frames are
+partitioned into contiguous ranges, one per rank (one process per GPU).  Everything per-token (LayerNorm, QKV / proj /
+MLP GEMMs, LayerScale-residual) stays rank-local on the rank's rows; only the attention core couples ranks:
+
+    step s = 0 .. R-1:   O_r, m_r, l_r  <-  online-softmax merge of  Q_r  x  (K, V)_{(r - s) mod R}
+
+The K|V block of a rank ([T_r, 2C] bf16, post QK-norm / RoPE) travels around the ring: while the flash kernel works on
+block s (sr_attn_fwd_bf16 with the (m, l, acc) carry of include/sailrecon_b200.h), block s is forwarded to rank r+1 and
+block s+1 is received from rank r-1 into the other half of a double buffer (NCCL send/recv over NVLink 5 / NVSwitch,
+issued before the kernel so the transfer overlaps it).
+
+Why staged copies and not peer-memory loads from inside the attention kernel: every 256-row query tile re-reads the
+whole K/V block (343 query tiles per head at 64 frames per rank).  Local reads of that pattern are L2 hits; peer
+addresses bypass the local L2, so direct peer TMA loads would put the same bytes on NVLink hundreds of times.  One copy
+per block per step is 2 * T_r * C * 2 B = 360 MB per step at R = 8, Na = 512 (0.47 ms at 770 GB/s) against 40 ms of
+attention math per step at 800 TFLOP/s: the exchange is ~1 % of the step and fully hidden.
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+from dataclasses import dataclass
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+from . import engine
+from .engine import RowPositions
+
+
+# ------------------------------------------------------------------------------------------------ partition
+def partition_frames(n_frames: int, world: int) -> List[Tuple[int, int]]:
+    """Contiguous, balanced frame ranges: [(first_frame, count)] per rank; the first n_frames % world ranks get one
+    extra frame.  Ranks beyond n_frames get (n_frames, 0)."""
+    if n_frames < 0 or world <= 0:
+        raise ValueError("partition_frames: n_frames >= 0 and world > 0 required")
+    base, extra = divmod(n_frames, world)
+    out, start = [], 0
+    for r in range(world):
+        c = base + (1 if r < extra else 0)
+        out.append((start, c))
+        start += c
+    return out
+
+
+@dataclass
+class RingPlan:
+    """Who holds what and the order blocks arrive in: at step s rank r works on the K/V block of rank (r - s) mod R."""
+    rank: int
+    world: int
+    tokens_per_frame: int
+    frames: List[Tuple[int, int]]                      # per rank (first_frame, count)
+
+    @classmethod
+    def make(cls, n_frames: int, tokens_per_frame: int, rank: int, world: int) -> "RingPlan":
+        fr = partition_frames(n_frames, world)
+        if any(c == 0 for _, c in fr):
+            raise ValueError(f"ring attention needs at least one frame per rank (frames {n_frames}, ranks {world})")
+        return cls(rank, world, tokens_per_frame, fr)
+
+    def rows(self, r: Optional[int] = None) -> int:
+        return self.frames[self.rank if r is None else r][1] * self.tokens_per_frame
+
+    def row0(self, r: Optional[int] = None) -> int:
+        return self.frames[self.rank if r is None else r][0] * self.tokens_per_frame
+
+    @property
+    def max_rows(self) -> int:
+        return max(c for _, c in self.frames) * self.tokens_per_frame
+
+    def source(self, step: int) -> int:
+        return (self.rank - step) % self.world
+
+    @property
+    def next_rank(self) -> int:
+        return (self.rank + 1) % self.world
+
+    @property
+    def prev_rank(self) -> int:
+        return (self.rank - 1) % self.world
+
+
+# ------------------------------------------------------------------------------------------------ the ring
+@dataclass
+class Carry:
+    """Online-softmax state across ring steps (sr_attn.carry_*): running row max m and row sum l in the log2 domain,
+    fp32 [H, T]; un-normalised accumulator fp32 [T, H*d]."""
+    m: torch.Tensor
+    l: torch.Tensor
+    acc: torch.Tensor
+
+    @classmethod
+    def empty(cls, rows: int, heads: int, head_dim: int, device) -> "Carry":
+        return cls(torch.empty(heads, rows, dtype=torch.float32, device=device),
+                   torch.empty(heads, rows, dtype=torch.float32, device=device),
+                   torch.empty(rows, heads * head_dim, dtype=torch.float32, device=device))
+
+
+def _cuda_step(q, kv, n_kv, out, carry: Optional[Carry], carry_in: bool, carry_out: bool, heads: int, head_dim: int,
+               scale: float) -> None:
+    """One ring step on the GPU: the tcgen05 flash kernel over one K/V block (no CPU path exists)."""
+    from . import ops
+    C = heads * head_dim
+    ops.attention(q, kv[:n_kv, :C], kv[:n_kv, C:], None if carry_out else out, heads, head_dim, 1, q.shape[0], n_kv,
+                  scale=scale, carry=None if carry is None else (carry.m, carry.l, carry.acc), carry_in=carry_in,
+                  carry_out=carry_out)
+
+
+def ring_attention(q: torch.Tensor, kv_bufs: Sequence[torch.Tensor], out: torch.Tensor, plan: RingPlan, heads: int,
+                   head_dim: int, scale: float, carry: Optional[Carry], group=None,
+                   step_fn: Callable = _cuda_step) -> torch.Tensor:
+    """softmax(Q_r [K_0 .. K_{R-1}]^T) [V_0 .. V_{R-1}] for this rank's query rows.
+
+    q [T_r, C]; kv_bufs = two [max_rows, 2C] buffers, kv_bufs[0][:T_r] holding this rank's own K|V block on entry (both
+    are overwritten); out [T_r, C].  Per step: post (isend current block -> next rank, irecv next block <- previous
+    rank), launch the attention step on the current block, then make the compute stream wait for the transfer.  The
+    transfer is enqueued BEFORE the kernel, so it runs under it; the receive buffer was last read two steps ago.
+    `step_fn` is the attention step (the CUDA kernel; tests inject a reference to exercise the schedule on CPU)."""
+    R = plan.world
+    if R == 1:
+        step_fn(q, kv_bufs[0], plan.rows(), out, None, False, False, heads, head_dim, scale)
+        return out
+    if carry is None:
+        raise ValueError("ring_attention: carry buffers are required when world > 1")
+    for s in range(R):
+        cur, nxt = kv_bufs[s % 2], kv_bufs[(s + 1) % 2]
+        n_cur = plan.rows(plan.source(s))
+        reqs = []
+        if s + 1 < R:
+            n_nxt = plan.rows(plan.source(s + 1))
+            ops_ = [dist.P2POp(dist.isend, cur[:n_cur], _global_rank(group, plan.next_rank), group),
+                    dist.P2POp(dist.irecv, nxt[:n_nxt], _global_rank(group, plan.prev_rank), group)]
+            reqs = dist.batch_isend_irecv(ops_)
+        step_fn(q, cur, n_cur, out, carry, s > 0, s + 1 < R, heads, head_dim, scale)
+        for r in reqs:
+            r.wait()
+    return out
+
+
+def _global_rank(group, group_rank: int) -> int:
+    return group_rank if group is None else dist.get_global_rank(group, group_rank)
+
+
+# ------------------------------------------------------------------------------------------------ sharded global block
+class RingWorkspace:
+    """Per-rank buffers of the sharded global stack, allocated once (sized for the largest shard)."""
+
+    def __init__(self, plan: RingPlan, C: int, heads: int, device, act=torch.bfloat16):
+        T, Tm = plan.rows(), plan.max_rows
+        self.a = torch.empty(T, C, dtype=act, device=device)              # LN output / attention output
+        self.q = torch.empty(T, C, dtype=act, device=device)
+        self.kv = [torch.empty(Tm, 2 * C, dtype=act, device=device) for _ in range(2)]
+        self.carry = Carry.empty(T, heads, C // heads, device) if plan.world > 1 else None
+
+
+def ring_global_block(blk, x: torch.Tensor, rows_pos: Optional[RowPositions], plan: RingPlan, ws: RingWorkspace,
+                      group=None, mode: str = "bf16") -> torch.Tensor:
+    """One global Block (aggregator.py:743-769 -> block.py:86-112) on this rank's anchor rows x [T_r, C] (fp32, in place),
+    attending to the anchor rows of every rank."""
+    from . import ops
+    if mode != "bf16":
+        raise NotImplementedError("sailrecon_b200: the ring path runs the bf16 (autocast) mode")
+    attn = blk.attn
+    C = x.shape[1]
+    T = plan.rows()
+    if x.shape[0] != T:
+        raise ValueError(f"ring_global_block: rank {plan.rank} owns {T} rows, got {x.shape[0]}")
+    w1, b1, eps1 = engine.ln_params(blk.norm1)
+    ops.layernorm(x, w1, b1, eps1, ws.a)
+    engine.qkv_rows(attn, ws.a, ws.q, mode, rows_pos, col_offset=0, n_cols=C)              # q columns
+    engine.qkv_rows(attn, ws.a, ws.kv[0][:T], mode, rows_pos, col_offset=C, n_cols=2 * C)  # k | v, contiguous for the ring
+    ring_attention(ws.q, ws.kv, ws.a, plan, attn.num_heads, C // attn.num_heads, attn.scale, ws.carry, group)
+    engine.block_tail(blk, x, ws.a, mode, tag="ring.")
+    return x
+
+
+def run_global_stack(blocks, x: torch.Tensor, rows_pos: Optional[RowPositions], plan: RingPlan, group=None,
+                     ws: Optional[RingWorkspace] = None) -> torch.Tensor:
+    """All global blocks over the sharded anchor tokens (the O(L^2) term of the aggregator, BASELINE.json configs[3])."""
+    blk0 = blocks[0]
+    ws = ws or RingWorkspace(plan, x.shape[1], blk0.attn.num_heads, x.device)
+    for blk in blocks:
+        ring_global_block(blk, x, rows_pos, plan, ws, group)
+    return x
+
+
+# ------------------------------------------------------------------------------------------------ bench (bench.py --workload ring)
+def _frame_tokens(frame: int, P: int, C: int, device) -> torch.Tensor:
+    """Synthetic anchor tokens of one frame, ~N(0,1), seeded by the GLOBAL frame index so every world size sees the
+    same scene."""
+    g = torch.Generator(device=device)
+    g.manual_seed(2_000_003 + frame)
+    return torch.randn(P, C, generator=g, device=device, dtype=torch.float32)
+
+
+def bench_ring(args, rank: int, world: int, local: int) -> None:
+    """BASELINE.json configs[3]: the 24 global blocks over `--ring-frames` (512) anchor frames of 518x518 (1374 tokens
+    each), frames sharded over the ranks, ring K/V over NVLink.  Strong scaling: total work is fixed as N grows.
+    One step = one pass of the whole sharded stack; value = frames / s."""
+    from .layers.block import Block
+    from .layers.rope import PositionGetter, RotaryPositionEmbedding2D
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --workload ring needs B200s: sailrecon_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+    C, H, P, patch = 1024, 16, 1374, 14
+    n_frames, depth = args.ring_frames, args.ring_depth
+    plan = RingPlan.make(n_frames, P, rank, world)
+    torch.manual_seed(0)                                   # identical weights on every rank
+    rope = RotaryPositionEmbedding2D(frequency=100)
+    with torch.device(dev):
+        blocks = torch.nn.ModuleList([Block(dim=C, num_heads=H, mlp_ratio=4.0, init_values=0.01, qk_norm=True, rope=rope)
+                                      for _ in range(depth)]).eval()
+    f0, fc = plan.frames[rank]
+    x0 = torch.cat([_frame_tokens(f, P, C, dev) for f in range(f0, f0 + fc)], dim=0)
+    hw = 518 // patch
+    grid = PositionGetter()(1, hw, hw, dev)[0] + 1
+    frame_pos = torch.cat([torch.zeros(5, 2, dtype=grid.dtype, device=dev), grid], 0).to(torch.int32)
+    rows_pos = RowPositions(frame_pos.repeat(fc, 1).contiguous(), hw + 1)
+    ws = RingWorkspace(plan, C, H, dev)
+    x = torch.empty_like(x0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        x.copy_(x0)
+        with torch.no_grad():
+            run_global_stack(blocks, x, rows_pos, plan, None, ws)
+
+    from . import ops
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    import bench as _bench                                   # clock sampler + peaks live in bench.py
+    clocks = _bench.ClockSampler(local)
+    clocks.start()
+    n0 = ops.num_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    launches = ops.num_kernel_launches() - n0
+    clk = clocks.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    finite = bool(torch.isfinite(x).all())
+    probe = float(x[:P].double().norm()) if rank == 0 else 0.0      # frame 0 lives on rank 0 for every world size
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    if rank == 0:
+        L = n_frames * P
+        flops_attn = depth * 4.0 * L * L * C
+        flops_lin = depth * L * 24.0 * C * C
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak_tf = peaks.get("bf16_tflops_sustained", 1400.0)
+        achieved = (flops_attn + flops_lin) / (ms * 1e-3) / 1e12 / world
+        kv_bytes = 2 * plan.max_rows * C * 2
+        line = {"metric": "global-attention stack frames/s at N=%d (518px), sequence-sharded" % n_frames,
+                "value": n_frames / (ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": f"ring: {depth} global blocks over {n_frames} anchor frames x {P} tokens, frames sharded "
+                                       f"over {world} rank(s), ring K/V ({kv_bytes / 1e6:.0f} MB per step per rank) over NCCL send/recv",
+                           "l2": "K/V block per head (>= 11 MB) x 16 heads and the fp32 carry exceed L2; no flush needed"},
+                "gpu_launches": launches, "clocks": clk,
+                "roofline": {"bound": "tensor", "kernel": "attn_tc + gemm_tc (whole stack)", "achieved": achieved, "peak": peak_tf,
+                             "unit": "TFLOP/s", "frac": achieved / peak_tf, "traffic": None,
+                             "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if peaks else "fallback"},
+                "algorithmic_tflop_per_step": (flops_attn + flops_lin) / 1e12, "frame0_out_l2": probe, "outputs_finite": finite}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
