@@ -53,7 +53,7 @@ def _digest() -> str:
     deps = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [HEADER]
     for path in deps:
         with open(path, "rb") as f:
-            h.update(path.encode())
+            h.update(os.path.basename(path).encode())      # not the absolute path: the snapshot lives elsewhere on the GPU box
             h.update(f.read())
     h.update(" ".join(NVCC_FLAGS).encode())
     return h.hexdigest()
@@ -87,14 +87,21 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
         return LIB_PATH
     os.makedirs(LIB_DIR, exist_ok=True)
     os.makedirs(OBJ_DIR, exist_ok=True)
-    with concurrent.futures.ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
-        objs = list(ex.map(lambda s: _compile(s, verbose), SOURCES))
-    cmd = [_nvcc(), "-shared", "-o", LIB_PATH, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    with open(LIB_PATH + ".sha256", "w") as f:
-        f.write(_digest())
+    import fcntl
+    with open(os.path.join(LIB_DIR, ".build.lock"), "w") as lock:        # one builder at a time (torchrun: N ranks)
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if not force and is_current():                                    # another rank built it while we waited
+            return LIB_PATH
+        with concurrent.futures.ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
+            objs = list(ex.map(lambda s: _compile(s, verbose), SOURCES))
+        tmp = LIB_PATH + f".tmp{os.getpid()}"
+        cmd = [_nvcc(), "-shared", "-o", tmp, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+        os.replace(tmp, LIB_PATH)                                         # atomic: a concurrent dlopen never sees a partial file
+        with open(LIB_PATH + ".sha256", "w") as f:
+            f.write(_digest())
     return LIB_PATH
 
 

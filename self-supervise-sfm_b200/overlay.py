@@ -1,0 +1,25 @@
+"""Drop-in overlay: make the reference's own `sailrecon.models.sail_recon.SailRecon` (and through it
+train/demo_imc_forward.py, train/demo_imc.py) build its aggregator and camera head from this package.
+
+    import sailrecon_b200.overlay as overlay
+    overlay.install()                      # before `import sailrecon.models.sail_recon`
+    from sailrecon.models.sail_recon import SailRecon
+
+Only `sys.modules` aliases are installed; the reference tree is not modified.
+"""
+from __future__ import annotations
+
+import importlib
+import sys
+
+_LAYER_MODULES = ("attention", "block", "rope", "mlp", "layer_scale", "patch_embed", "vision_transformer")
+
+
+def install() -> None:
+    if "sailrecon.models.sail_recon" in sys.modules:
+        raise RuntimeError("sailrecon_b200.overlay.install() must run before sailrecon.models.sail_recon is imported")
+    pkg = __name__.rsplit(".", 1)[0]
+    sys.modules["sailrecon.models.aggregator"] = importlib.import_module(pkg + ".models.aggregator")
+    sys.modules["sailrecon.heads.camera_head"] = importlib.import_module(pkg + ".heads.camera_head")
+    for name in _LAYER_MODULES:
+        sys.modules[f"sailrecon.layers.{name}"] = importlib.import_module(f"{pkg}.layers.{name}")
