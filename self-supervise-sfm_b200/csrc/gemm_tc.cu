@@ -43,10 +43,29 @@ struct GemmCfg {
   static constexpr int kTmemCols = 2 * BN;                         // double-buffered accumulator
 };
 
+// Exact-erf GELU (mlp.py:36, nn.GELU()) for the tensor-core epilogue: erf by Abramowitz-Stegun 7.1.26
+// (|error| <= 1.5e-7, four orders below the bf16 rounding that follows) = 2 MUFU + ~13 FMA-pipe instructions per value
+// instead of the ~27 of erff(); the fp32 check path (gemm_f32.cu) keeps erff().
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
+  const float erf_abs = fmaf(-poly * t, e, 1.0f);          // erf(|x| / sqrt 2)
+  const float hx = 0.5f * x;
+  return fmaf(fabsf(hx), erf_abs, hx);                     // 0.5 x (1 + sign(x) erf_abs)
+}
+
 // ---------------------------------------------------------------------------------------------- epilogues
 // v[32] = raw fp32 accumulators of row `row`, columns [col, col+32) of the output.
 template <int EPI, bool OUT_BF16>
-__device__ __forceinline__ void epi_store32(const GemmParams& p, int row, int col, uint32_t (&v)[32]) {
+__device__ __forceinline__ void epi_store32(const GemmParams& p, int row, int col, uint32_t (&v)[32],
+                                            const float4* resid_regs = nullptr) {
   const sr_epilogue_t& e = p.e;
   float x[32];
 #pragma unroll
@@ -59,14 +78,13 @@ __device__ __forceinline__ void epi_store32(const GemmParams& p, int row, int co
   }
   if (EPI == SR_EPI_BIAS_GELU) {
 #pragma unroll
-    for (int i = 0; i < 32; ++i) x[i] = gelu_erf(bf16_round(x[i]));
+    for (int i = 0; i < 32; ++i) x[i] = gelu_erf_fast(bf16_round(x[i]));
   }
   if (EPI == SR_EPI_LS_RESIDUAL) {
-    const float* r = e.resid + static_cast<int64_t>(row) * e.ldr + col;
     float* o = reinterpret_cast<float*>(e.out) + static_cast<int64_t>(row) * e.ldo + col;
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
-      float4 rr = *reinterpret_cast<const float4*>(r + i);
+      const float4 rr = resid_regs[i >> 2];                  // loaded before the accumulator was ready (see kernel)
       float4 g = e.gamma ? __ldg(reinterpret_cast<const float4*>(e.gamma + col + i)) : make_float4(1.f, 1.f, 1.f, 1.f);
       float4 y;
       y.x = rr.x + g.x * bf16_round(x[i + 0]);
@@ -95,10 +113,32 @@ __device__ __forceinline__ void epi_store32(const GemmParams& p, int row, int co
   }
 }
 
+// RoPE table rows of one token, fetched before the accumulator is ready (pos -> table is a dependent load chain).
+struct RopeRow {
+  float c[2][16];   // [y | x][frequency]
+  float s[2][16];
+};
+__device__ __forceinline__ void load_rope_row(const sr_epilogue_t& e, int row, RopeRow& rr) {
+  const int2 yx = __ldg(reinterpret_cast<const int2*>(e.pos) + row);
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int ppos = half == 0 ? yx.x : yx.y;
+    const float4* ct = reinterpret_cast<const float4*>(e.rope_cos + static_cast<int64_t>(ppos) * 16);
+    const float4* st = reinterpret_cast<const float4*>(e.rope_sin + static_cast<int64_t>(ppos) * 16);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float4 c = __ldg(ct + i), sn = __ldg(st + i);
+      rr.c[half][4 * i + 0] = c.x; rr.c[half][4 * i + 1] = c.y; rr.c[half][4 * i + 2] = c.z; rr.c[half][4 * i + 3] = c.w;
+      rr.s[half][4 * i + 0] = sn.x; rr.s[half][4 * i + 1] = sn.y; rr.s[half][4 * i + 2] = sn.z; rr.s[half][4 * i + 3] = sn.w;
+    }
+  }
+}
+
 // One 64-wide head of q or k for one token: bias -> bf16 round -> LayerNorm(64) -> 2D RoPE -> bf16 store.
-// `which` = 0 (q) / 1 (k) / 2 (v: bias + store only).
+// `which` = 0 (q) / 1 (k) / 2 (v: bias + store only).  Reductions run as 4 independent chains: with 2 epilogue warps per
+// SM sub-partition a 64-long dependent FADD chain is pure exposed latency.
 __device__ __forceinline__ void epi_qkv_head(const GemmParams& p, int row, int col, int which, uint32_t (&v0)[32],
-                                             uint32_t (&v1)[32]) {
+                                             uint32_t (&v1)[32], const RopeRow& rope) {
   const sr_epilogue_t& e = p.e;
   float x[64];
 #pragma unroll
@@ -118,14 +158,17 @@ __device__ __forceinline__ void epi_qkv_head(const GemmParams& p, int row, int c
 #pragma unroll
     for (int i = 0; i < 64; ++i) x[i] = bf16_round(x[i]);
     if (e.qk_norm) {
-      float mean = 0.f;
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) mean += x[i];
-      mean *= (1.0f / 64.0f);
-      float var = 0.f;
+      for (int i = 0; i < 64; i += 4) { s0 += x[i]; s1 += x[i + 1]; s2 += x[i + 2]; s3 += x[i + 3]; }
+      const float mean = ((s0 + s1) + (s2 + s3)) * (1.0f / 64.0f);
+      float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { float d = x[i] - mean; var += d * d; }
-      float rstd = rsqrtf(var * (1.0f / 64.0f) + e.qk_eps);
+      for (int i = 0; i < 64; i += 4) {
+        const float d0 = x[i] - mean, d1 = x[i + 1] - mean, d2 = x[i + 2] - mean, d3 = x[i + 3] - mean;
+        q0 = fmaf(d0, d0, q0); q1 = fmaf(d1, d1, q1); q2 = fmaf(d2, d2, q2); q3 = fmaf(d3, d3, q3);
+      }
+      const float rstd = rsqrtf(((q0 + q1) + (q2 + q3)) * (1.0f / 64.0f) + e.qk_eps);
       const float* w = which == 0 ? e.qn_w : e.kn_w;
       const float* b = which == 0 ? e.qn_b : e.kn_b;
 #pragma unroll
@@ -141,23 +184,13 @@ __device__ __forceinline__ void epi_qkv_head(const GemmParams& p, int row, int c
     if (e.rope) {
       // rope.py:196-207: first 32 features rotate with the y position, last 32 with x; inside each half the
       // pairs are (i, i+16) (rotate-half, rope.py:136-138) and both members share frequency i (rope.py:119).
-      int2 yx = __ldg(reinterpret_cast<const int2*>(e.pos) + row);
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
-        int ppos = half == 0 ? yx.x : yx.y;
-        const float* ct = e.rope_cos + static_cast<int64_t>(ppos) * 16;
-        const float* st = e.rope_sin + static_cast<int64_t>(ppos) * 16;
 #pragma unroll
-        for (int i = 0; i < 16; i += 4) {
-          float4 c = __ldg(reinterpret_cast<const float4*>(ct + i));
-          float4 s = __ldg(reinterpret_cast<const float4*>(st + i));
-          float cc[4] = {c.x, c.y, c.z, c.w}, ss[4] = {s.x, s.y, s.z, s.w};
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float a = x[half * 32 + i + j], b = x[half * 32 + 16 + i + j];
-            x[half * 32 + i + j] = a * cc[j] - b * ss[j];
-            x[half * 32 + 16 + i + j] = b * cc[j] + a * ss[j];
-          }
+        for (int i = 0; i < 16; ++i) {
+          const float a = x[half * 32 + i], b = x[half * 32 + 16 + i];
+          x[half * 32 + i] = a * rope.c[half][i] - b * rope.s[half][i];
+          x[half * 32 + 16 + i] = b * rope.c[half][i] + a * rope.s[half][i];
         }
       }
     }
@@ -217,6 +250,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_slot;
 
+  // register re-distribution: the 4 control warps keep 72 registers, the 8 epilogue warps (which hold a 128-wide fp32
+  // residual row fragment across the accumulator wait) grow to 216:  128 x 72 + 256 x 216 = 64512 <= 65536
+  if (warp < kEpiWarp0) {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
@@ -265,8 +302,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         umma_commit(&tmem_full_bar[as]);
       }
     }
-  } else if (warp >= kEpiWarp0) {
+  }
+  } else {
     // ------------------------------------------------------------------ epilogue
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
     const int ew = warp - kEpiWarp0;
     const int quarter = warp & 3;          // TMEM lane quarter this warp may access
     const int half = ew >> 2;              // which half of the BN columns
@@ -275,11 +314,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
       const int m_blk = t / num_n, n_blk = t % num_n;
       const int as = it & 1;
-      mbar_wait(&tmem_full_bar[as], (it >> 1) & 1);
-      tc_fence_after();
       const int row = m_blk * kBM + quarter * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN + half * kColsPerWarp;
       const int col_base = n_blk * BN + half * kColsPerWarp;
+      // LayerScale-residual epilogue: the fp32 residual row fragment does not depend on the accumulator, so its loads
+      // are issued BEFORE the wait for the MMA and fly under it (they were the epilogue's critical path: every chunk
+      // used to stall a full memory latency after the accumulator was ready).
+      float4 resid_regs[EPI == SR_EPI_LS_RESIDUAL ? kColsPerWarp / 4 : 1];
+      if (EPI == SR_EPI_LS_RESIDUAL && row < p.M) {
+        const float4* r4 = reinterpret_cast<const float4*>(p.e.resid + static_cast<int64_t>(row) * p.e.ldr + col_base);
+#pragma unroll
+        for (int i = 0; i < kColsPerWarp / 4; ++i) resid_regs[i] = r4[i];
+      }
+      RopeRow rope_row;
+      if (EPI == SR_EPI_QKV && p.e.rope && row < p.M && p.e.col_offset + col_base < 2 * p.e.qkv_dim)
+        load_rope_row(p.e, row, rope_row);
+      mbar_wait(&tmem_full_bar[as], (it >> 1) & 1);
+      tc_fence_after();
       if (EPI == SR_EPI_QKV) {
 #pragma unroll 1
         for (int c = 0; c < kColsPerWarp; c += 64) {
@@ -290,16 +341,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
           if (row < p.M) {
             const int col = col_base + c;
             const int which = static_cast<int>((p.e.col_offset + col) / p.e.qkv_dim);
-            epi_qkv_head(p, row, col, which, v0, v1);
+            epi_qkv_head(p, row, col, which, v0, v1, rope_row);
           }
         }
       } else {
+        if (EPI == SR_EPI_LS_RESIDUAL) {
+#pragma unroll
+          for (int c = 0; c < kColsPerWarp; c += 32) {
+            uint32_t v[32];
+            tmem_ld32(taddr + c, v);
+            tmem_ld_wait();
+            if (row < p.M) epi_store32<EPI, OUT_BF16>(p, row, col_base + c, v, &resid_regs[c / 4]);
+          }
+        } else {
 #pragma unroll 1
-        for (int c = 0; c < kColsPerWarp; c += 32) {
-          uint32_t v[32];
-          tmem_ld32(taddr + c, v);
-          tmem_ld_wait();
-          if (row < p.M) epi_store32<EPI, OUT_BF16>(p, row, col_base + c, v);
+          for (int c = 0; c < kColsPerWarp; c += 32) {
+            uint32_t v[32];
+            tmem_ld32(taddr + c, v);
+            tmem_ld_wait();
+            if (row < p.M) epi_store32<EPI, OUT_BF16>(p, row, col_base + c, v);
+          }
         }
       }
       tc_fence_before();
