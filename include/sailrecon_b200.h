@@ -114,6 +114,11 @@ typedef struct sr_attn {
   int32_t carry_out;     /* 1: write the state back and skip the final normalisation + out store           */
 } sr_attn_t;
 
+/* Profiling aid: with SR_ATTN_TRACE set in the environment, CTA (0,0,0) of sr_attn_fwd_bf16 records clock64() at its
+ * pipeline hand-offs for the first 64 K/V tiles; this copies the [3 roles][64 tiles][8 events] table to HOST memory
+ * (synchronises the device). */
+int sr_debug_trace_read(long long* host_dst, int64_t count);
+
 int sr_attn_fwd_bf16(const sr_attn_t* p, void* stream);  /* tcgen05 flash attention, head_dim 64           */
 int sr_attn_fwd_f32(const sr_attn_t* p, void* stream);   /* fp32 SIMT, head_dim <= 128 (check mode, camera) */
 

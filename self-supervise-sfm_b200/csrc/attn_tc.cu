@@ -53,8 +53,18 @@ struct AttnParams {
   int n_prefix_tiles, n_own_tiles;
   int64_t total_q_rows;
   float scale_log2;
+  int trace;                     // SR_ATTN_TRACE
   int lag_ns;                    // start-up lag of the second softmax warpgroup (de-phases the two MUFU streams)
 };
+
+// Profiling aid: SR_ATTN_TRACE=1 makes CTA (0,0,0) record clock64() at the pipeline hand-offs of its first 64 K/V tiles
+// (read back with sr_debug_trace_read, printed by scripts/attn_trace.py).  Layout: g_attn_trace[role][tile][event],
+// role 0 = softmax warp 4, 1 = MMA issuer of query tile 0, 2 = TMA producer.
+__device__ long long g_attn_trace[3 * 64 * 8];
+#define SR_TRACE(role, j, ev)                                                           \
+  do {                                                                                  \
+    if (trace_on && (j) < 64) g_attn_trace[((role) * 64 + (j)) * 8 + (ev)] = clock64(); \
+  } while (0)
 
 // ---- packed fp32 helpers (FFMA2 / FADD2 on sm_100) and bare MUFU.EX2
 __device__ __forceinline__ uint64_t pack2(float lo, float hi) {
@@ -145,6 +155,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
   const int q0 = blockIdx.x * (128 * kAtNQ);                 // first query row (within the segment) of this CTA
   const int nq_valid = (q0 + 128 < p.q_len) ? 2 : 1;         // second tile entirely past q_len -> skipped
   const int n_tiles = p.n_prefix_tiles + p.n_own_tiles;
+  const bool trace_on = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
@@ -195,10 +206,12 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         const bool pre = j < p.n_prefix_tiles;
         const int r0 = (pre ? j : j - p.n_prefix_tiles) * 128;
         mbar_wait(&k_empty[s], ph);
+        SR_TRACE(2, j, 0);
         mbar_arrive_expect_tx(&k_full[s], kAtTile);
         if (pre) tma_load_2d(sK + s * kAtTile, &tmap_pk, &k_full[s], head * 64, r0);
         else     tma_load_3d(sK + s * kAtTile, &tmap_k, &k_full[s], head * 64, r0, b);
         mbar_wait(&v_empty[s], ph);
+        SR_TRACE(2, j, 1);
         mbar_arrive_expect_tx(&v_full[s], kAtTile);
         if (pre) tma_load_2d(sV + s * kAtTile, &tmap_pv, &v_full[s], head * 64, r0);
         else     tma_load_3d(sV + s * kAtTile, &tmap_v, &v_full[s], head * 64, r0, b);
@@ -241,14 +254,20 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         if (j + 1 < n_tiles) {
           const int sn = (j + 1) % kAtStages;
           mbar_wait(&k_full[sn], ((j + 1) / kAtStages) & 1);
+          if (q == 0) SR_TRACE(1, j, 0);
           mbar_wait(&s_free[q], j & 1);          // softmax q holds S_q(j) in registers
+          if (q == 0) SR_TRACE(1, j, 1);
           tc_fence_after();
           issue_s(sn);
+          if (q == 0) SR_TRACE(1, j, 2);
         }
         mbar_wait(&v_full[s], (j / kAtStages) & 1);
+        if (q == 0) SR_TRACE(1, j, 3);
         mbar_wait(&p_full[q], j & 1);            // P_q(j) in TMEM, O_q rescaled
+        if (q == 0) SR_TRACE(1, j, 4);
         tc_fence_after();
         issue_pv(s, p.carry_in != 0 || j > 0);
+        if (q == 0) SR_TRACE(1, j, 5);
       }
     }
   }
@@ -322,6 +341,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
       if (q == 1 && p.lag_ns > 0) __nanosleep(p.lag_ns);
       for (int j = 0; j < n_tiles; ++j) {
         if (!s_ready) mbar_wait(&s_full[q], j & 1);
+        if (warp == 4) SR_TRACE(0, j, 0);
         tc_fence_after();
 #pragma unroll
         for (int c = 0; c < 4; ++c) tmem_ld32(tS + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[c * 32]));
@@ -329,6 +349,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         tc_fence_before();
         if (elect_one()) mbar_arrive(&s_free[q]);   // S_q may be overwritten by Q_q K(j+1)^T (wait::ld is warp-wide)
         const float mx = row_max(valid_cols(j)) * p.scale_log2;            // scale > 0
+        if (warp == 4 && mx == mx) SR_TRACE(0, j, 2);                      // (data-dependent so it cannot be hoisted)
         const bool pv_ready = j > 0 && mbar_test_wait(&pv_done[q], (j - 1) & 1);
         float m_new = m;
         if (mx > m + kLazyRescaleLog2) m_new = mx;                         // also the first tile (m = -inf)
@@ -360,8 +381,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         float r0, r1;
         unpack2(add2(add2(sum0, sum1), add2(sum2, sum3)), r0, r1);
         l = l * alpha + (r0 + r1);
+        if (warp == 4 && l >= 0.f) SR_TRACE(0, j, 3);
 
         if (j > 0 && !pv_ready) mbar_wait(&pv_done[q], (j - 1) & 1);   // P_q and O_q no longer in use by the tensor core
+        if (warp == 4) SR_TRACE(0, j, 4);
         tc_fence_after();
         {
           uint32_t(&h0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&pk[0]);
@@ -386,6 +409,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
         m = m_new;
         tc_fence_before();
         if (elect_one()) mbar_arrive(&p_full[q]);
+        if (warp == 4) SR_TRACE(0, j, 5);
       }
 
       // ---------------------------------------------------------------- epilogue
@@ -457,6 +481,13 @@ static int launch_attn(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const 
 }
 
 }  // namespace sr
+
+extern "C" int sr_debug_trace_read(long long* host_dst, int64_t count) {
+  using namespace sr;
+  SR_REQUIRE(host_dst && count > 0 && count <= 3 * 64 * 8, "sr_debug_trace_read: count out of range");
+  SR_CHECK_CUDA(cudaMemcpyFromSymbol(host_dst, g_attn_trace, static_cast<size_t>(count) * sizeof(long long)));
+  return SR_OK;
+}
 
 extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
   using namespace sr;
@@ -533,6 +564,7 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
   p.total_q_rows = a->batch > 1 ? static_cast<int64_t>(a->batch - 1) * a->q_batch_stride + a->q_len : a->q_len;
   p.scale_log2 = a->scale * 1.4426950408889634f;
   p.lag_ns = 0;
+  p.trace = getenv("SR_ATTN_TRACE") != nullptr;
   if (const char* env = getenv("SR_ATTN_LAG_NS")) p.lag_ns = atoi(env);
 
   dim3 grid(static_cast<unsigned>((a->q_len + 128 * kAtNQ - 1) / (128 * kAtNQ)), static_cast<unsigned>(a->num_heads),
