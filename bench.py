@@ -214,6 +214,18 @@ def summarize_profile(records) -> dict:
     return agg
 
 
+def ncu_traffic(kernel, S, H):
+    """dram read+write bytes per launch of `kernel` from the committed ncu --set full capture (profiles/ncu_traffic.json,
+    written from profiles/r*_ncu_*.txt); only valid for the workload it was captured on, else None."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(kernel)
+    except OSError:
+        return None
+    if not rec or (S, H) != (32, 518):
+        return None
+    return rec["bytes_per_launch_mean"]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -327,7 +339,7 @@ def main():
             "gpu_launches": launches,
             "clocks": clk,
             "roofline": {"bound": "tensor", "kernel": top, "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": achieved / peak_tf, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak_tf, "traffic": ncu_traffic(top, S, H), "peak_source": peak_src,
                          "launches_per_step": d["launches"] // args.steps},
             "kernels": kern,
             "algorithmic_tflop_per_step": fl["total"] / 1e12,

@@ -13,7 +13,7 @@ tail -5 gpurun_out/bench.err; cat gpurun_out/bench.log
 if [ -n "$SKIP_NCU" ]; then exit 0; fi
 CMD="python bench.py --steps 1 --warmup 1 --no-cpu-baseline"
 timeout 600 $CMD > gpurun_out/ncu_plain.log 2>&1 &&
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 4000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 20000 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "list exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:attn_tc -s 24 -c 3 -o gpurun_out/prof_attn_tc -f $CMD > gpurun_out/ncu_full_attn.log 2>&1
 echo "full attn exit $?"

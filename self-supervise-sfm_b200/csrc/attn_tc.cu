@@ -54,6 +54,7 @@ struct AttnParams {
   int64_t total_q_rows;
   float scale_log2;
   int trace;                     // SR_ATTN_TRACE
+  int dbg;                       // SR_ATTN_DBG (timing experiments only): 1 = skip PV MMAs, 2 = skip QK MMAs
   int lag_ns;                    // start-up lag of the second softmax warpgroup (de-phases the two MUFU streams)
 };
 
@@ -143,7 +144,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
   __shared__ __align__(8) uint64_t s_full[kAtNQ], s_free[kAtNQ], p_full[kAtNQ], pv_done[kAtNQ];
   __shared__ uint32_t tmem_base_slot;
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle: the compiler then knows it is warp-uniform, keeps the producer / MMA-issuer address
+  // arithmetic in uniform registers and emits UTMALDG / UTCHMMA directly (a `lane == 0` branch made every issue a
+  // 12-instruction R2UR waterfall loop: ~100 clk per MMA, which was the bottleneck of the whole kernel)
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
@@ -196,53 +200,67 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
   if (warp < 4) {
   asm volatile("setmaxnreg.dec.sync.aligned.u32 72;");
   if (warp == 0) {
-    // ------------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    // ------------------------------------------------------------------ TMA producer (whole warp; one elected lane issues)
+    if (elect_one()) {
       mbar_arrive_expect_tx(&q_full, nq_valid * kAtTile);
       for (int q = 0; q < nq_valid; ++q) tma_load_3d(sQ + q * kAtTile, &tmap_q, &q_full, head * 64, q0 + q * 128, b);
-      for (int j = 0; j < n_tiles; ++j) {
-        const int s = j % kAtStages;
-        const uint32_t ph = ((j / kAtStages) & 1) ^ 1;
-        const bool pre = j < p.n_prefix_tiles;
-        const int r0 = (pre ? j : j - p.n_prefix_tiles) * 128;
-        mbar_wait(&k_empty[s], ph);
-        SR_TRACE(2, j, 0);
+    }
+    __syncwarp();
+    for (int j = 0; j < n_tiles; ++j) {
+      const int s = j % kAtStages;
+      const uint32_t ph = ((j / kAtStages) & 1) ^ 1;
+      const bool pre = j < p.n_prefix_tiles;
+      const int r0 = (pre ? j : j - p.n_prefix_tiles) * 128;
+      mbar_wait(&k_empty[s], ph);
+      SR_TRACE(2, j, 0);
+      if (elect_one()) {
         mbar_arrive_expect_tx(&k_full[s], kAtTile);
         if (pre) tma_load_2d(sK + s * kAtTile, &tmap_pk, &k_full[s], head * 64, r0);
         else     tma_load_3d(sK + s * kAtTile, &tmap_k, &k_full[s], head * 64, r0, b);
-        mbar_wait(&v_empty[s], ph);
-        SR_TRACE(2, j, 1);
+      }
+      __syncwarp();
+      mbar_wait(&v_empty[s], ph);
+      SR_TRACE(2, j, 1);
+      if (elect_one()) {
         mbar_arrive_expect_tx(&v_full[s], kAtTile);
         if (pre) tma_load_2d(sV + s * kAtTile, &tmap_pv, &v_full[s], head * 64, r0);
         else     tma_load_3d(sV + s * kAtTile, &tmap_v, &v_full[s], head * 64, r0, b);
       }
+      __syncwarp();
     }
   } else if (warp == 1 || warp == 3) {
     // ------------------------------------------------------------------ MMA issuer of query tile q
     const int q = warp >> 1;
-    if (lane == 0 && q < nq_valid) {
+    if (q < nq_valid) {   // whole warp runs the loop (uniform control flow); one elected lane issues
       constexpr uint32_t idesc_s = umma_idesc_bf16(128, 128, 0, 0);   // Q (K-major) x K (K-major)
       constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);    // P (TMEM)    x V (MN-major: d contiguous)
       const uint32_t tS = tmem_S0 + q * 128, tO = tmem_O0 + q * 64, tP = tmem_P0 + q * 64;
       const uint64_t dq = umma_desc_sw128(smem_u32(sQ + q * kAtTile), 16, 1024);
       auto issue_s = [&](int stage) {
         const uint64_t db = umma_desc_sw128(smem_u32(sK + stage * kAtTile), 16, 1024);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) umma_ss(tS, dq + 2 * k, db + 2 * k, idesc_s, k != 0 ? 1u : 0u);
-        umma_commit(&s_full[q]);
-        umma_commit(&k_empty[stage]);
+          for (int k = 0; k < 4; ++k)
+            if (!(p.dbg & 2)) umma_ss(tS, dq + 2 * k, db + 2 * k, idesc_s, k != 0 ? 1u : 0u);
+          umma_commit(&s_full[q]);
+          umma_commit(&k_empty[stage]);
+        }
+        __syncwarp();
       };
       auto issue_pv = [&](int stage, bool accumulate) {
         const uint32_t vbase = smem_u32(sV + stage * kAtTile);
+        if (elect_one()) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          // A: P columns [8k, 8k+8) hold kv [16k, 16k+16) as packed bf16 pairs
-          // B: V rows [16k, 16k+16) = two 8-row swizzle atoms (SBO 1024 B); one 64-wide MN block (LBO unused)
-          const uint64_t db = umma_desc_sw128(vbase + k * 2048, 0, 1024);
-          umma_ts(tO, tP + k * 8, db, idesc_o, (accumulate || k != 0) ? 1u : 0u);
+          for (int k = 0; k < 8; ++k) {
+            // A: P columns [8k, 8k+8) hold kv [16k, 16k+16) as packed bf16 pairs
+            // B: V rows [16k, 16k+16) = two 8-row swizzle atoms (SBO 1024 B); one 64-wide MN block (LBO unused)
+            const uint64_t db = umma_desc_sw128(vbase + k * 2048, 0, 1024);
+            if (!(p.dbg & 1)) umma_ts(tO, tP + k * 8, db, idesc_o, (accumulate || k != 0) ? 1u : 0u);
+          }
+          umma_commit(&pv_done[q]);
+          umma_commit(&v_empty[stage]);
         }
-        umma_commit(&pv_done[q]);
-        umma_commit(&v_empty[stage]);
+        __syncwarp();
       };
 
       mbar_wait(&q_full, 0);
@@ -363,7 +381,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant
 #pragma unroll
           for (int t = 0; t < 4; ++t) {
             const uint64_t x2 = fma2(pack2(__uint_as_float(sraw[i + 2 * t]), __uint_as_float(sraw[i + 2 * t + 1])), scale2, negm2);
-            if ((((i >> 1) + t) & 7) < kPoly) {
+            if (kPoly == 8) {   // timing experiment: no exponential at all
+              unpack2(x2, e[2 * t], e[2 * t + 1]);
+            } else if ((((i >> 1) + t) & 7) < kPoly) {
               ex2_poly2(x2, e[2 * t], e[2 * t + 1]);
             } else {
               float x0, x1;
@@ -564,6 +584,8 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
   p.total_q_rows = a->batch > 1 ? static_cast<int64_t>(a->batch - 1) * a->q_batch_stride + a->q_len : a->q_len;
   p.scale_log2 = a->scale * 1.4426950408889634f;
   p.lag_ns = 0;
+  p.dbg = 0;
+  if (const char* env = getenv("SR_ATTN_DBG")) p.dbg = atoi(env);
   p.trace = getenv("SR_ATTN_TRACE") != nullptr;
   if (const char* env = getenv("SR_ATTN_LAG_NS")) p.lag_ns = atoi(env);
 
@@ -578,6 +600,7 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
     case 2: return launch_attn<2>(grid, st, tq, tk, tv, tpk, tpv, p);
     case 3: return launch_attn<3>(grid, st, tq, tk, tv, tpk, tpv, p);
     case 4: return launch_attn<4>(grid, st, tq, tk, tv, tpk, tpv, p);
+    case 8: return launch_attn<8>(grid, st, tq, tk, tv, tpk, tpv, p);
   }
   return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16: SR_ATTN_POLY must be 0, 2, 3 or 4 (got %d)", poly);
 }
