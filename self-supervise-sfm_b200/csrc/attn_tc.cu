@@ -113,11 +113,6 @@ __device__ __forceinline__ void ex2_poly2(uint64_t x2, float& e0, float& e1) {
   e0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
   e1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
 }
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-  return pred != 0;
-}
 __device__ __forceinline__ void named_bar_arrive(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }

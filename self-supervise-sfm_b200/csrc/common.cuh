@@ -68,6 +68,16 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #endif
 }
 
+// One lane of a fully converged warp.  TMA / tcgen05 issue code runs warp-wide (uniform control flow, warp index taken
+// through __shfl_sync so the compiler knows it is uniform) with only the issuing instruction under this predicate: the
+// operands then live in uniform registers.  Issuing from an `if (lane == 0)` branch instead makes every UTCHMMA /
+// UTMALDG a R2UR waterfall loop (~100 clk per instruction).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ----------------------------------------------------------------------------- proxies / fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
