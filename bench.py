@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — SAIL-Recon hot path on B200: aggregator + camera head, frames/s (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload agg32|ring]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload agg32|imc|ring]
 
 Workload "agg32" (default, BASELINE.json configs[1]): 32 frames of 518x518 = 16 anchors + 16 query frames
 (the train/demo_imc_forward.py duplication), full-size model (DINOv2 ViT-L patch embed + 3 x 24 blocks + camera head),
@@ -12,6 +12,8 @@ One "step" = one aggregator + camera-head forward over one synthetic 32-frame sc
          read of the pose encodings inside the timed region
 N > 1 (torchrun): one process per GPU, one independent scene per rank (the reference's own DDP decomposition,
 train/train_imc.py:494-504) — no data-path collective, weak scaling.
+Workload "imc" (BASELINE.json configs[2]): --anchors 100 --queries 200 in ONE pass (the reference's dense mask would
+need 170 GB here; the structured prefix + own-frame attention does not build it).
 Workload "ring" (BASELINE.json configs[3]): the sequence-sharded global-attention stack, see parallel.py.
 
 --impl reference: the reference's CPU path restated by the oracle (oracle/sailrecon_oracle.py; the Python reference
@@ -232,7 +234,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="agg32", choices=["agg32", "ring"])
+    ap.add_argument("--workload", default="agg32", choices=["agg32", "imc", "ring"])
+    ap.add_argument("--anchors", type=int, default=100, help="workload imc: anchor frames (build the scene tokens)")
+    ap.add_argument("--queries", type=int, default=200, help="workload imc: query frames localised against the anchors")
     ap.add_argument("--frames", type=int, default=32)
     ap.add_argument("--size", type=int, default=518)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -259,7 +263,12 @@ def main():
     from sailrecon_b200 import ops
 
     Na = Nq = args.frames // 2
+    if args.workload == "imc":
+        # BASELINE.json configs[2]: demo_imc_forward one-pass semantics, anchors build the scene tokens and every query
+        # frame is localised against them (the reference cannot run this in one pass: its dense mask would be 170 GB)
+        Na, Nq = args.anchors, args.queries
     S, H, W = Na + Nq, args.size, args.size
+    metric = METRIC if args.workload == "agg32" else f"aggregator+camera-head frames/s at N={S} ({Na} anchors + {Nq} queries, {H}px)"
     agg, head = build_models(dev)
     host_images = torch.rand(1, S, 3, H, W, generator=torch.Generator().manual_seed(1 + rank)).pin_memory()
     images = host_images.to(dev)
@@ -327,10 +336,10 @@ def main():
         fl = algorithmic_flops(Na, Nq, H, W)
         step_s = ms * 1e-3 / args.steps
         line = {
-            "metric": METRIC, "value": world * S / step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "metric": metric, "value": world * S / step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"agg{S}: {Na} anchors + {Nq} queries, {H}x{W}, fix_rank 300, DINOv2 ViT-L patch embed + "
+            "config": {"workload": f"{args.workload if args.workload != 'agg32' else 'agg'}{S}: {Na} anchors + {Nq} queries, {H}x{W}, fix_rank 300, DINOv2 ViT-L patch embed + "
                                    "24x(frame, global, reloc) blocks + camera head, random-init weights, one scene per GPU",
                        "l2": "activations per layer (>= 180 MB residual + 270 MB qkv + 360 MB MLP hidden) exceed the 126 MB L2; "
                              "no flush needed"},
@@ -346,7 +355,7 @@ def main():
             "tensor_frac_whole_step": fl["total"] / step_s / 1e12 / peak_tf,
             "outputs_finite": finite,
         }
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and args.workload == "agg32":
             threads = os.cpu_count() or 1
             cs = cpu_sample(Na, Nq, H, W, threads)
             line["cpu_baseline"] = {"value": S / cs["full_forward_s"], "unit": UNIT, "cores": threads, "kind": "port",

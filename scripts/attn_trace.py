@@ -17,8 +17,9 @@ L = 16 * 1374
 g = torch.Generator(device=dev).manual_seed(0)
 qkv = torch.randn(L, 3 * Cc, device=dev, generator=g).to(torch.bfloat16)
 out = torch.empty(L, Cc, device=dev, dtype=torch.bfloat16)
+QL = int(os.environ.get("TRACE_Q_LEN", L))   # 128 -> one query tile per CTA: a lone softmax warp per sub-partition
 for _ in range(3):
-    ops.attention(qkv[:, :Cc], qkv[:, Cc:2 * Cc], qkv[:, 2 * Cc:], out, H, D, 1, L, L)
+    ops.attention(qkv[:, :Cc], qkv[:, Cc:2 * Cc], qkv[:, 2 * Cc:], out, H, D, 1, QL, L)
 torch.cuda.synchronize()
 buf = (C.c_longlong * (3 * 64 * 8))()
 _lib.check(_lib.load().sr_debug_trace_read(buf, 3 * 64 * 8))

@@ -199,3 +199,46 @@ def test_full_width_reduced_depth_518():
     assert rel_l2(cam.cpu(), ref_cam) < 8e-3
     for a, b in zip(poses, ref_poses):                      # O(1) LayerScale weights: pose values are O(3), compare relatively
         assert rel_l2(a.cpu(), b) < 1e-2
+
+
+def test_imc_style_scene_more_queries_than_anchors():
+    """BASELINE.json configs[2] in miniature (train/demo_imc_forward.py:76-101): 3 anchors build the scene tokens, 6 query
+    frames are localised against them in ONE pass; full width (C = 1024, 16 heads), 224 px (P = 261), fix_rank 100 so
+    that the scene prefix (3 x 105 rows) ends inside a 128-row K/V tile, 2 ViT blocks + 2 aggregator layers, fp32 check
+    mode (1e-4) and autocast(bf16) (2e-2) against the oracle; the scene-token draw order is part of the comparison."""
+    from sailrecon_b200.heads import CameraHead
+    from sailrecon_b200.models import Aggregator
+    torch.manual_seed(0)
+    agg = Aggregator(img_size=224, depth=2, intermediate_layer_idx=[0, 1]).eval()
+    agg.patch_embed.blocks = agg.patch_embed.blocks[:2]
+    head = CameraHead(dim_in=2048, trunk_depth=1).eval()
+    shapes = {"agg." + k: list(v.shape) for k, v in agg.state_dict().items()}
+    shapes.update({"head." + k: list(v.shape) for k, v in head.state_dict().items()})
+    params = make_params(shapes, 33)
+    agg_p = {k[4:]: v for k, v in params.items() if k.startswith("agg.")}
+    head_p = {k[5:]: v for k, v in params.items() if k.startswith("head.")}
+    agg.load_state_dict(agg_p)
+    head.load_state_dict(head_p)
+    Na, Nq = 3, 6
+    images = make_images(Na + Nq, 224, 224, 133)
+    anchors, queries = list(range(Na)), list(range(Na, Na + Nq))
+    agg, head = agg.to(DEV), head.to(DEV)
+    for bf16, tol in ((False, 1e-4), (True, 2e-2)):
+        agg.generator.manual_seed(1234)
+        with torch.no_grad():
+            if bf16:
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    out, psi, cam = agg(images.to(DEV), anchors, queries, fix_rank=100)
+            else:
+                out, psi, cam = agg(images.to(DEV), anchors, queries, fix_rank=100)
+            poses = head(out, cam)
+        ref, _, ref_cam = O.aggregator_forward(images, agg_p, anchors, queries, 100, torch.Generator().manual_seed(1234),
+                                               depth=2, vit_depth=2, intermediate_layer_idx=(0, 1), bf16=bf16)
+        ref_poses = O.camera_head_forward(ref[-1][:, :, 0], ref_cam, head_p, 4, 16, 1)
+        assert psi == 5 and tuple(out[-1].shape) == (1, Nq, 261, 2048) and tuple(cam.shape) == (1, Na, 2048)
+        for k in out:
+            assert rel_l2(out[k].cpu(), ref[k]) < tol, (bf16, k)
+        assert rel_l2(cam.cpu(), ref_cam) < tol
+        assert len(poses) == 4 and tuple(poses[-1].shape) == (1, Nq, 9)
+        for a, b in zip(poses, ref_poses):
+            assert rel_l2(a.cpu(), b) < 1e-2
