@@ -29,6 +29,7 @@ SOURCES = [
     "attn_f32.cu",
     "gemm_tc.cu",
     "attn_tc.cu",
+    "attn_tc4.cu",
 ]
 
 NVCC_FLAGS = [
