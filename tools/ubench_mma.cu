@@ -24,24 +24,27 @@ __global__ void k_mma(long long* out, int iters, int per) {
   fence_proxy_async_smem();
   tc_fence_before(); __syncthreads(); tc_fence_after();
   const uint32_t tm = slot;
-  if (threadIdx.x == 0) {
+  if (__shfl_sync(0xffffffffu, threadIdx.x >> 5, 0) == 0) {   // whole warp, uniform control flow; one elected lane issues
     const uint32_t a_addr = smem_u32(smem), b_addr = smem_u32(smem + 32768);
     constexpr uint32_t idesc = umma_idesc_bf16(128, N, 0, (MODE == 1 || MODE == 2) ? 1 : 0);
     long long t0 = clock64();
     for (int it = 0; it < iters; ++it) {
-      for (int k = 0; k < per; ++k) {
-        const uint64_t da = umma_desc_sw128(a_addr + (k & 3) * 32, 16, 1024);
-        const uint64_t db = (MODE == 1 || MODE == 2) ? umma_desc_sw128(b_addr + (k & 7) * 2048, 0, 1024)
-                                                     : umma_desc_sw128(b_addr + (k & 3) * 32, 16, 1024);
-        const uint32_t td = tm + (k % NACC) * 64;     // NACC independent accumulators (64 columns apart)
-        if (MODE <= 1) umma_ss(td, da, db, idesc, 1u);
-        else           umma_ts(td, tm + 256 + (k & 7) * 8, db, idesc, 1u);
+      if (elect_one()) {
+        for (int k = 0; k < per; ++k) {
+          const uint64_t da = umma_desc_sw128(a_addr + (k & 3) * 32, 16, 1024);
+          const uint64_t db = (MODE == 1 || MODE == 2) ? umma_desc_sw128(b_addr + (k & 7) * 2048, 0, 1024)
+                                                       : umma_desc_sw128(b_addr + (k & 3) * 32, 16, 1024);
+          const uint32_t td = tm + (k % NACC) * 64;     // NACC independent accumulators (64 columns apart)
+          if (MODE <= 1) umma_ss(td, da, db, idesc, 1u);
+          else           umma_ts(td, tm + 256 + (k & 7) * 8, db, idesc, 1u);
+        }
+        umma_commit(&bar);
       }
-      umma_commit(&bar);
+      __syncwarp();
       mbar_wait(&bar, it & 1);
     }
     long long t1 = clock64();
-    out[0] = t1 - t0;
+    if (threadIdx.x == 0) out[0] = t1 - t0;
   }
   tc_fence_before(); __syncthreads();
   if (warp == 0) { tc_fence_after(); tmem_dealloc<512>(tm); }
