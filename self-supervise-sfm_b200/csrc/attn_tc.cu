@@ -30,6 +30,7 @@
 namespace sr {
 extern int g_launch_count;
 int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st);   // attn_tc4.cu
+int attn_tc4_trace_read(long long* host_dst, int64_t count);
 constexpr int kAtKernelDefault = 4;   // query tiles per CTA: 2 (this file) or 4 (attn_tc4.cu); SR_ATTN_KERNEL overrides
 
 constexpr int kAtNQ = 2;
@@ -64,7 +65,7 @@ struct AttnParams {
 // Profiling aid: SR_ATTN_TRACE=1 makes CTA (0,0,0) record clock64() at the pipeline hand-offs of its first 64 K/V tiles
 // (read back with sr_debug_trace_read, printed by scripts/attn_trace.py).  Layout: g_attn_trace[role][tile][event],
 // role 0 = softmax warp 4, 1 = MMA issuer of query tile 0, 2 = TMA producer.
-__device__ long long g_attn_trace[3 * 64 * 8];
+static __device__ long long g_attn_trace[3 * 64 * 8];
 #define SR_TRACE(role, j, ev)                                                           \
   do {                                                                                  \
     if (trace_on && (j) < 64) g_attn_trace[((role) * 64 + (j)) * 8 + (ev)] = clock64(); \
@@ -443,6 +444,11 @@ static int launch_attn(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const 
 extern "C" int sr_debug_trace_read(long long* host_dst, int64_t count) {
   using namespace sr;
   SR_REQUIRE(host_dst && count > 0 && count <= 3 * 64 * 8, "sr_debug_trace_read: count out of range");
+  {
+    int variant = kAtKernelDefault;
+    if (const char* env = getenv("SR_ATTN_KERNEL")) variant = atoi(env);
+    if (variant == 4) return attn_tc4_trace_read(host_dst, count);
+  }
   SR_CHECK_CUDA(cudaMemcpyFromSymbol(host_dst, g_attn_trace, static_cast<size_t>(count) * sizeof(long long)));
   return SR_OK;
 }

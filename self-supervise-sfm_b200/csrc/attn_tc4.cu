@@ -6,14 +6,14 @@
 // P store): with two softmax warps per sub-partition MUFU is busy only 79 % of the time.  Here every
 // sub-partition runs FOUR independent softmax streams (one per query tile), each on half-width tiles:
 //   TMEM (512 columns)  S0..S3 (64 fp32 columns each; P_q, 64 bf16 = 32 columns, is written back over S_q) | O0..O3 (64 each)
-//   smem                Q 4 x 16 KB | K ring 6 x 8 KB | V ring 6 x 8 KB                                   (161 KB)
+//   smem                Q 4 x 16 KB | ring of 6 x (V(j) 8 KB + K(j+1) 8 KB) | K(0) 8 KB                  (169 KB)
 //   warp 0              TMA producer (Q tiles once, then 64 x 64 K and V tiles)
-//   warp 1              the one MMA issuer, round-robin over the query tiles:
+//   warps 1, 3          MMA issuers (query tiles 0-1 and 2-3), each round-robin over its tiles:
 //                           wait p_full[q](j)  ->  O_q += P_q(j) V(j)      TS, M=128 N=64 K=16 x4
 //                                                  S_q  = Q_q K(j+1)^T     SS, M=128 N=64 K=16 x4  (after the PV: it overwrites P_q)
 //                       the in-order tensor pipe makes "S_q(j+1) complete" imply "PV_q(j) complete", so the softmax warps
 //                       need no pv_done / s_free barriers at all
-//   warp 2              TMEM allocator;  warp 3 idle
+//   warp 2              TMEM allocator
 //   warps 4-19          softmax: warp 4 + 4q + r owns rows [32r, 32r + 32) of query tile q, one thread per row
 // 640 threads; registers re-distributed with setmaxnreg (control 56, softmax 104).
 #include <cstdlib>
@@ -24,13 +24,18 @@
 
 namespace sr {
 extern int g_launch_count;
+static __device__ long long g_attn_trace[3 * 64 * 8];   // SR_ATTN_TRACE: [role][tile][event] clock64() of CTA (0,0,0)
+#define SR_TRACE4(role, j, ev)                                                          \
+  do {                                                                                  \
+    if (trace_on && (j) < 64) g_attn_trace[((role) * 64 + (j)) * 8 + (ev)] = clock64(); \
+  } while (0)
 
 constexpr int k4NQ = 4;
 constexpr int k4Stages = 6;
 constexpr int k4QTile = 128 * 64 * 2;                 // 16 KB: 128 x 64 bf16
 constexpr int k4KvTile = 64 * 64 * 2;                 //  8 KB:  64 x 64 bf16
 constexpr int k4Threads = 128 + k4NQ * 128;
-constexpr int k4Smem = k4NQ * k4QTile + k4Stages * 2 * k4KvTile + 1024;
+constexpr int k4Smem = k4NQ * k4QTile + (k4Stages * 2 + 1) * k4KvTile + 1024;
 constexpr float k4LazyRescaleLog2 = 8.0f;
 
 struct Attn4Params {
@@ -47,6 +52,7 @@ struct Attn4Params {
   int n_prefix_tiles, n_own_tiles;   // 64-row tiles
   int64_t total_q_rows;
   float scale_log2;
+  int trace;
 };
 
 template <int kPoly>
@@ -56,7 +62,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
                 const __grid_constant__ CUtensorMap tmap_pv, const Attn4Params p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t q_full;
-  __shared__ __align__(8) uint64_t k_full[k4Stages], k_empty[k4Stages], v_full[k4Stages], v_empty[k4Stages];
+  __shared__ __align__(8) uint64_t kv_full[k4Stages], kv_empty[k4Stages];
   __shared__ __align__(8) uint64_t s_full[k4NQ], p_full[k4NQ], o_done[k4NQ];
   __shared__ uint32_t tmem_base_slot;
 
@@ -66,12 +72,14 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + k4NQ * k4QTile;
   uint8_t* sV = sK + k4Stages * k4KvTile;
+  uint8_t* sK0 = sV + k4Stages * k4KvTile;                           // K(0)
 
   const int head = blockIdx.y;
   const int b = blockIdx.z;
   const int q0 = blockIdx.x * (128 * k4NQ);                          // first query row (within the segment) of this CTA
   const int nq_valid = min(k4NQ, (p.q_len - q0 + 127) / 128);        // query tiles that hold at least one row
   const int n_tiles = p.n_prefix_tiles + p.n_own_tiles;
+  const bool trace_on = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
@@ -85,10 +93,8 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   if (warp == 1 && lane == 0) {
     mbar_init(&q_full, 1);
     for (int s = 0; s < k4Stages; ++s) {
-      mbar_init(&k_full[s], 1);
-      mbar_init(&k_empty[s], 1);             // one tcgen05.commit after the last query tile's MMA on the stage
-      mbar_init(&v_full[s], 1);
-      mbar_init(&v_empty[s], 1);
+      mbar_init(&kv_full[s], 1);
+      mbar_init(&kv_empty[s], nq_valid > 2 ? 2 : 1);   // one tcgen05.commit per active MMA issuer
     }
     for (int q = 0; q < k4NQ; ++q) {
       mbar_init(&s_full[q], 1);
@@ -109,78 +115,88 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (whole warp; one elected lane issues)
+    // Step j of the MMA issuers needs V(j) and K(j+1): both travel on ONE barrier into stage j % k4Stages (one wait and
+    // one release per step instead of two each); K(0) has its own buffer and barrier.
+    auto load_tile = [&](uint8_t* dst, uint64_t* bar, int t, bool is_k) {
+      const bool pre = t < p.n_prefix_tiles;
+      const int r0 = (pre ? t : t - p.n_prefix_tiles) * 64;
+      if (pre) tma_load_2d(dst, is_k ? &tmap_pk : &tmap_pv, bar, head * 64, r0);
+      else     tma_load_3d(dst, is_k ? &tmap_k : &tmap_v, bar, head * 64, r0, b);
+    };
     if (elect_one()) {
-      mbar_arrive_expect_tx(&q_full, nq_valid * k4QTile);
+      mbar_arrive_expect_tx(&q_full, nq_valid * k4QTile + k4KvTile);
       for (int q = 0; q < nq_valid; ++q) tma_load_3d(sQ + q * k4QTile, &tmap_q, &q_full, head * 64, q0 + q * 128, b);
+      load_tile(sK0, &q_full, 0, true);
     }
     __syncwarp();
     for (int j = 0; j < n_tiles; ++j) {
       const int s = j % k4Stages;
-      const uint32_t ph = ((j / k4Stages) & 1) ^ 1;
-      const bool pre = j < p.n_prefix_tiles;
-      const int r0 = (pre ? j : j - p.n_prefix_tiles) * 64;
-      mbar_wait(&k_empty[s], ph);
+      mbar_wait(&kv_empty[s], ((j / k4Stages) & 1) ^ 1);
       if (elect_one()) {
-        mbar_arrive_expect_tx(&k_full[s], k4KvTile);
-        if (pre) tma_load_2d(sK + s * k4KvTile, &tmap_pk, &k_full[s], head * 64, r0);
-        else     tma_load_3d(sK + s * k4KvTile, &tmap_k, &k_full[s], head * 64, r0, b);
-      }
-      __syncwarp();
-      mbar_wait(&v_empty[s], ph);
-      if (elect_one()) {
-        mbar_arrive_expect_tx(&v_full[s], k4KvTile);
-        if (pre) tma_load_2d(sV + s * k4KvTile, &tmap_pv, &v_full[s], head * 64, r0);
-        else     tma_load_3d(sV + s * k4KvTile, &tmap_v, &v_full[s], head * 64, r0, b);
+        const bool has_k = j + 1 < n_tiles;
+        mbar_arrive_expect_tx(&kv_full[s], has_k ? 2 * k4KvTile : k4KvTile);
+        load_tile(sV + s * k4KvTile, &kv_full[s], j, false);
+        if (has_k) load_tile(sK + s * k4KvTile, &kv_full[s], j + 1, true);
       }
       __syncwarp();
     }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer (whole warp; one elected lane issues)
-    constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);   // Q (K-major) x K (K-major)
-    constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);   // P (TMEM)    x V (MN-major: d contiguous)
-    auto issue_s = [&](int q, int stage, bool last_q) {
-      const uint64_t dq = umma_desc_sw128(smem_u32(sQ + q * k4QTile), 16, 1024);
-      const uint64_t db = umma_desc_sw128(smem_u32(sK + stage * k4KvTile), 16, 1024);
-      const uint32_t tS = tmem_S0 + q * 64;
-      if (elect_one()) {
+  } else if (warp == 1 || warp == 3) {
+    // ------------------------------------------------------------------ MMA issuers: warp 1 serves query tiles 0-1,
+    // warp 3 tiles 2-3 (whole warp runs the loop; one elected lane issues).  One issuer for all four tiles was the
+    // bottleneck: ~560 clk per tile served (barrier wait + 8 MMAs + commits on a sub-partition it shares with four busy
+    // softmax warps) = 2780 clk per step against 2048 clk of MUFU work.
+    const int qa = warp == 1 ? 0 : 2;                        // first query tile of this issuer
+    const int nq_mine = min(2, nq_valid - qa);               // <= 0: nothing to do
+    if (nq_mine > 0) {
+      constexpr uint32_t idesc_s = umma_idesc_bf16(128, 64, 0, 0);   // Q (K-major) x K (K-major)
+      constexpr uint32_t idesc_o = umma_idesc_bf16(128, 64, 0, 1);   // P (TMEM)    x V (MN-major: d contiguous)
+      auto issue_s = [&](int q, uint32_t k_addr) {
+        const uint64_t dq = umma_desc_sw128(smem_u32(sQ + q * k4QTile), 16, 1024);
+        const uint64_t db = umma_desc_sw128(k_addr, 16, 1024);
+        const uint32_t tS = tmem_S0 + q * 64;
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_ss(tS, dq + 2 * k, db + 2 * k, idesc_s, k != 0 ? 1u : 0u);
         umma_commit(&s_full[q]);
-        if (last_q) umma_commit(&k_empty[stage]);
-      }
-      __syncwarp();
-    };
-    auto issue_pv = [&](int q, int stage, bool accumulate, bool last_q, bool last_tile) {
-      const uint32_t vbase = smem_u32(sV + stage * k4KvTile);
-      const uint32_t tO = tmem_O0 + q * 64, tP = tmem_S0 + q * 64;
-      if (elect_one()) {
+      };
+      auto issue_pv = [&](int q, uint32_t v_addr, bool accumulate) {
+        const uint32_t tO = tmem_O0 + q * 64, tP = tmem_S0 + q * 64;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           // A: P columns [8k, 8k+8) hold kv [16k, 16k+16) as packed bf16 pairs
           // B: V rows [16k, 16k+16) = two 8-row swizzle atoms (SBO 1024 B); one 64-wide MN block (LBO unused)
-          const uint64_t db = umma_desc_sw128(vbase + k * 2048, 0, 1024);
+          const uint64_t db = umma_desc_sw128(v_addr + k * 2048, 0, 1024);
           umma_ts(tO, tP + k * 8, db, idesc_o, (accumulate || k != 0) ? 1u : 0u);
         }
-        if (last_tile) umma_commit(&o_done[q]);
-        if (last_q) umma_commit(&v_empty[stage]);
+      };
+
+      mbar_wait(&q_full, 0);
+      tc_fence_after();
+      if (elect_one()) {
+        for (int qi = 0; qi < nq_mine; ++qi) issue_s(qa + qi, smem_u32(sK0));
       }
       __syncwarp();
-    };
-
-    mbar_wait(&q_full, 0);
-    mbar_wait(&k_full[0], 0);
-    tc_fence_after();
-    for (int q = 0; q < nq_valid; ++q) issue_s(q, 0, q == nq_valid - 1);
-    for (int j = 0; j < n_tiles; ++j) {
-      const int s = j % k4Stages;
-      const int sn = (j + 1) % k4Stages;
-      mbar_wait(&v_full[s], (j / k4Stages) & 1);
-      if (j + 1 < n_tiles) mbar_wait(&k_full[sn], ((j + 1) / k4Stages) & 1);
-      for (int q = 0; q < nq_valid; ++q) {
-        mbar_wait(&p_full[q], j & 1);              // P_q(j) in TMEM, O_q rescaled
-        tc_fence_after();
-        issue_pv(q, s, p.carry_in != 0 || j > 0, q == nq_valid - 1, j == n_tiles - 1);
-        if (j + 1 < n_tiles) issue_s(q, sn, q == nq_valid - 1);
+      for (int j = 0; j < n_tiles; ++j) {
+        const int s = j % k4Stages;
+        const bool has_next = j + 1 < n_tiles;
+        mbar_wait(&kv_full[s], (j / k4Stages) & 1);
+        if (qa == 0) SR_TRACE4(1, j, 0);
+#pragma unroll
+        for (int qi = 0; qi < 2; ++qi) {
+          if (qi < nq_mine) {
+            const int q = qa + qi;
+            mbar_wait(&p_full[q], j & 1);            // P_q(j) in TMEM, O_q rescaled
+            if (qa == 0) SR_TRACE4(1, j, 1 + qi);    // events 1..2: p_full[q] seen
+            tc_fence_after();
+            if (elect_one()) {
+              issue_pv(q, smem_u32(sV + s * k4KvTile), p.carry_in != 0 || j > 0);
+              if (has_next) issue_s(q, smem_u32(sK + s * k4KvTile));
+              else umma_commit(&o_done[q]);
+              if (qi == nq_mine - 1) umma_commit(&kv_empty[s]);
+            }
+            __syncwarp();
+          }
+        }
+        if (qa == 0) SR_TRACE4(1, j, 5);
       }
     }
   }
@@ -245,13 +261,16 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         return fmaxf(max3(mx0, mx1, mx2), mx3);
       };
 
+      const int tr_role = warp == 4 ? 0 : (warp == 16 ? 2 : -1);   // softmax of query tile 0 / 3
       for (int j = 0; j < n_tiles; ++j) {
         mbar_wait(&s_full[q], j & 1);            // S_q(j) complete; implies PV_q(j-1) complete (in-order tensor pipe)
+        if (tr_role >= 0) SR_TRACE4(tr_role, j, 0);
         tc_fence_after();
         tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&sraw[0]));
         tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[32]));
         tmem_ld_wait();
         const float mx = row_max(valid_cols(j)) * p.scale_log2;            // scale > 0
+        if (tr_role >= 0 && mx == mx) SR_TRACE4(tr_role, j, 2);
         float m_new = m;
         if (mx > m + k4LazyRescaleLog2) m_new = mx;                        // also the first tile (m = -inf)
         const float alpha = ex2_approx(m - m_new);                         // 1 when unchanged, 0 on the first tile
@@ -284,6 +303,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         float r0, r1;
         unpack2(add2(add2(sum0, sum1), add2(sum2, sum3)), r0, r1);
         l = l * alpha + (r0 + r1);
+        if (tr_role >= 0 && l >= 0.f) SR_TRACE4(tr_role, j, 3);
 
         tmem_st32(tS, pk);                       // P_q(j) over the first 32 columns of S_q (this warp's lanes are in registers)
         const bool have_acc = (j > 0) || p.carry_in;
@@ -302,6 +322,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         m = m_new;
         tc_fence_before();
         if (elect_one()) mbar_arrive(&p_full[q]);
+        if (tr_role >= 0) SR_TRACE4(tr_role, j, 5);
       }
 
       // ---------------------------------------------------------------- epilogue
@@ -362,6 +383,11 @@ static int launch4(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUte
   return SR_OK;
 }
 
+int attn_tc4_trace_read(long long* host_dst, int64_t count) {
+  SR_CHECK_CUDA(cudaMemcpyFromSymbol(host_dst, g_attn_trace, static_cast<size_t>(count) * sizeof(long long)));
+  return SR_OK;
+}
+
 // Called by sr_attn_fwd_bf16 (attn_tc.cu) after argument validation.
 int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
   const int64_t hd = static_cast<int64_t>(a->num_heads) * 64;
@@ -409,6 +435,7 @@ int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
   p.n_own_tiles = (p.kv_len + 63) / 64;
   p.total_q_rows = a->batch > 1 ? static_cast<int64_t>(a->batch - 1) * a->q_batch_stride + a->q_len : a->q_len;
   p.scale_log2 = a->scale * 1.4426950408889634f;
+  p.trace = getenv("SR_ATTN_TRACE") != nullptr;
   dim3 grid(static_cast<unsigned>((a->q_len + 128 * k4NQ - 1) / (128 * k4NQ)), static_cast<unsigned>(a->num_heads),
             static_cast<unsigned>(a->batch));
   switch (poly) {
