@@ -488,7 +488,7 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
     int variant = kAtKernelDefault;
     if (const char* env = getenv("SR_ATTN_KERNEL")) variant = atoi(env);
     if (variant == 4) {
-      int poly4 = 0;
+      int poly4 = 2;   // polynomial exp2 on the FMA pipe for 2 of every 8 pairs: measured best (0: 851, 1: 905, 2: 921, 3: 892, 4: 843 TF/s)
       if (const char* env = getenv("SR_ATTN_POLY")) poly4 = atoi(env);
       return attn_tc4_launch(a, poly4, reinterpret_cast<cudaStream_t>(stream));
     }

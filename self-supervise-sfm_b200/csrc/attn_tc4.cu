@@ -440,10 +440,13 @@ int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
             static_cast<unsigned>(a->batch));
   switch (poly) {
     case 0: return launch4<0>(grid, st, tq, tk, tv, tpk, tpv, p);
+    case 1: return launch4<1>(grid, st, tq, tk, tv, tpk, tpv, p);
     case 2: return launch4<2>(grid, st, tq, tk, tv, tpk, tpv, p);
+    case 3: return launch4<3>(grid, st, tq, tk, tv, tpk, tpv, p);
+    case 4: return launch4<4>(grid, st, tq, tk, tv, tpk, tpv, p);
     case 8: return launch4<8>(grid, st, tq, tk, tv, tpk, tpv, p);
   }
-  return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16 (4-tile kernel): SR_ATTN_POLY must be 0, 2 or 8 (got %d)", poly);
+  return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16 (4-tile kernel): SR_ATTN_POLY must be 0..4 or 8 (got %d)", poly);
 }
 
 }  // namespace sr
