@@ -39,7 +39,8 @@ struct GemmCfg {
   static constexpr int kABytes = kBM * kBK * 2;
   static constexpr int kBBytes = BN * kBK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // +1024: manual 1 KB alignment
+  static constexpr int kEpiStageBytes = 8 * 4096;                  // 4 KB transpose buffer per epilogue warp (LS_RESIDUAL)
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiStageBytes + 1024;  // +1024: manual 1 KB alignment
   static constexpr int kTmemCols = 2 * BN;                         // double-buffered accumulator
 };
 
@@ -320,14 +321,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       const int row = m_blk * kBM + quarter * 32 + lane;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + as * BN + half * kColsPerWarp;
       const int col_base = n_blk * BN + half * kColsPerWarp;
-      // LayerScale-residual epilogue: the fp32 residual row fragment does not depend on the accumulator, so its loads
-      // are issued BEFORE the wait for the MMA and fly under it (they were the epilogue's critical path: every chunk
-      // used to stall a full memory latency after the accumulator was ready).
+      // LayerScale-residual epilogue (fp32 read-modify-write of the residual stream).  tcgen05.ld hands every lane one
+      // ROW, and a row-per-lane float4 access touches 32 cache lines per instruction -- at K = 1024 (proj) that L1
+      // traffic, not the MMA, bounded the kernel (596 TFLOP/s).  The accumulator chunk is therefore transposed through a
+      // 4 KB XOR-swizzled shared-memory buffer per warp so that global loads / stores are row-contiguous: lane l handles
+      // row 4 i + l / 8, float4 column l % 8 -- four full 128 B lines per instruction.  The residual fragment does not
+      // depend on the accumulator: it is loaded (in that layout) BEFORE the wait for the MMA and flies under it.
       float4 resid_regs[EPI == SR_EPI_LS_RESIDUAL ? kColsPerWarp / 4 : 1];
-      if (EPI == SR_EPI_LS_RESIDUAL && row < p.M) {
-        const float4* r4 = reinterpret_cast<const float4*>(p.e.resid + static_cast<int64_t>(row) * p.e.ldr + col_base);
+      const int trow = lane >> 3, tc4 = lane & 7;
+      const int row0 = m_blk * kBM + quarter * 32;
+      if (EPI == SR_EPI_LS_RESIDUAL) {
 #pragma unroll
-        for (int i = 0; i < kColsPerWarp / 4; ++i) resid_regs[i] = r4[i];
+        for (int c = 0; c < kColsPerWarp / 32; ++c) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = row0 + i * 4 + trow;
+            if (r < p.M)
+              resid_regs[c * 8 + i] = *reinterpret_cast<const float4*>(p.e.resid + static_cast<int64_t>(r) * p.e.ldr +
+                                                                       col_base + c * 32 + tc4 * 4);
+          }
+        }
       }
       RopeRow rope_row;
       if (EPI == SR_EPI_QKV && p.e.rope && row < p.M && p.e.col_offset + col_base < 2 * p.e.qkv_dim)
@@ -349,12 +362,38 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
       } else {
         if (EPI == SR_EPI_LS_RESIDUAL) {
+          float* tbuf = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes) + ew * 1024;
+          const sr_epilogue_t& e = p.e;
 #pragma unroll
-          for (int c = 0; c < kColsPerWarp; c += 32) {
+          for (int c = 0; c < kColsPerWarp / 32; ++c) {
             uint32_t v[32];
-            tmem_ld32(taddr + c, v);
+            tmem_ld32(taddr + c * 32, v);
             tmem_ld_wait();
-            if (row < p.M) epi_store32<EPI, OUT_BF16>(p, row, col_base + c, v, &resid_regs[c / 4]);
+            // lane = row: float4 k of the row goes to slot k ^ (lane & 7) (conflict-free both ways)
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              *reinterpret_cast<uint4*>(tbuf + lane * 32 + ((k ^ (lane & 7)) << 2)) =
+                  make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+            __syncwarp();
+            const int col = col_base + c * 32 + tc4 * 4;
+            const float4 b4 = e.bias ? __ldg(reinterpret_cast<const float4*>(e.bias + col)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 g4 = e.gamma ? __ldg(reinterpret_cast<const float4*>(e.gamma + col)) : make_float4(1.f, 1.f, 1.f, 1.f);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int rl = i * 4 + trow;
+              const float4 a = *reinterpret_cast<const float4*>(tbuf + rl * 32 + ((tc4 ^ (rl & 7)) << 2));
+              const int r = row0 + rl;
+              if (r < p.M) {
+                const float4 rr = resid_regs[c * 8 + i];
+                float4 y;
+                y.x = rr.x + g4.x * bf16_round(a.x + b4.x);
+                y.y = rr.y + g4.y * bf16_round(a.y + b4.y);
+                y.z = rr.z + g4.z * bf16_round(a.z + b4.z);
+                y.w = rr.w + g4.w * bf16_round(a.w + b4.w);
+                *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + static_cast<int64_t>(r) * e.ldo + col) = y;
+              }
+            }
+            __syncwarp();
           }
         } else {
 #pragma unroll 1
