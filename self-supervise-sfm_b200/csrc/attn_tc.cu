@@ -31,6 +31,7 @@ namespace sr {
 extern int g_launch_count;
 int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st);   // attn_tc4.cu
 int attn_tc4_trace_read(long long* host_dst, int64_t count);
+int attn_tc3_launch(const sr_attn_t* a, int poly, cudaStream_t st);   // attn_tc3.cu
 constexpr int kAtKernelDefault = 4;   // query tiles per CTA: 2 (this file) or 4 (attn_tc4.cu); SR_ATTN_KERNEL overrides
 
 constexpr int kAtNQ = 2;
@@ -485,13 +486,30 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
              "sr_attn_fwd_bf16: sequence too long");
 
   {
+    // Kernel choice.  The three- and four-tile kernels run the same ~590 clk per (128-row query tile x 64-row K/V tile)
+    // and one CTA per SM, so the launch time is  waves x tiles-per-CTA: pick the variant whose CTA count quantises
+    // better onto the SMs (16-anchor global: 688 CTAs of four tiles = 5 waves against 928 of three = 7 x 0.75;
+    // 16-frame reloc: 768 = 6 waves against 1024 = 7 x 0.75).  SR_ATTN_KERNEL = 2 / 3 / 4 forces a variant.
     int variant = kAtKernelDefault;
-    if (const char* env = getenv("SR_ATTN_KERNEL")) variant = atoi(env);
-    if (variant == 4) {
-      int poly4 = 2;   // polynomial exp2 on the FMA pipe for 2 of every 8 pairs: measured best (0: 851, 1: 905, 2: 921, 3: 892, 4: 843 TF/s)
-      if (const char* env = getenv("SR_ATTN_POLY")) poly4 = atoi(env);
-      return attn_tc4_launch(a, poly4, reinterpret_cast<cudaStream_t>(stream));
+    if (const char* env = getenv("SR_ATTN_KERNEL")) {
+      variant = atoi(env);
+    } else {
+      static int num_sms = 0;
+      if (num_sms == 0) {
+        int dev = 0;
+        SR_CHECK_CUDA(cudaGetDevice(&dev));
+        SR_CHECK_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+      }
+      const int64_t hb = static_cast<int64_t>(a->num_heads) * a->batch;
+      const int64_t waves3 = (((a->q_len + 383) / 384) * hb + num_sms - 1) / num_sms;
+      const int64_t waves4 = (((a->q_len + 511) / 512) * hb + num_sms - 1) / num_sms;
+      variant = (3 * waves3 < 4 * waves4) ? 3 : 4;
     }
+    // polynomial exp2 on the FMA pipe for 2 of every 8 pairs: measured best (0: 851, 1: 905, 2: 921, 3: 892, 4: 843 TF/s)
+    int poly = 2;
+    if (const char* env = getenv("SR_ATTN_POLY")) poly = atoi(env);
+    if (variant == 4) return attn_tc4_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
+    if (variant == 3) return attn_tc3_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
   }
   const uint64_t qbs = a->batch > 1 ? a->q_batch_stride : a->q_len;
   const uint64_t kbs = a->batch > 1 ? a->kv_batch_stride : a->kv_len;
