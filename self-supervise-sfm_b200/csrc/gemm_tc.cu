@@ -362,7 +362,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
       } else {
         if (EPI == SR_EPI_LS_RESIDUAL) {
-          float* tbuf = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes) + ew * 1024;
+          const uint32_t tbuf = smem_u32(smem + Cfg::kStages * Cfg::kStageBytes) + ew * 4096;   // shared-space byte address
           const sr_epilogue_t& e = p.e;
 #pragma unroll
           for (int c = 0; c < kColsPerWarp / 32; ++c) {
@@ -372,8 +372,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             // lane = row: float4 k of the row goes to slot k ^ (lane & 7) (conflict-free both ways)
 #pragma unroll
             for (int k = 0; k < 8; ++k)
-              *reinterpret_cast<uint4*>(tbuf + lane * 32 + ((k ^ (lane & 7)) << 2)) =
-                  make_uint4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+              sts128(tbuf + lane * 128 + ((k ^ (lane & 7)) << 4), v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
             __syncwarp();
             const int col = col_base + c * 32 + tc4 * 4;
             const float4 b4 = e.bias ? __ldg(reinterpret_cast<const float4*>(e.bias + col)) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -381,7 +380,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const int rl = i * 4 + trow;
-              const float4 a = *reinterpret_cast<const float4*>(tbuf + rl * 32 + ((tc4 ^ (rl & 7)) << 2));
+              const float4 a = lds128(tbuf + rl * 128 + ((tc4 ^ (rl & 7)) << 4));
               const int r = row0 + rl;
               if (r < p.M) {
                 const float4 rr = resid_regs[c * 8 + i];
