@@ -83,12 +83,12 @@ gemm_f32_kernel(const GemmF32Params p) {
 
 // ---------------------------------------------------------------------------------------------- skinny path
 // Few rows (the camera head: M = Na + Nq camera tokens, tens of rows) against big weights (216 M fp32 parameters,
-// camera_head.py:59-83): the work is streaming W once from HBM.  Warp-per-output-column: a warp owns 2 rows of W, its
+// camera_head.py:59-83): the work is streaming W once from HBM.  Warp-per-output-column: a warp owns 4 rows of W, its
 // lanes split K in float4s (fully coalesced 512 B per row per step), A[32 rows, 256 k] is staged in shared memory by
-// cp.async (double buffered) and every A float4 read from smem feeds 8 FMAs.  The 2 x 32 per-lane partial sums are
+// cp.async (double buffered) and every A float4 read from smem feeds 16 FMAs.  The 4 x 32 per-lane partial sums are
 // reduced with a 31-shuffle transpose-reduce so that lane l ends up owning row m0 + l.  Grid = N/16 x ceil(M/32) CTAs
 // (128 ... 512 CTAs for the camera-head shapes) instead of the 32 ... 128 CTAs of the 64x64 tiling above.
-constexpr int kSkM = 32, kSkKC = 256, kSkWarps = 8, kSkNPerWarp = 2;
+constexpr int kSkM = 32, kSkKC = 256, kSkWarps = 4, kSkNPerWarp = 4;   // 16 FMAs per LDS.128: shared-memory reads no longer bound the loop
 constexpr int kSkSmem = 2 * kSkM * kSkKC * 4;
 
 __device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
@@ -125,10 +125,10 @@ gemm_f32_skinny_kernel(const GemmF32Params p) {
   const int num_kc = (p.K + kSkKC - 1) / kSkKC;
 
   auto stage_a = [&](int kc, int buf) {
-    // 32 rows x 64 float4 = 2048 float4, 256 threads -> 8 each; a warp covers 512 contiguous bytes of one row
+    // 32 rows x 64 float4 = 2048 float4 over the CTA's threads; a warp covers 512 contiguous bytes of one row
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int f = tid + i * 256;
+    for (int i = 0; i < kSkM * (kSkKC / 4) / (kSkWarps * 32); ++i) {
+      const int f = tid + i * kSkWarps * 32;
       const int r = f >> 6, c4 = f & 63;
       const int gm = m0 + r, gk = kc * kSkKC + c4 * 4;
       const bool ok = gm < p.M && gk < p.K;
