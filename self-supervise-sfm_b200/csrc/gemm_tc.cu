@@ -114,6 +114,26 @@ __device__ __forceinline__ void epi_store32(const GemmParams& p, int row, int co
   }
 }
 
+// v[32] = raw accumulators of one row, columns [col, col+32): bias (+ GELU) and pack to 16 bf16x2 words.
+template <int EPI>
+__device__ __forceinline__ void epi_pack32(const GemmParams& p, int col, const uint32_t (&v)[32], uint32_t* out16) {
+  const sr_epilogue_t& e = p.e;
+#pragma unroll
+  for (int i = 0; i < 32; i += 4) {
+    const float4 b = e.bias ? __ldg(reinterpret_cast<const float4*>(e.bias + col + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float x0 = __uint_as_float(v[i + 0]) + b.x, x1 = __uint_as_float(v[i + 1]) + b.y;
+    float x2 = __uint_as_float(v[i + 2]) + b.z, x3 = __uint_as_float(v[i + 3]) + b.w;
+    if (EPI == SR_EPI_BIAS_GELU) {
+      x0 = gelu_erf_fast(bf16_round(x0));
+      x1 = gelu_erf_fast(bf16_round(x1));
+      x2 = gelu_erf_fast(bf16_round(x2));
+      x3 = gelu_erf_fast(bf16_round(x3));
+    }
+    out16[(i >> 1) + 0] = pack_bf16x2(x0, x1);
+    out16[(i >> 1) + 1] = pack_bf16x2(x2, x3);
+  }
+}
+
 // RoPE table rows of one token, fetched before the accumulator is ready (pos -> table is a dependent load chain).
 struct RopeRow {
   float c[2][16];   // [y | x][frequency]
@@ -138,8 +158,8 @@ __device__ __forceinline__ void load_rope_row(const sr_epilogue_t& e, int row, R
 // One 64-wide head of q or k for one token: bias -> bf16 round -> LayerNorm(64) -> 2D RoPE -> bf16 store.
 // `which` = 0 (q) / 1 (k) / 2 (v: bias + store only).  Reductions run as 4 independent chains: with 2 epilogue warps per
 // SM sub-partition a 64-long dependent FADD chain is pure exposed latency.
-__device__ __forceinline__ void epi_qkv_head(const GemmParams& p, int row, int col, int which, uint32_t (&v0)[32],
-                                             uint32_t (&v1)[32], const RopeRow& rope) {
+__device__ __forceinline__ void epi_qkv_head(const GemmParams& p, int col, int which, uint32_t (&v0)[32],
+                                             uint32_t (&v1)[32], const RopeRow& rope, uint32_t (&pk)[32]) {
   const sr_epilogue_t& e = p.e;
   float x[64];
 #pragma unroll
@@ -196,16 +216,8 @@ __device__ __forceinline__ void epi_qkv_head(const GemmParams& p, int row, int c
       }
     }
   }
-  __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + static_cast<int64_t>(row) * e.ldo + col;
 #pragma unroll
-  for (int i = 0; i < 64; i += 8) {
-    uint4 w;
-    w.x = pack_bf16x2(x[i + 0], x[i + 1]);
-    w.y = pack_bf16x2(x[i + 2], x[i + 3]);
-    w.z = pack_bf16x2(x[i + 4], x[i + 5]);
-    w.w = pack_bf16x2(x[i + 6], x[i + 7]);
-    *reinterpret_cast<uint4*>(o + i) = w;
-  }
+  for (int i = 0; i < 64; i += 2) pk[i >> 1] = pack_bf16x2(x[i], x[i + 1]);   // the kernel stores them row-contiguously
 }
 
 // ---------------------------------------------------------------------------------------------- kernel
@@ -348,17 +360,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       mbar_wait(&tmem_full_bar[as], (it >> 1) & 1);
       tc_fence_after();
       if (EPI == SR_EPI_QKV) {
+        // one head (64 columns = 128 B of bf16) per row and chunk; stored through the swizzled transpose buffer like the
+        // other bf16 epilogues (rows past M compute on garbage and are simply not stored)
+        const uint32_t tbuf = smem_u32(smem + Cfg::kStages * Cfg::kStageBytes) + ew * 4096;
+        __nv_bfloat16* outp = reinterpret_cast<__nv_bfloat16*>(p.e.out);
 #pragma unroll 1
         for (int c = 0; c < kColsPerWarp; c += 64) {
-          uint32_t v0[32], v1[32];
+          uint32_t v0[32], v1[32], pk[32];
           tmem_ld32(taddr + c, v0);
           tmem_ld32(taddr + c + 32, v1);
           tmem_ld_wait();
-          if (row < p.M) {
-            const int col = col_base + c;
-            const int which = static_cast<int>((p.e.col_offset + col) / p.e.qkv_dim);
-            epi_qkv_head(p, row, col, which, v0, v1, rope_row);
+          const int col = col_base + c;
+          const int which = static_cast<int>((p.e.col_offset + col) / p.e.qkv_dim);
+          epi_qkv_head(p, col, which, v0, v1, rope_row, pk);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            sts128(tbuf + lane * 128 + ((k ^ (lane & 7)) << 4), pk[4 * k], pk[4 * k + 1], pk[4 * k + 2], pk[4 * k + 3]);
+          __syncwarp();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rl = i * 4 + trow;
+            const uint4 w = lds128u(tbuf + rl * 128 + ((tc4 ^ (rl & 7)) << 4));
+            const int r = row0 + rl;
+            if (r < p.M) *reinterpret_cast<uint4*>(outp + static_cast<int64_t>(r) * p.e.ldo + col + tc4 * 8) = w;
           }
+          __syncwarp();
         }
       } else {
         if (EPI == SR_EPI_LS_RESIDUAL) {
@@ -391,6 +417,33 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 y.w = rr.w + g4.w * bf16_round(a.w + b4.w);
                 *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + static_cast<int64_t>(r) * e.ldo + col) = y;
               }
+            }
+            __syncwarp();
+          }
+        } else if (OUT_BF16) {
+          // bf16 outputs (bias / bias + GELU): 64 columns = 128 B per row and chunk, transposed through the same swizzled
+          // 4 KB/warp buffer so that every store instruction writes four full 128 B lines (lane l: row 4 i + l / 8,
+          // 16 B piece l % 8) instead of 16 B in each of 32 rows.
+          const uint32_t tbuf = smem_u32(smem + Cfg::kStages * Cfg::kStageBytes) + ew * 4096;
+          __nv_bfloat16* outp = reinterpret_cast<__nv_bfloat16*>(p.e.out);
+#pragma unroll 1
+          for (int c = 0; c < kColsPerWarp; c += 64) {
+            uint32_t v0[32], v1[32], pk[32];
+            tmem_ld32(taddr + c, v0);
+            tmem_ld32(taddr + c + 32, v1);
+            tmem_ld_wait();
+            epi_pack32<EPI>(p, col_base + c, v0, &pk[0]);
+            epi_pack32<EPI>(p, col_base + c + 32, v1, &pk[16]);
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+              sts128(tbuf + lane * 128 + ((k ^ (lane & 7)) << 4), pk[4 * k], pk[4 * k + 1], pk[4 * k + 2], pk[4 * k + 3]);
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int rl = i * 4 + trow;
+              const uint4 w = lds128u(tbuf + rl * 128 + ((tc4 ^ (rl & 7)) << 4));
+              const int r = row0 + rl;
+              if (r < p.M) *reinterpret_cast<uint4*>(outp + static_cast<int64_t>(r) * p.e.ldo + col_base + c + tc4 * 8) = w;
             }
             __syncwarp();
           }
