@@ -120,14 +120,14 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       const uint32_t ph = ((j / k3Stages) & 1) ^ 1;
       const bool pre = j < p.n_prefix_tiles;
       const int r0 = (pre ? j : j - p.n_prefix_tiles) * 64;
-      mbar_wait(&k_empty[s], ph);
+      mbar_wait_relaxed(&k_empty[s], ph);
       if (elect_one()) {
         mbar_arrive_expect_tx(&k_full[s], k3KvTile);
         if (pre) tma_load_2d(sK + s * k3KvTile, &tmap_pk, &k_full[s], head * 64, r0);
         else     tma_load_3d(sK + s * k3KvTile, &tmap_k, &k_full[s], head * 64, r0, b);
       }
       __syncwarp();
-      mbar_wait(&v_empty[s], ph);
+      mbar_wait_relaxed(&v_empty[s], ph);
       if (elect_one()) {
         mbar_arrive_expect_tx(&v_full[s], k3KvTile);
         if (pre) tma_load_2d(sV + s * k3KvTile, &tmap_pv, &v_full[s], head * 64, r0);

@@ -131,7 +131,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     __syncwarp();
     for (int j = 0; j < n_tiles; ++j) {
       const int s = j % k4Stages;
-      mbar_wait(&kv_empty[s], ((j / k4Stages) & 1) ^ 1);
+      mbar_wait_relaxed(&kv_empty[s], ((j / k4Stages) & 1) ^ 1);
       if (elect_one()) {
         const bool has_k = j + 1 < n_tiles;
         mbar_arrive_expect_tx(&kv_full[s], has_k ? 2 * k4KvTile : k4KvTile);

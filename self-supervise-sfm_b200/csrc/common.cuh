@@ -68,6 +68,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #endif
 }
 
+// Wait of a warp whose wake-up latency is not critical (TMA producer far ahead of its ring, epilogue warps behind a
+// double-buffered accumulator): sleeps between probes.  The step runs into the board power cap; a tight polling loop
+// burns issue energy for nothing (ncu: 28 % of the instructions executed by the attention kernel were the BRA / UIADD3 /
+// UISETP / SYNCS of spinning warps).
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t* bar, uint32_t parity, uint32_t sleep_ns = 96) {
+#ifdef SR_DEBUG_HANG_TRAP
+  uint32_t spins = 0;
+#endif
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(sleep_ns);
+#ifdef SR_DEBUG_HANG_TRAP
+    if (++spins > (1u << 24)) { __trap(); }
+#endif
+  }
+}
+
 // One lane of a fully converged warp.  TMA / tcgen05 issue code runs warp-wide (uniform control flow, warp index taken
 // through __shfl_sync so the compiler knows it is uniform) with only the issuing instruction under this predicate: the
 // operands then live in uniform registers.  Issuing from an `if (lane == 0)` branch instead makes every UTCHMMA /

@@ -274,7 +274,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
       const int m_blk = t / num_n, n_blk = t % num_n;
       for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_wait_relaxed(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kABytes;
         if (elect_one()) {
@@ -357,7 +357,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
       RopeRow rope_row;
       if (EPI == SR_EPI_QKV && p.e.rope && row < p.M && p.e.col_offset + col_base < 2 * p.e.qkv_dim)
         load_rope_row(p.e, row, rope_row);
-      mbar_wait(&tmem_full_bar[as], (it >> 1) & 1);
+      mbar_wait_relaxed(&tmem_full_bar[as], (it >> 1) & 1);
       tc_fence_after();
       if (EPI == SR_EPI_QKV) {
         // one head (64 columns = 128 B of bf16) per row and chunk; stored through the swizzled transpose buffer like the
