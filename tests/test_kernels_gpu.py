@@ -242,6 +242,41 @@ def test_attention_bf16_carry_equals_single_pass():
     assert rel_l2(two.float().cpu(), one.float().cpu()) < 4e-3
 
 
+@pytest.mark.parametrize("variant", [2, 3, 4])
+def test_attention_bf16_every_kernel_variant(variant, monkeypatch):
+    """sr_attn_fwd_bf16 picks the three- or four-tile kernel per launch by wave quantisation (attn_tc.cu); SR_ATTN_KERNEL
+    forces a variant.  Every variant (incl. the original two-tile kernel) must pass the segment, ragged-tail, prefix and
+    carry cases on its own: partial last query tile, K/V length that is not a multiple of the 64- or 128-row tile, a
+    scene prefix that ends inside a tile, and the ring carry in / out."""
+    monkeypatch.setenv("SR_ATTN_KERNEL", str(variant))
+    ops = _ops()
+    H, d = 16, 64
+    g = _g(40 + variant)
+    for batch, L, prefix_len in ((2, 1374, 0), (1, 600, 0), (3, 70, 0), (2, 333, 305), (1, 129, 64)):
+        qkv = torch.randn(batch * L, 3 * H * d, generator=g)
+        pkv = torch.randn(max(prefix_len, 1), 2 * H * d, generator=g)
+        qkv_d, pkv_d = bf(qkv).to(DEV), bf(pkv).to(DEV)
+        q, k, v = (qkv_d[:, i * H * d:(i + 1) * H * d] for i in range(3))
+        out = torch.empty(batch * L, H * d, dtype=torch.bfloat16, device=DEV)
+        kw = dict(prefix_k=pkv_d[:, :H * d], prefix_v=pkv_d[:, H * d:], prefix_len=prefix_len) if prefix_len else {}
+        ops.attention(q, k, v, out, H, d, batch, L, L, L, L, **kw)
+        qc, kc, vc = (bf(qkv[:, i * H * d:(i + 1) * H * d]).float() for i in range(3))
+        pre = (bf(pkv[:, :H * d]).float(), bf(pkv[:, H * d:]).float(), prefix_len) if prefix_len else None
+        ref = _attn_ref(qc, kc, vc, H, d, [(b * L, L, b * L, L) for b in range(batch)], prefix=pre)
+        assert rel_l2(out.cpu().float(), ref) < 6e-3, (variant, batch, L, prefix_len)
+    # carry: two K/V halves with (m, l, acc) carried == one pass
+    L, half = 700, 333
+    qkv = bf(torch.randn(L, 3 * H * d, generator=g)).to(DEV)
+    q, k, v = (qkv[:, i * H * d:(i + 1) * H * d] for i in range(3))
+    one = torch.empty(L, H * d, dtype=torch.bfloat16, device=DEV)
+    ops.attention(q, k, v, one, H, d, 1, L, L)
+    m, l, acc = torch.empty(H, L, device=DEV), torch.empty(H, L, device=DEV), torch.empty(L, H * d, device=DEV)
+    two = torch.empty(L, H * d, dtype=torch.bfloat16, device=DEV)
+    ops.attention(q, k[:half], v[:half], None, H, d, 1, L, half, carry=(m, l, acc), carry_out=True)
+    ops.attention(q, k[half:], v[half:], two, H, d, 1, L, L - half, carry=(m, l, acc), carry_in=True)
+    assert rel_l2(two.float().cpu(), one.float().cpu()) < 4e-3
+
+
 @pytest.mark.parametrize("d,H", [(128, 16), (64, 2)])
 def test_attention_f32(d, H):
     ops = _ops()
