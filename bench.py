@@ -14,6 +14,8 @@ N > 1 (torchrun): one process per GPU, one independent scene per rank (the refer
 train/train_imc.py:494-504) — no data-path collective, weak scaling.
 Workload "imc" (BASELINE.json configs[2]): --anchors 100 --queries 200 in ONE pass (the reference's dense mask would
 need 170 GB here; the structured prefix + own-frame attention does not build it).
+Workload "scene": ONE scene of 256 + 256 frames (N = 512) sharded by frame over the ranks, full aggregator + camera head
+(parallel.sharded_scene_forward); strong scaling.
 Workload "ring" (BASELINE.json configs[3]): the sequence-sharded global-attention stack, see parallel.py.
 
 --impl reference: the reference's CPU path restated by the oracle (oracle/sailrecon_oracle.py; the Python reference
@@ -234,7 +236,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="agg32", choices=["agg32", "imc", "ring"])
+    ap.add_argument("--workload", default="agg32", choices=["agg32", "imc", "ring", "scene"])
     ap.add_argument("--anchors", type=int, default=100, help="workload imc: anchor frames (build the scene tokens)")
     ap.add_argument("--queries", type=int, default=200, help="workload imc: query frames localised against the anchors")
     ap.add_argument("--frames", type=int, default=32)
@@ -252,6 +254,12 @@ def main():
     if args.workload == "ring":
         from sailrecon_b200 import parallel
         parallel.bench_ring(args, rank, world, local)
+        return
+    if args.workload == "scene":
+        from sailrecon_b200 import parallel
+        if args.anchors == 100 and args.queries == 200:      # defaults of --workload imc; scene defaults to N = 512
+            args.anchors = args.queries = 256
+        parallel.bench_scene(args, rank, world, local)
         return
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a B200: sailrecon_b200 has no CPU fallback (use --impl reference for the CPU arm)")

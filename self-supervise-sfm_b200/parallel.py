@@ -288,3 +288,230 @@ def bench_ring(args, rank: int, world: int, local: int) -> None:
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------ whole scene, frame-sharded
+@dataclass
+class ScenePlan:
+    """contiguous frame ranges per rank, anchors Na/R each and queries Nq/R each; the residual stream of
+    a rank's frames stays on that rank for the whole 24-layer loop."""
+    rank: int
+    world: int
+    Na: int
+    Nq: int
+    anchors: List[Tuple[int, int]]                     # per rank (first anchor, count)
+    queries: List[Tuple[int, int]]                     # per rank (first query, count), query j is input frame Na + j
+
+    @classmethod
+    def make(cls, Na: int, Nq: int, rank: int, world: int) -> "ScenePlan":
+        if Na < world:
+            raise ValueError(f"sharded scene needs at least one anchor frame per rank (anchors {Na}, ranks {world})")
+        return cls(rank, world, Na, Nq, partition_frames(Na, world), partition_frames(Nq, world))
+
+    def local_frames(self, r: Optional[int] = None) -> List[int]:
+        """Input-frame indices ([anchors ; queries] numbering of demo_imc_forward) held by rank r, anchors first."""
+        r = self.rank if r is None else r
+        (a0, na), (q0, nq) = self.anchors[r], self.queries[r]
+        return list(range(a0, a0 + na)) + list(range(self.Na + q0, self.Na + q0 + nq))
+
+
+def _allgather_rows(dst: torch.Tensor, local: torch.Tensor, counts: Sequence[int], rank: int, group=None) -> torch.Tensor:
+    """dst[sum(counts), ...] <- concatenation of every rank's `local` rows (uneven counts: one broadcast per rank)."""
+    off = 0
+    for r, c in enumerate(counts):
+        if c:
+            if r == rank:
+                dst[off:off + c].copy_(local)
+            if dist.is_initialized() and len(counts) > 1:
+                dist.broadcast(dst[off:off + c], src=_global_rank(group, r), group=group)
+        off += c
+    return dst
+
+
+def sharded_scene_forward(agg, head, images_local: torch.Tensor, plan: ScenePlan, fix_rank: Optional[int] = 300, group=None):
+    """Aggregator.forward + CameraHead.forward (models/aggregator.py:242-433, heads/camera_head.py:85-121) for ONE scene
+    whose frames are partitioned over the ranks.  `images_local` [1, na_r + nq_r, 3, H, W] holds this rank's anchors, then
+    its queries (ScenePlan.local_frames).  Per layer: frame block rank-local; scene tokens of the local anchors projected to
+    K|V locally and all-gathered (the reloc block's shared prefix); reloc block on the local query frames; global block
+    with ring K/V over the anchors (ring_global_block).  The camera head runs on [all anchor camera tokens ; local queries]
+    (its mask lets queries see the anchors and themselves only, camera_head.py:197-228).  agg.generator must be seeded
+    identically on every rank: each rank replays the whole scene-token draw (aggregator.py:617-619) and keeps its part.
+    Returns (output_dict of the local query frames, pose encodings of the local query frames)."""
+    from . import ops
+    from .engine import AttnCall, Prefix
+    mode = engine.compute_mode()
+    if mode != "bf16":
+        raise NotImplementedError("sailrecon_b200: the sharded scene path runs the bf16 (autocast) mode")
+    B, S_l, C_in, H, W = images_local.shape
+    r, R = plan.rank, plan.world
+    (a0, na), (q0, nq) = plan.anchors[r], plan.queries[r]
+    if B != 1 or C_in != 3 or S_l != na + nq:
+        raise ValueError(f"sharded_scene_forward: rank {r} expects [1, {na + nq}, 3, H, W], got {tuple(images_local.shape)}")
+    engine.require_cuda_f32(images_local, "images_local")
+    dev = images_local.device
+    Na, Nq = plan.Na, plan.Nq
+    agg.num_recon = Na
+    C = agg.camera_token.shape[-1]
+    psi = agg.patch_start_idx
+    h, w = H // agg.patch_size, W // agg.patch_size
+    hw = h * w
+    P = psi + hw
+    agg.rank = agg._draw_rank(fix_rank, hw, clamp=True)
+    l_prime = min(agg.rank, hw)
+    Pp = psi + l_prime
+    act = torch.bfloat16
+
+    X = engine.WS.get("shard.x", (S_l * P, C), torch.float32, dev)
+    agg._embed(images_local[0].contiguous(), mode, X, S_l, P, C)
+    with torch.no_grad():
+        X.view(S_l, P, C)[:, :psi] = agg._special_rows(plan.local_frames(), set(range(Na, Na + Nq)), False)
+    rows_pos, frame_pos_cpu = agg._positions(S_l, h, w, dev)
+    pos_a = RowPositions(rows_pos.pos32[:na * P], rows_pos.max_pos)
+    pos_q = RowPositions(rows_pos.pos32[na * P:], rows_pos.max_pos)
+    Xa, Xq = X[:na * P], X[na * P:]
+    frame_calls = engine.full_segments(S_l, P)
+    ring = RingPlan(r, R, P, plan.anchors)
+    key = ("shard.ring", Na, P, r, R, str(dev))
+    ws = agg.__dict__.setdefault("_sr_ring_ws", {}).get(key)
+    if ws is None:
+        ws = RingWorkspace(ring, C, agg.global_blocks[0].attn.num_heads, dev)
+        agg.__dict__["_sr_ring_ws"] = {key: ws}
+    scene_counts = [c * Pp for _, c in plan.anchors]
+    output_dict = {}
+    cam_token_last_layer = None
+    for i in range(agg.depth):
+        engine.run_block(agg.frame_blocks[i], X, frame_calls, rows_pos, mode, tag="agg.")
+        out_i = None
+        if i in agg.intermediate_layer_idx and nq > 0:
+            out_i = torch.empty(1, nq, P, 2 * C, dtype=torch.float32, device=dev)
+            ops.copy_cols(Xq, out_i.view(nq * P, 2 * C), 0)
+        if i == agg.depth - 1:
+            cam_frame = X.view(S_l, P, C)[:na, 0].clone()
+        # scene tokens: every rank replays the draw for ALL anchors, projects its own anchors' rows, gathers the rest
+        packed, _ = agg._draw_scene(Na, P, hw, l_prime, frame_pos_cpu)
+        mine = packed[a0 * Pp:(a0 + na) * Pp].clone()
+        mine[:, 0] -= a0 * P                                                             # row index into the local X
+        mine = mine.pin_memory().to(dev, non_blocking=True)
+        idx, spos = mine[:, 0].contiguous(), mine[:, 1:].contiguous()
+        rblk = agg.global_reloc_blocks[i]
+        if Nq > 0:
+            a_s = engine.WS.get("shard.scene_a", (na * Pp, C), act, dev)
+            w1, b1, eps1 = engine.ln_params(rblk.norm1)
+            ops.layernorm(X, w1, b1, eps1, a_s, idx=idx)
+            skv_l = engine.WS.get("shard.scene_kv_local", (na * Pp, 2 * C), act, dev)
+            engine.qkv_rows(rblk.attn, a_s, skv_l, mode, RowPositions(spos, rows_pos.max_pos), col_offset=C)
+            skv = engine.WS.get("shard.scene_kv", (Na * Pp, 2 * C), act, dev)
+            _allgather_rows(skv, skv_l, scene_counts, r, group)
+            if nq > 0:
+                engine.run_block(rblk, Xq, [AttnCall(0, nq, P, P, Prefix(skv[:, :C], skv[:, C:], 0, Na * Pp))], pos_q, mode,
+                                 tag="agg.")
+        ring_global_block(agg.global_blocks[i], Xa, pos_a, ring, ws, group, mode)
+        if out_i is not None:
+            ops.copy_cols(Xq, out_i.view(nq * P, 2 * C), C)
+            output_dict[i] = out_i
+        if i == agg.depth - 1:
+            cam_l = torch.cat([cam_frame, X.view(S_l, P, C)[:na, 0]], dim=-1).contiguous()
+            cam_all = torch.empty(Na, 2 * C, dtype=torch.float32, device=dev)
+            _allgather_rows(cam_all, cam_l, [c for _, c in plan.anchors], r, group)
+            cam_token_last_layer = cam_all[None]
+    poses = []
+    if nq > 0:
+        output_dict[-1] = output_dict[agg.depth - 1]
+        with torch.autocast("cuda", enabled=False):
+            poses = head(output_dict, cam_token_last_layer)
+    return output_dict, poses
+
+
+def bench_scene(args, rank: int, world: int, local: int) -> None:
+    """bench.py --workload scene: ONE scene of --anchors + --queries frames (default 256 + 256 = the N = 512 of the
+    BASELINE.json metric), full aggregator + camera head, frames sharded over the ranks (sharded_scene_forward).  Strong
+    scaling: total work is fixed as N grows.  value = frames / s, device time, max over ranks."""
+    import bench as _bench
+    from . import ops
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --workload scene needs B200s: sailrecon_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+    Na, Nq, size = args.anchors, args.queries, args.size
+    plan = ScenePlan.make(Na, Nq, rank, world)
+    agg, head = _bench.build_models(dev)                    # torch.manual_seed(0): identical weights on every rank
+    frames = plan.local_frames()
+    host = torch.empty(1, len(frames), 3, size, size).pin_memory()
+    for i, f in enumerate(frames):                          # seeded by the GLOBAL frame index: same scene for every world size
+        host[0, i] = torch.rand(3, size, size, generator=torch.Generator().manual_seed(10_007 + f))
+    images = host.to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(img):
+        agg.generator.manual_seed(1234)                     # the same scene-token draw on every rank
+        with torch.no_grad():
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                return sharded_scene_forward(agg, head, img, plan, fix_rank=300)[1]
+
+    for _ in range(args.warmup):
+        step(images)
+    barrier()
+    clocks = _bench.ClockSampler(local)
+    clocks.start()
+    n0 = ops.num_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        poses = step(images)
+    e1.record()
+    barrier()
+    launches = ops.num_kernel_launches() - n0
+    clk = clocks.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    # end to end: local frames from pinned host memory in, local pose encodings out
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0.record()
+    for _ in range(args.steps):
+        poses = step(host.to(dev, non_blocking=True))
+        host_poses = torch.stack(poses).cpu() if poses else torch.zeros(0)
+    t1.record()
+    barrier()
+    ms_e2e = t0.elapsed_time(t1) / args.steps
+    finite = bool(all(torch.isfinite(p).all() for p in poses))
+    if world > 1:
+        t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(t[0]), float(t[1])
+        fin = torch.tensor([1.0 if finite else 0.0], device=dev)
+        dist.all_reduce(fin, op=dist.ReduceOp.MIN)
+        finite = bool(fin.item() > 0)
+    if rank == 0:
+        fl = _bench.algorithmic_flops(Na, Nq, size, size)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(_bench.ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak_tf = peaks.get("bf16_tflops_sustained", 1400.0)
+        S = Na + Nq
+        line = {"metric": f"aggregator+camera-head frames/s at N={S} ({Na} anchors + {Nq} queries, {size}px), frame-sharded",
+                "value": S / (ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
+                "data": "synthetic",
+                "config": {"workload": f"scene{S}: one scene of {Na} anchors + {Nq} queries, {size}x{size}, fix_rank 300, frames "
+                                       f"sharded over {world} rank(s): frame blocks local, scene K|V all-gathered per layer, "
+                                       "global blocks with ring K/V over NCCL, camera head on gathered anchor tokens",
+                           "l2": "per-layer activations exceed the 126 MB L2; no flush needed"},
+                "e2e": {"value": S / (ms_e2e * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": host.numel() * 4 * world,
+                        "d2h_bytes_per_step": int(host_poses.numel() * 4 * world)},
+                "gpu_launches": launches, "clocks": clk,
+                "roofline": {"bound": "tensor", "kernel": "whole step", "achieved": fl["total"] / (ms * 1e-3) / 1e12,
+                             "peak": peak_tf * world, "unit": "TFLOP/s", "frac": fl["total"] / (ms * 1e-3) / 1e12 / (peak_tf * world),
+                             "traffic": None, "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops_sustained) x n_gpus"},
+                "algorithmic_tflop_per_step": fl["total"] / 1e12, "outputs_finite": finite}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()

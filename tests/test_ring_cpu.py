@@ -113,3 +113,41 @@ def test_world_one_is_plain_attention():
     out = torch.empty_like(ref)
     parallel.ring_attention(q, [kv.clone(), kv.clone()], out, plan, H, D, D ** -0.5, None, None, step_fn=_step_ref)
     assert (out - ref).abs().max() < 1e-5
+
+
+def test_scene_plan_partitions_every_frame_once():
+    """ScenePlan (frame-sharded whole scene): anchors and queries are partitioned separately; every input frame of the
+    [anchors ; queries] numbering lands on exactly one rank, anchors first."""
+    for Na, Nq, world in [(256, 256, 8), (100, 200, 8), (3, 3, 2), (5, 0, 4), (9, 2, 4)]:
+        seen = []
+        for r in range(world):
+            plan = parallel.ScenePlan.make(Na, Nq, r, world)
+            fr = plan.local_frames()
+            na = plan.anchors[r][1]
+            assert all(f < Na for f in fr[:na]) and all(f >= Na for f in fr[na:])
+            assert fr == plan.local_frames(r)
+            seen += fr
+        assert sorted(seen) == list(range(Na + Nq))
+    with pytest.raises(ValueError):
+        parallel.ScenePlan.make(3, 100, 0, 4)                    # a rank without an anchor frame
+
+
+def _gather_worker(rank, world, port, counts, errs):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        full = torch.arange(sum(counts) * 3, dtype=torch.float32).reshape(sum(counts), 3)
+        off = sum(counts[:rank])
+        dst = torch.full_like(full, float("nan"))
+        parallel._allgather_rows(dst, full[off:off + counts[rank]].clone(), counts, rank)
+        errs[rank] = float((dst - full).abs().max())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("counts", [[2, 1], [3, 0, 2]])
+def test_allgather_rows_uneven_counts(counts):
+    errs = mp.Manager().dict()
+    mp.spawn(_gather_worker, args=(len(counts), _free_port(), counts, errs), nprocs=len(counts), join=True)
+    assert len(errs) == len(counts) and max(errs.values()) == 0.0, dict(errs)
