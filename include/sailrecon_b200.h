@@ -112,6 +112,10 @@ typedef struct sr_attn {
   float* carry_m; float* carry_l; float* carry_acc;
   int32_t carry_in;      /* 1: start from the carried state instead of (-inf, 0, 0)                        */
   int32_t carry_out;     /* 1: write the state back and skip the final normalisation + out store           */
+  /* training: row-wise log-sum-exp of the scaled scores in the log2 domain, fp32 [num_heads, batch, lse_pad]
+   * (lse_pad >= q_len, a multiple of 64; the caller pre-fills the buffer with +inf so padding rows stay +inf).
+   * NULL = inference.  Consumed by sr_attn_bwd_bf16.  bf16 tensor-core path only.                           */
+  float* lse; int64_t lse_pad;
 } sr_attn_t;
 
 /* Profiling aid: with SR_ATTN_TRACE set in the environment, CTA (0,0,0) of sr_attn_fwd_bf16 records clock64() at its
@@ -121,6 +125,33 @@ int sr_debug_trace_read(long long* host_dst, int64_t count);
 
 int sr_attn_fwd_bf16(const sr_attn_t* p, void* stream);  /* tcgen05 flash attention, head_dim 64           */
 int sr_attn_fwd_f32(const sr_attn_t* p, void* stream);   /* fp32 SIMT, head_dim <= 128 (check mode, camera) */
+
+/* ---- Attention backward (training step, train_imc.py:358-380: autograd through attention.py:103-109) -----
+ * Same structured layout as sr_attn.  Inputs: q, k, v (and the prefix pk, pv) as given to the forward, the
+ * forward output `out`, its gradient `dout` (bf16, head h at columns [64h, 64h+64)), and the forward's `lse`.
+ * `delta` is workspace of the shape of lse (row-wise sum(out * dout) per head, written here first).
+ * Outputs (bf16, same row / head-column layout as their inputs; they may be column slices of one [rows, 3C]
+ * buffer): dq, dk, dv, and — when dpk != NULL — dpk, dpv [prefix_len rows] (the prefix is shared by all `batch`
+ * segments, its gradient is the sum over them).  Two tcgen05 passes: query-stationary CTAs produce dq
+ * (S and dP recomputed per K/V tile, dS kept in TMEM as the A operand of dq += dS K), key-stationary CTAs
+ * produce dk, dv (S^T, dP^T in TMEM; dv += P^T dO, dk += dS^T Q).  No atomics: results are deterministic.   */
+typedef struct sr_attn_bwd {
+  const void* q;  int64_t ldq;
+  const void* k;  const void* v;  int64_t ldkv;
+  const void* pk; const void* pv; int64_t ldp; int64_t prefix_len;
+  const void* out;  int64_t ldo;
+  const void* dout; int64_t lddo;
+  const float* lse; float* delta; int64_t lse_pad;
+  void* dq;  int64_t lddq;
+  void* dk;  void* dv;  int64_t lddkv;
+  void* dpk; void* dpv; int64_t lddp;
+  int32_t num_heads, head_dim;
+  int32_t batch;
+  int64_t q_len, q_batch_stride;
+  int64_t kv_len, kv_batch_stride;
+  float scale;
+} sr_attn_bwd_t;
+int sr_attn_bwd_bf16(const sr_attn_bwd_t* p, void* stream);
 
 /* ---- token re-layout (aggregator.py:355-357,393-399,406-423,603-625) ----------------------------------- */
 /* dst[i, :] = src[idx[i], :] for i < n; fp32 rows of C elements; idx int32 (scene-token selection).       */

@@ -41,6 +41,26 @@ class SrAttn(C.Structure):
         ("q_len", _i64), ("q_batch_stride", _i64), ("kv_len", _i64), ("kv_batch_stride", _i64),
         ("scale", _f32),
         ("carry_m", _vp), ("carry_l", _vp), ("carry_acc", _vp), ("carry_in", _i32), ("carry_out", _i32),
+        ("lse", _vp), ("lse_pad", _i64),
+    ]
+
+
+class SrAttnBwd(C.Structure):
+    """struct sr_attn_bwd (include/sailrecon_b200.h)."""
+
+    _fields_ = [
+        ("q", _vp), ("ldq", _i64),
+        ("k", _vp), ("v", _vp), ("ldkv", _i64),
+        ("pk", _vp), ("pv", _vp), ("ldp", _i64), ("prefix_len", _i64),
+        ("out", _vp), ("ldo", _i64),
+        ("dout", _vp), ("lddo", _i64),
+        ("lse", _vp), ("delta", _vp), ("lse_pad", _i64),
+        ("dq", _vp), ("lddq", _i64),
+        ("dk", _vp), ("dv", _vp), ("lddkv", _i64),
+        ("dpk", _vp), ("dpv", _vp), ("lddp", _i64),
+        ("num_heads", _i32), ("head_dim", _i32), ("batch", _i32),
+        ("q_len", _i64), ("q_batch_stride", _i64), ("kv_len", _i64), ("kv_batch_stride", _i64),
+        ("scale", _f32),
     ]
 
 
@@ -57,6 +77,7 @@ SIGNATURES = {
     "sr_debug_trace_read": (C.c_int, [C.POINTER(C.c_longlong), _i64]),
     "sr_attn_fwd_bf16": (C.c_int, [C.POINTER(SrAttn), _vp]),
     "sr_attn_fwd_f32": (C.c_int, [C.POINTER(SrAttn), _vp]),
+    "sr_attn_bwd_bf16": (C.c_int, [C.POINTER(SrAttnBwd), _vp]),
     "sr_gather_rows_f32": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _vp]),
     "sr_copy_cols_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp]),
     "sr_cast_f32_to_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _vp]),

@@ -508,6 +508,10 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
     // polynomial exp2 on the FMA pipe for 2 of every 8 pairs: measured best (0: 851, 1: 905, 2: 921, 3: 892, 4: 843 TF/s)
     int poly = 2;
     if (const char* env = getenv("SR_ATTN_POLY")) poly = atoi(env);
+    if (a->lse != nullptr) {
+      SR_REQUIRE(a->lse_pad >= a->q_len && a->lse_pad % 64 == 0, "sr_attn_fwd_bf16: lse_pad must be a multiple of 64 >= q_len");
+      SR_REQUIRE(variant == 3 || variant == 4, "sr_attn_fwd_bf16: the two-tile kernel (SR_ATTN_KERNEL=2) does not write lse");
+    }
     if (variant == 4) return attn_tc4_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
     if (variant == 3) return attn_tc3_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
   }

@@ -46,6 +46,8 @@ struct Attn3Params {
   int n_prefix_tiles, n_own_tiles;   // 64-row tiles
   int64_t total_q_rows;
   float scale_log2;
+  float* lse;                        // training: [num_heads, batch, lse_pad] log2-domain log-sum-exp (nullptr = off)
+  int lse_pad;
 };
 
 template <int kPoly>
@@ -346,6 +348,8 @@ attn_tc3_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
           }
         }
       }
+      if (row_ok && p.lse != nullptr)
+        p.lse[(static_cast<int64_t>(head) * gridDim.z + b) * p.lse_pad + q_row] = m + log2f(l);
       if (row_ok && p.carry_out) {
         p.carry_m[static_cast<int64_t>(head) * p.total_q_rows + g_row] = m;
         p.carry_l[static_cast<int64_t>(head) * p.total_q_rows + g_row] = l;
@@ -423,6 +427,8 @@ int attn_tc3_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
   p.n_own_tiles = (p.kv_len + 63) / 64;
   p.total_q_rows = a->batch > 1 ? static_cast<int64_t>(a->batch - 1) * a->q_batch_stride + a->q_len : a->q_len;
   p.scale_log2 = a->scale * 1.4426950408889634f;
+  p.lse = a->lse;
+  p.lse_pad = static_cast<int>(a->lse_pad);
   dim3 grid(static_cast<unsigned>((a->q_len + 128 * k3NQ - 1) / (128 * k3NQ)), static_cast<unsigned>(a->num_heads),
             static_cast<unsigned>(a->batch));
   switch (poly) {
