@@ -184,7 +184,8 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: to
 def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[torch.Tensor], num_heads: int,
               head_dim: int, batch: int, q_len: int, kv_len: int, q_batch_stride: int = 0, kv_batch_stride: int = 0,
               prefix_k: Optional[torch.Tensor] = None, prefix_v: Optional[torch.Tensor] = None, prefix_len: int = 0,
-              scale: Optional[float] = None, carry=None, carry_in: bool = False, carry_out: bool = False):
+              scale: Optional[float] = None, carry=None, carry_in: bool = False, carry_out: bool = False,
+              lse: Optional[torch.Tensor] = None):
     """Structured attention (see sr_attn in the header).  q/k/v are 2-D row views [rows, >= heads*head_dim]
     (column slices of the fused qkv buffer are fine); bf16 -> tcgen05 flash kernel, fp32 -> SIMT kernel."""
     dt = q.dtype
@@ -216,6 +217,11 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[t
         m, l, acc = carry
         a.carry_m, a.carry_l, a.carry_acc = m.data_ptr(), l.data_ptr(), acc.data_ptr()
     a.carry_in, a.carry_out = int(carry_in), int(carry_out)
+    if lse is not None:                                     # training: see new_lse()
+        if dt != torch.bfloat16 or lse.dtype != torch.float32 or not lse.is_contiguous() or lse.dim() != 3 \
+                or lse.shape[0] != num_heads or lse.shape[1] != batch or lse.shape[2] % 64 or lse.shape[2] < q_len:
+            raise ValueError("sailrecon_b200: lse must be contiguous fp32 [num_heads, batch, q_pad] (bf16 attention only)")
+        a.lse, a.lse_pad = lse.data_ptr(), lse.shape[2]
     lib = _lib.load()
     fn = lib.sr_attn_fwd_bf16 if dt == torch.bfloat16 else lib.sr_attn_fwd_f32
     hd = num_heads * head_dim
@@ -224,6 +230,61 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[t
     _lib.check(fn(C.byref(a), _stream()), "attention")
     t.done()
     return out
+
+
+def new_lse(num_heads: int, batch: int, q_len: int, device) -> torch.Tensor:
+    """Row log-sum-exp buffer of attention(..., lse=) / attention_bwd: [num_heads, batch, q_len rounded up to 64], +inf."""
+    return torch.full((num_heads, batch, (q_len + 63) // 64 * 64), float("inf"), dtype=torch.float32, device=device)
+
+
+def attention_bwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.Tensor, dout: torch.Tensor, lse: torch.Tensor,
+                  dq: torch.Tensor, dk: torch.Tensor, dv: torch.Tensor, num_heads: int, head_dim: int, batch: int, q_len: int,
+                  kv_len: int, q_batch_stride: int = 0, kv_batch_stride: int = 0, prefix_k: Optional[torch.Tensor] = None,
+                  prefix_v: Optional[torch.Tensor] = None, prefix_len: int = 0, dprefix_k: Optional[torch.Tensor] = None,
+                  dprefix_v: Optional[torch.Tensor] = None, scale: Optional[float] = None) -> None:
+    """Gradient of attention() (sr_attn_bwd in the header): all tensors bf16 2-D row views, lse from the forward."""
+    bf = torch.bfloat16
+    for name, t in (("q", q), ("k", k), ("v", v), ("out", out), ("dout", dout), ("dq", dq), ("dk", dk), ("dv", dv)):
+        _rows2d(t, bf, name)
+    if k.stride(0) != v.stride(0) or dk.stride(0) != dv.stride(0):
+        raise ValueError("sailrecon_b200: k/v and dk/dv must share a row stride")
+    a = _lib.SrAttnBwd()
+    a.q, a.ldq = q.data_ptr(), q.stride(0)
+    a.k, a.v, a.ldkv = k.data_ptr(), v.data_ptr(), k.stride(0)
+    a.out, a.ldo = out.data_ptr(), out.stride(0)
+    a.dout, a.lddo = dout.data_ptr(), dout.stride(0)
+    a.dq, a.lddq = dq.data_ptr(), dq.stride(0)
+    a.dk, a.dv, a.lddkv = dk.data_ptr(), dv.data_ptr(), dk.stride(0)
+    if prefix_k is not None and prefix_len > 0:
+        _rows2d(prefix_k, bf, "prefix_k")
+        _rows2d(prefix_v, bf, "prefix_v")
+        if prefix_k.stride(0) != prefix_v.stride(0) or prefix_k.shape[0] < prefix_len:
+            raise ValueError("sailrecon_b200: bad prefix K/V")
+        a.pk, a.pv, a.ldp, a.prefix_len = prefix_k.data_ptr(), prefix_v.data_ptr(), prefix_k.stride(0), prefix_len
+        if dprefix_k is not None:
+            _rows2d(dprefix_k, bf, "dprefix_k")
+            _rows2d(dprefix_v, bf, "dprefix_v")
+            if dprefix_k.stride(0) != dprefix_v.stride(0) or dprefix_k.shape[0] < prefix_len:
+                raise ValueError("sailrecon_b200: bad prefix gradient buffers")
+            a.dpk, a.dpv, a.lddp = dprefix_k.data_ptr(), dprefix_v.data_ptr(), dprefix_k.stride(0)
+    a.num_heads, a.head_dim, a.batch = num_heads, head_dim, batch
+    a.q_len, a.q_batch_stride = q_len, q_batch_stride or q_len
+    a.kv_len, a.kv_batch_stride = kv_len, kv_batch_stride or kv_len
+    need_q = (batch - 1) * a.q_batch_stride + q_len
+    need_kv = (batch - 1) * a.kv_batch_stride + kv_len
+    if min(q.shape[0], out.shape[0], dout.shape[0], dq.shape[0]) < need_q or min(k.shape[0], v.shape[0], dk.shape[0], dv.shape[0]) < need_kv:
+        raise ValueError("sailrecon_b200: attention row ranges exceed the tensors")
+    if lse.dtype != torch.float32 or not lse.is_contiguous() or tuple(lse.shape[:2]) != (num_heads, batch) or lse.shape[2] % 64 \
+            or lse.shape[2] < q_len:
+        raise ValueError("sailrecon_b200: lse must be the contiguous fp32 [num_heads, batch, q_pad] buffer of the forward")
+    delta = torch.empty_like(lse)
+    a.lse, a.delta, a.lse_pad = lse.data_ptr(), delta.data_ptr(), lse.shape[2]
+    a.scale = float(scale if scale is not None else head_dim ** -0.5)
+    hd = num_heads * head_dim
+    t = _Timed("attn_bwd", 10.0 * batch * q_len * (prefix_len + kv_len) * hd,
+               (4 * batch * q_len + 4 * batch * kv_len + 4 * prefix_len) * hd * 2)
+    _lib.check(_lib.load().sr_attn_bwd_bf16(C.byref(a), _stream()), "attention_bwd")
+    t.done()
 
 
 # ------------------------------------------------------------------------------------------------ re-layout

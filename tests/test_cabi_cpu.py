@@ -28,12 +28,24 @@ def test_header_symbols_exported_and_bound():
     assert lib.sr_version() >= 100
 
 
-def test_struct_layouts_match_header():
+def test_struct_layouts_match_header(tmp_path):
+    """ctypes mirrors of the C-ABI structs against what gcc computes from include/sailrecon_b200.h (LP64)."""
+    import subprocess
     from sailrecon_b200 import _lib
-    # sizes / offsets printed by a C program including include/sailrecon_b200.h (gcc, LP64)
-    assert ctypes.sizeof(_lib.SrEpilogue) == 152
-    assert ctypes.sizeof(_lib.SrAttn) == 176
-    assert _lib.SrEpilogue.pos.offset == 144 and _lib.SrAttn.carry_in.offset == 168
+    hdr = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "sailrecon_b200.h")
+    src = tmp_path / "layout.c"
+    src.write_text(
+        '#include <stdio.h>\n#include <stddef.h>\n#include "%s"\n'
+        'int main(void) { printf("%%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu\\n", sizeof(sr_epilogue_t), offsetof(sr_epilogue_t, pos), '
+        'sizeof(sr_attn_t), offsetof(sr_attn_t, carry_in), offsetof(sr_attn_t, lse_pad), sizeof(sr_attn_bwd_t), '
+        'offsetof(sr_attn_bwd_t, num_heads), offsetof(sr_attn_bwd_t, scale)); return 0; }\n' % hdr)
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-o", str(exe), str(src)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
+    assert got == [ctypes.sizeof(_lib.SrEpilogue), _lib.SrEpilogue.pos.offset, ctypes.sizeof(_lib.SrAttn), _lib.SrAttn.carry_in.offset,
+                   _lib.SrAttn.lse_pad.offset, ctypes.sizeof(_lib.SrAttnBwd), _lib.SrAttnBwd.num_heads.offset,
+                   _lib.SrAttnBwd.scale.offset]
+    assert ctypes.sizeof(_lib.SrEpilogue) == 152 and _lib.SrAttn.carry_in.offset == 168
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
