@@ -153,6 +153,35 @@ typedef struct sr_attn_bwd {
 } sr_attn_bwd_t;
 int sr_attn_bwd_bf16(const sr_attn_bwd_t* p, void* stream);
 
+/* ---- Training-step row kernels (autograd of block.py:86-112; csrc/train_rows.cu) -------------------------
+ * The Linear gradients run on sr_gemm_bf16 itself: dX = dY W is sr_gemm_bf16(dY, W^T), dW = dY^T X is
+ * sr_gemm_bf16(dY^T, X^T) with fp32 output; sr_transpose_bf16 makes the transposed bf16 operands
+ * (dst [C, ldd >= R_pad], columns [R, R_pad) zero-filled so that the contraction length is a multiple of 64).  */
+int sr_transpose_bf16(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t R, int64_t C, int64_t R_pad, void* stream);
+/* out[c] (+)= sum_r a[r,c] * b[r,c]   (a fp32 or bf16, b bf16 or NULL = 1): bias and LayerScale gamma gradients */
+int sr_colsum(const void* a, int a_bf16, int64_t lda, const void* b, int64_t ldb, float* out, int64_t R, int64_t C,
+              int accumulate, void* stream);
+/* out = bf16(x * gamma[c]): gradient entering the Linear under a LayerScale (layer_scale.py:22)               */
+int sr_scale_cast_bf16(const float* x, int64_t ldx, const float* gamma, void* out, int64_t ldo, int64_t rows, int64_t C,
+                       void* stream);
+/* out = resid + gamma * z (z bf16 = the Linear's rounded output, kept for d gamma); contiguous [rows, C]       */
+int sr_ls_residual_f32(const float* resid, const void* z, const float* gamma, float* out, int64_t rows, int64_t C, void* stream);
+/* mlp.py:36 on the saved pre-activation u (bf16): g = gelu_erf(u);  du = dg * gelu'(u)                         */
+int sr_gelu_fwd_bf16(const void* u, void* out, int64_t n, void* stream);
+int sr_gelu_bwd_bf16(const void* u, const void* dg, void* du, int64_t n, void* stream);
+/* LayerNorm gradient (block.py norm1 / norm2, C = 1024): dx += dLN(dy) (dx fp32 holds the residual-path gradient
+ * already), dweight / dbias (fp32 [C], accumulated with atomics; NULL = skip).  x fp32, dy bf16.                */
+int sr_layernorm_bwd(const float* x, int64_t ldx, const float* weight, const void* dy, int64_t lddy, float* dx, int64_t lddx,
+                     float* dweight, float* dbias, int64_t rows, int64_t C, float eps, void* stream);
+/* attention.py:78-82 on a saved raw qkv buffer (bf16 [M, 3C], the qkv Linear's rounded output): per-head
+ * LayerNorm(64) + 2D RoPE on q and k, v copied — the un-fused form of SR_EPI_QKV (fields qkv_dim, head_dim,
+ * qk_norm, q/k norm parameters, qk_eps, rope tables, pos of `qkv` are read).  _bwd turns the gradient w.r.t. the
+ * normalised / rotated q, k (in place in dqkv; the v third is left as is) into the gradient w.r.t. raw and
+ * accumulates the q_norm / k_norm parameter gradients (fp32 [64] each, NULL = skip).                             */
+int sr_qknorm_rope_fwd(const void* raw, int64_t ldr, void* out, int64_t ldo, const sr_epilogue_t* qkv, int64_t M, void* stream);
+int sr_qknorm_rope_bwd(const void* raw, int64_t ldr, void* dqkv, int64_t ldd, const sr_epilogue_t* qkv, float* dqn_w,
+                       float* dqn_b, float* dkn_w, float* dkn_b, int64_t M, void* stream);
+
 /* ---- token re-layout (aggregator.py:355-357,393-399,406-423,603-625) ----------------------------------- */
 /* dst[i, :] = src[idx[i], :] for i < n; fp32 rows of C elements; idx int32 (scene-token selection).       */
 int sr_gather_rows_f32(const float* src, int64_t lds, const int32_t* idx, float* dst, int64_t ldd, int64_t n,

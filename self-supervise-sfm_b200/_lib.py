@@ -78,6 +78,15 @@ SIGNATURES = {
     "sr_attn_fwd_bf16": (C.c_int, [C.POINTER(SrAttn), _vp]),
     "sr_attn_fwd_f32": (C.c_int, [C.POINTER(SrAttn), _vp]),
     "sr_attn_bwd_bf16": (C.c_int, [C.POINTER(SrAttnBwd), _vp]),
+    "sr_transpose_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp]),
+    "sr_colsum": (C.c_int, [_vp, C.c_int, _i64, _vp, _i64, _vp, _i64, _i64, C.c_int, _vp]),
+    "sr_scale_cast_bf16": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _vp]),
+    "sr_ls_residual_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _vp]),
+    "sr_gelu_fwd_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
+    "sr_gelu_bwd_bf16": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
+    "sr_layernorm_bwd": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _f32, _vp]),
+    "sr_qknorm_rope_fwd": (C.c_int, [_vp, _i64, _vp, _i64, C.POINTER(SrEpilogue), _i64, _vp]),
+    "sr_qknorm_rope_bwd": (C.c_int, [_vp, _i64, _vp, _i64, C.POINTER(SrEpilogue), _vp, _vp, _vp, _vp, _i64, _vp]),
     "sr_gather_rows_f32": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _vp]),
     "sr_copy_cols_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp]),
     "sr_cast_f32_to_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _vp]),

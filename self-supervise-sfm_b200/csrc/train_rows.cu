@@ -1,0 +1,424 @@
+// HBM-bound row kernels of the TRAINING step (forward with saved intermediates + backward of one Block,
+// sailrecon/layers/block.py:86-112 under torch.utils.checkpoint as in models/aggregator.py:654-657,726-729,758-761):
+//   sr_transpose_bf16      [R, C] -> [C, R_pad]  (operands of the dgrad / wgrad GEMMs, which run on sr_gemm_bf16)
+//   sr_colsum              out[c] += sum_r a[r, c] * b[r, c]            (bias and LayerScale-gamma gradients)
+//   sr_scale_cast_bf16     out = bf16(x * gamma)                         (gradient entering a LayerScale'd Linear)
+//   sr_ls_residual_f32     out = resid + gamma * z                       (block.py:110-111 with z kept for d gamma)
+//   sr_gelu_fwd / _bwd     g = gelu_erf(u);  du = dg * gelu'(u)          (mlp.py:36)
+//   sr_layernorm_bwd       dx += LN'(dy), dw += ..., db += ...           (block.py:87-91 norm1 / norm2)
+//   sr_qknorm_rope_fwd/bwd per-head LayerNorm(64) + 2D RoPE on the q, k thirds of a [M, 3C] bf16 buffer
+//                          (attention.py:78-82) and its gradient, in place
+#include "common.cuh"
+#include "sr_internal.h"
+
+namespace sr {
+extern int g_launch_count;
+
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+
+// ------------------------------------------------------------------------------------------------ transpose
+// 64 x 64 tiles through shared memory; reads and writes are 128-byte rows of bf16.
+__global__ void __launch_bounds__(256)
+transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, int64_t lds, __nv_bfloat16* __restrict__ dst, int64_t ldd,
+                      int R, int C, int R_pad) {
+  __shared__ __nv_bfloat16 tile[64][66];
+  const int r0 = blockIdx.x * 64, c0 = blockIdx.y * 64;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;          // 64 x 4
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int r = r0 + ty + 4 * i, c = c0 + tx;
+    tile[ty + 4 * i][tx] = (r < R && c < C) ? src[static_cast<int64_t>(r) * lds + c] : __float2bfloat16(0.f);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const int c = c0 + ty + 4 * i, r = r0 + tx;
+    if (c < C && r < R_pad) dst[static_cast<int64_t>(c) * ldd + r] = tile[tx][ty + 4 * i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ column sums
+// One thread per column, 128 columns x 128 rows per block, atomics into out (zeroed by the launcher unless accumulate).
+template <bool A_BF16>
+__global__ void __launch_bounds__(128)
+colsum_kernel(const void* __restrict__ a_, int64_t lda, const __nv_bfloat16* __restrict__ b, int64_t ldb, float* __restrict__ out,
+              int R, int C) {
+  const int c = blockIdx.x * 128 + threadIdx.x;
+  if (c >= C) return;
+  const int r0 = blockIdx.y * 128, r1 = min(R, r0 + 128);
+  float acc = 0.f;
+  for (int r = r0; r < r1; ++r) {
+    const float av = A_BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(a_)[static_cast<int64_t>(r) * lda + c])
+                            : reinterpret_cast<const float*>(a_)[static_cast<int64_t>(r) * lda + c];
+    acc += b ? av * __bfloat162float(b[static_cast<int64_t>(r) * ldb + c]) : av;
+  }
+  atomicAdd(out + c, acc);
+}
+
+// ------------------------------------------------------------------------------------------------ elementwise
+__global__ void __launch_bounds__(256)
+scale_cast_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ gamma, __nv_bfloat16* __restrict__ out,
+                  int64_t ldo, int64_t rows, int C) {
+  const int64_t e = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+  if (e >= rows * C) return;
+  const int64_t r = e / C;
+  const int c = static_cast<int>(e % C);
+  const float4 v = *reinterpret_cast<const float4*>(x + r * ldx + c);
+  const float4 g = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+  uint2 w;
+  w.x = pack_bf16x2(v.x * g.x, v.y * g.y);
+  w.y = pack_bf16x2(v.z * g.z, v.w * g.w);
+  *reinterpret_cast<uint2*>(out + r * ldo + c) = w;
+}
+
+__global__ void __launch_bounds__(256)
+ls_residual_kernel(const float* __restrict__ resid, const __nv_bfloat16* __restrict__ z, const float* __restrict__ gamma,
+                   float* __restrict__ out, int64_t rows, int C) {
+  const int64_t e = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+  if (e >= rows * C) return;
+  const int c = static_cast<int>(e % C);
+  const float4 r = *reinterpret_cast<const float4*>(resid + e);
+  const uint2 zz = *reinterpret_cast<const uint2*>(z + e);
+  const float4 g = gamma ? __ldg(reinterpret_cast<const float4*>(gamma + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+  float4 y;
+  y.x = r.x + g.x * bf16_lo(zz.x);
+  y.y = r.y + g.y * bf16_hi(zz.x);
+  y.z = r.z + g.z * bf16_lo(zz.y);
+  y.w = r.w + g.w * bf16_hi(zz.y);
+  *reinterpret_cast<float4*>(out + e) = y;
+}
+
+// mode 0: out = bf16(gelu_erf(u));  mode 1: out = bf16(dg * gelu'(u)),  gelu'(u) = Phi(u) + u * phi(u)
+template <int kMode>
+__global__ void __launch_bounds__(256)
+gelu_kernel(const __nv_bfloat16* __restrict__ u, const __nv_bfloat16* __restrict__ dg, __nv_bfloat16* __restrict__ out, int64_t n) {
+  const int64_t e = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 8;
+  if (e >= n) return;
+  const uint4 uu = *reinterpret_cast<const uint4*>(u + e);
+  uint4 gg = make_uint4(0, 0, 0, 0);
+  if (kMode == 1) gg = *reinterpret_cast<const uint4*>(dg + e);
+  const uint32_t uw[4] = {uu.x, uu.y, uu.z, uu.w}, gw[4] = {gg.x, gg.y, gg.z, gg.w};
+  uint32_t ow[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float r[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const float x = h ? bf16_hi(uw[i]) : bf16_lo(uw[i]);
+      if (kMode == 0) {
+        r[h] = gelu_erf(x);
+      } else {
+        const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
+        const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
+        r[h] = (h ? bf16_hi(gw[i]) : bf16_lo(gw[i])) * (cdf + x * pdf);
+      }
+    }
+    ow[i] = pack_bf16x2(r[0], r[1]);
+  }
+  *reinterpret_cast<uint4*>(out + e) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+}
+
+// ------------------------------------------------------------------------------------------------ LayerNorm backward
+// One warp per row, lane holds columns {128 i + 4 lane .. +3}, i < NCH (C = 128 NCH).  dx += rstd * (g - mean(g) -
+// xhat * mean(g * xhat)) with g = dy * w; per-block partial dw / db reduced through shared memory, then atomics.
+template <int NCH>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, const __nv_bfloat16* __restrict__ dy,
+                     int64_t lddy, float* __restrict__ dx, int64_t lddx, float* __restrict__ dw, float* __restrict__ db, int rows,
+                     int rows_per_block, float eps) {
+  constexpr int C = NCH * 128;
+  __shared__ float red[8][C];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float pw[NCH * 4], pb[NCH * 4];
+#pragma unroll
+  for (int i = 0; i < NCH * 4; ++i) pw[i] = pb[i] = 0.f;
+  const int r_begin = blockIdx.x * rows_per_block, r_end = min(rows, r_begin + rows_per_block);
+  for (int r = r_begin + warp; r < r_end; r += 8) {
+    float xv[NCH * 4], gv[NCH * 4];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const float4 v = *reinterpret_cast<const float4*>(x + static_cast<int64_t>(r) * ldx + i * 128 + lane * 4);
+      xv[4 * i] = v.x; xv[4 * i + 1] = v.y; xv[4 * i + 2] = v.z; xv[4 * i + 3] = v.w;
+      s += v.x + v.y + v.z + v.w;
+    }
+    const float mean = warp_sum(s) * (1.0f / C);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH * 4; ++i) { xv[i] -= mean; q += xv[i] * xv[i]; }
+    const float rstd = rsqrtf(warp_sum(q) * (1.0f / C) + eps);
+    float sg = 0.f, sgx = 0.f;
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      const uint2 d = *reinterpret_cast<const uint2*>(dy + static_cast<int64_t>(r) * lddy + i * 128 + lane * 4);
+      const float4 wv = w ? __ldg(reinterpret_cast<const float4*>(w + i * 128 + lane * 4)) : make_float4(1.f, 1.f, 1.f, 1.f);
+      const float dyv[4] = {bf16_lo(d.x), bf16_hi(d.x), bf16_lo(d.y), bf16_hi(d.y)};
+      const float wq[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const float xh = xv[4 * i + u] * rstd;
+        xv[4 * i + u] = xh;
+        pw[4 * i + u] += dyv[u] * xh;
+        pb[4 * i + u] += dyv[u];
+        const float g = dyv[u] * wq[u];
+        gv[4 * i + u] = g;
+        sg += g;
+        sgx += g * xh;
+      }
+    }
+    const float mg = warp_sum(sg) * (1.0f / C), mgx = warp_sum(sgx) * (1.0f / C);
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) {
+      float* o = dx + static_cast<int64_t>(r) * lddx + i * 128 + lane * 4;
+      float4 v = *reinterpret_cast<float4*>(o);
+      v.x += rstd * (gv[4 * i] - mg - xv[4 * i] * mgx);
+      v.y += rstd * (gv[4 * i + 1] - mg - xv[4 * i + 1] * mgx);
+      v.z += rstd * (gv[4 * i + 2] - mg - xv[4 * i + 2] * mgx);
+      v.w += rstd * (gv[4 * i + 3] - mg - xv[4 * i + 3] * mgx);
+      *reinterpret_cast<float4*>(o) = v;
+    }
+  }
+  // block reduction of the dw / db partials (two passes through the same buffer)
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass) {
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NCH; ++i)
+#pragma unroll
+      for (int u = 0; u < 4; ++u) red[warp][i * 128 + lane * 4 + u] = pass == 0 ? pw[4 * i + u] : pb[4 * i + u];
+    __syncthreads();
+    float* dst = pass == 0 ? dw : db;
+    if (dst != nullptr) {
+      for (int c = threadIdx.x; c < C; c += 256) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) t += red[k][c];
+        atomicAdd(dst + c, t);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ QK-norm + RoPE
+// One warp per (row, head): lane holds features `lane` (y half) and `lane + 32` (x half); the rotate-half partner of
+// feature j inside a half is j ^ 16 -> one shuffle.  blockIdx.x = head slot in [0, 3H): q heads, k heads, v heads.
+struct QkRopeParams {
+  const float* qn_w; const float* qn_b; const float* kn_w; const float* kn_b;
+  float eps;
+  int qk_norm, rope;
+  const float* rope_cos; const float* rope_sin;     // [max_pos, 16]
+  const int32_t* pos;                                // [M, 2] (y, x)
+  int H;
+  int64_t M;
+  int rows_per_warp;
+};
+
+template <bool BWD>
+__global__ void __launch_bounds__(256)
+qknorm_rope_kernel(const __nv_bfloat16* __restrict__ raw, int64_t ldr, __nv_bfloat16* __restrict__ io, int64_t ldio,
+                   float* __restrict__ dqn_w, float* __restrict__ dqn_b, float* __restrict__ dkn_w, float* __restrict__ dkn_b,
+                   const QkRopeParams p) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slot = blockIdx.x;                        // head slot
+  const int which = slot / p.H;                       // 0 q, 1 k, 2 v
+  const int col = slot * 64;
+  const int64_t r_begin = (static_cast<int64_t>(blockIdx.y) * 8 + warp) * p.rows_per_warp;
+  const int64_t r_end = min(p.M, r_begin + p.rows_per_warp);
+  if (which == 2) {
+    if (!BWD) {
+      for (int64_t r = r_begin; r < r_end; ++r) {
+        io[r * ldio + col + lane] = raw[r * ldr + col + lane];
+        io[r * ldio + col + 32 + lane] = raw[r * ldr + col + 32 + lane];
+      }
+    }
+    return;
+  }
+  const float* nw = which == 0 ? p.qn_w : p.kn_w;
+  const float* nb = which == 0 ? p.qn_b : p.kn_b;
+  float w0 = 1.f, w1 = 1.f, b0 = 0.f, b1 = 0.f;
+  if (p.qk_norm) { w0 = nw[lane]; w1 = nw[lane + 32]; b0 = nb[lane]; b1 = nb[lane + 32]; }
+  float aw0 = 0.f, aw1 = 0.f, ab0 = 0.f, ab1 = 0.f;
+  const int f = lane & 15;
+  const bool is_a = lane < 16;                        // first member of the (i, i + 16) pair
+  for (int64_t r = r_begin; r < r_end; ++r) {
+    float x0 = __bfloat162float(raw[r * ldr + col + lane]);
+    float x1 = __bfloat162float(raw[r * ldr + col + 32 + lane]);
+    float rstd = 1.f;
+    if (p.qk_norm) {
+      const float mean = warp_sum(x0 + x1) * (1.0f / 64.0f);
+      x0 -= mean; x1 -= mean;
+      rstd = rsqrtf(warp_sum(x0 * x0 + x1 * x1) * (1.0f / 64.0f) + p.eps);
+      x0 *= rstd; x1 *= rstd;                         // xhat
+    }
+    float c0 = 1.f, s0 = 0.f, c1 = 1.f, s1 = 0.f;
+    if (p.rope) {
+      const int2 yx = __ldg(reinterpret_cast<const int2*>(p.pos) + r);
+      c0 = __ldg(p.rope_cos + static_cast<int64_t>(yx.x) * 16 + f); s0 = __ldg(p.rope_sin + static_cast<int64_t>(yx.x) * 16 + f);
+      c1 = __ldg(p.rope_cos + static_cast<int64_t>(yx.y) * 16 + f); s1 = __ldg(p.rope_sin + static_cast<int64_t>(yx.y) * 16 + f);
+    }
+    if (!BWD) {
+      float y0 = p.qk_norm ? x0 * w0 + b0 : x0, y1 = p.qk_norm ? x1 * w1 + b1 : x1;
+      const float o0 = __shfl_xor_sync(0xffffffffu, y0, 16), o1 = __shfl_xor_sync(0xffffffffu, y1, 16);
+      // pair (a, b) = (i, i + 16): a' = a c - b s ; b' = b c + a s
+      y0 = is_a ? y0 * c0 - o0 * s0 : y0 * c0 + o0 * s0;
+      y1 = is_a ? y1 * c1 - o1 * s1 : y1 * c1 + o1 * s1;
+      io[r * ldio + col + lane] = __float2bfloat16_rn(y0);
+      io[r * ldio + col + 32 + lane] = __float2bfloat16_rn(y1);
+    } else {
+      float d0 = __bfloat162float(io[r * ldio + col + lane]);
+      float d1 = __bfloat162float(io[r * ldio + col + 32 + lane]);
+      const float o0 = __shfl_xor_sync(0xffffffffu, d0, 16), o1 = __shfl_xor_sync(0xffffffffu, d1, 16);
+      // da = da' c + db' s ; db = db' c - da' s
+      d0 = is_a ? d0 * c0 + o0 * s0 : d0 * c0 - o0 * s0;
+      d1 = is_a ? d1 * c1 + o1 * s1 : d1 * c1 - o1 * s1;
+      if (p.qk_norm) {
+        aw0 += d0 * x0; aw1 += d1 * x1; ab0 += d0; ab1 += d1;
+        const float g0 = d0 * w0, g1 = d1 * w1;
+        const float mg = warp_sum(g0 + g1) * (1.0f / 64.0f);
+        const float mgx = warp_sum(g0 * x0 + g1 * x1) * (1.0f / 64.0f);
+        d0 = rstd * (g0 - mg - x0 * mgx);
+        d1 = rstd * (g1 - mg - x1 * mgx);
+      }
+      io[r * ldio + col + lane] = __float2bfloat16_rn(d0);
+      io[r * ldio + col + 32 + lane] = __float2bfloat16_rn(d1);
+    }
+  }
+  if (BWD && p.qk_norm) {
+    float* gw = which == 0 ? dqn_w : dkn_w;
+    float* gb = which == 0 ? dqn_b : dkn_b;
+    if (gw) { atomicAdd(gw + lane, aw0); atomicAdd(gw + lane + 32, aw1); }
+    if (gb) { atomicAdd(gb + lane, ab0); atomicAdd(gb + lane + 32, ab1); }
+  }
+}
+
+}  // namespace sr
+
+using namespace sr;
+
+#define SR_LAUNCHED()          \
+  do {                         \
+    ++g_launch_count;          \
+    SR_CHECK_CUDA(cudaGetLastError()); \
+  } while (0)
+
+extern "C" int sr_transpose_bf16(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t R, int64_t C, int64_t R_pad,
+                                 void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(src && dst && R > 0 && C > 0 && R_pad >= R && ldd >= R_pad && lds >= C, "sr_transpose_bf16: bad shape");
+  dim3 grid(static_cast<unsigned>((R_pad + 63) / 64), static_cast<unsigned>((C + 63) / 64));
+  transpose_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(src), lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd, static_cast<int>(R),
+      static_cast<int>(C), static_cast<int>(R_pad));
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_colsum(const void* a, int a_bf16, int64_t lda, const void* b, int64_t ldb, float* out, int64_t R, int64_t C,
+                         int accumulate, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(a && out && R > 0 && C > 0, "sr_colsum: bad arguments");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (!accumulate) SR_CHECK_CUDA(cudaMemsetAsync(out, 0, static_cast<size_t>(C) * sizeof(float), st));
+  dim3 grid(static_cast<unsigned>((C + 127) / 128), static_cast<unsigned>((R + 127) / 128));
+  if (a_bf16)
+    colsum_kernel<true><<<grid, 128, 0, st>>>(a, lda, reinterpret_cast<const __nv_bfloat16*>(b), ldb, out, static_cast<int>(R),
+                                              static_cast<int>(C));
+  else
+    colsum_kernel<false><<<grid, 128, 0, st>>>(a, lda, reinterpret_cast<const __nv_bfloat16*>(b), ldb, out, static_cast<int>(R),
+                                               static_cast<int>(C));
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_scale_cast_bf16(const float* x, int64_t ldx, const float* gamma, void* out, int64_t ldo, int64_t rows, int64_t C,
+                                  void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(x && out && rows > 0 && C > 0 && C % 4 == 0 && ldx % 4 == 0 && ldo % 4 == 0, "sr_scale_cast_bf16: bad shape");
+  const int64_t n4 = rows * C / 4;
+  scale_cast_kernel<<<static_cast<unsigned>((n4 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x, ldx, gamma, reinterpret_cast<__nv_bfloat16*>(out), ldo, rows, static_cast<int>(C));
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_ls_residual_f32(const float* resid, const void* z, const float* gamma, float* out, int64_t rows, int64_t C,
+                                  void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(resid && z && out && rows > 0 && C > 0 && C % 4 == 0, "sr_ls_residual_f32: bad shape (contiguous [rows, C], C % 4 == 0)");
+  const int64_t n4 = rows * C / 4;
+  ls_residual_kernel<<<static_cast<unsigned>((n4 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      resid, reinterpret_cast<const __nv_bfloat16*>(z), gamma, out, rows, static_cast<int>(C));
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_gelu_fwd_bf16(const void* u, void* out, int64_t n, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(u && out && n > 0 && n % 8 == 0, "sr_gelu_fwd_bf16: n must be a positive multiple of 8");
+  gelu_kernel<0><<<static_cast<unsigned>((n / 8 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(u), nullptr, reinterpret_cast<__nv_bfloat16*>(out), n);
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_gelu_bwd_bf16(const void* u, const void* dg, void* du, int64_t n, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(u && dg && du && n > 0 && n % 8 == 0, "sr_gelu_bwd_bf16: n must be a positive multiple of 8");
+  gelu_kernel<1><<<static_cast<unsigned>((n / 8 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(u), reinterpret_cast<const __nv_bfloat16*>(dg), reinterpret_cast<__nv_bfloat16*>(du), n);
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_layernorm_bwd(const float* x, int64_t ldx, const float* weight, const void* dy, int64_t lddy, float* dx,
+                                int64_t lddx, float* dweight, float* dbias, int64_t rows, int64_t C, float eps, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(x && dy && dx && rows > 0, "sr_layernorm_bwd: null pointer / empty");
+  SR_REQUIRE(C == 1024, "sr_layernorm_bwd: C must be 1024 (got %lld)", static_cast<long long>(C));
+  SR_REQUIRE(ldx % 4 == 0 && lddy % 4 == 0 && lddx % 4 == 0, "sr_layernorm_bwd: row strides must be multiples of 4");
+  const int rows_per_block = 64;
+  layernorm_bwd_kernel<8><<<static_cast<unsigned>((rows + rows_per_block - 1) / rows_per_block), 256, 0,
+                            reinterpret_cast<cudaStream_t>(stream)>>>(x, ldx, weight, reinterpret_cast<const __nv_bfloat16*>(dy), lddy,
+                                                                      dx, lddx, dweight, dbias, static_cast<int>(rows),
+                                                                      rows_per_block, eps);
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+static int qk_launch(bool bwd, const void* raw, int64_t ldr, void* io, int64_t ldio, float* dqw, float* dqb, float* dkw, float* dkb,
+                     const sr_epilogue_t* e, int64_t M, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(raw && io && e && M > 0, "sr_qknorm_rope: null pointer / empty");
+  SR_REQUIRE(e->head_dim == 64 && e->qkv_dim > 0 && e->qkv_dim % 64 == 0, "sr_qknorm_rope: head_dim must be 64");
+  if (e->qk_norm) SR_REQUIRE(e->qn_w && e->qn_b && e->kn_w && e->kn_b, "sr_qknorm_rope: q/k norm parameters missing");
+  if (e->rope) SR_REQUIRE(e->rope_cos && e->rope_sin && e->pos, "sr_qknorm_rope: RoPE tables / positions missing");
+  QkRopeParams p;
+  p.qn_w = e->qn_w; p.qn_b = e->qn_b; p.kn_w = e->kn_w; p.kn_b = e->kn_b;
+  p.eps = e->qk_eps;
+  p.qk_norm = e->qk_norm; p.rope = e->rope;
+  p.rope_cos = e->rope_cos; p.rope_sin = e->rope_sin; p.pos = e->pos;
+  p.H = static_cast<int>(e->qkv_dim / 64);
+  p.M = M;
+  p.rows_per_warp = 32;
+  dim3 grid(static_cast<unsigned>(3 * p.H), static_cast<unsigned>((M + 8 * p.rows_per_warp - 1) / (8 * p.rows_per_warp)));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (bwd)
+    qknorm_rope_kernel<true><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(raw), ldr, reinterpret_cast<__nv_bfloat16*>(io),
+                                                   ldio, dqw, dqb, dkw, dkb, p);
+  else
+    qknorm_rope_kernel<false><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(raw), ldr, reinterpret_cast<__nv_bfloat16*>(io),
+                                                    ldio, nullptr, nullptr, nullptr, nullptr, p);
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_qknorm_rope_fwd(const void* raw, int64_t ldr, void* out, int64_t ldo, const sr_epilogue_t* qkv, int64_t M,
+                                  void* stream) {
+  return qk_launch(false, raw, ldr, out, ldo, nullptr, nullptr, nullptr, nullptr, qkv, M, stream);
+}
+
+extern "C" int sr_qknorm_rope_bwd(const void* raw, int64_t ldr, void* dqkv, int64_t ldd, const sr_epilogue_t* qkv, float* dqn_w,
+                                  float* dqn_b, float* dkn_w, float* dkn_b, int64_t M, void* stream) {
+  return qk_launch(true, raw, ldr, dqkv, ldd, dqn_w, dqn_b, dkn_w, dkn_b, qkv, M, stream);
+}

@@ -123,6 +123,30 @@ class QkvEpilogue:
         self.rope_cos, self.rope_sin, self.pos = rope_cos, rope_sin, pos
 
 
+def _fill_qkv(e: SrEpilogue, qkv: "QkvEpilogue", M: int) -> list:
+    """Copies the q/k LayerNorm + RoPE arguments into the C struct; returns the tensors that must stay alive."""
+    keep = []
+    e.qkv_dim, e.col_offset, e.head_dim = qkv.qkv_dim, qkv.col_offset, qkv.head_dim
+    e.qk_norm = int(qkv.q_norm is not None)
+    if qkv.q_norm is not None:
+        for t in (*qkv.q_norm, *qkv.k_norm):
+            _vec(t, qkv.head_dim, "q/k norm parameter")
+        e.qn_w, e.qn_b = qkv.q_norm[0].data_ptr(), qkv.q_norm[1].data_ptr()
+        e.kn_w, e.kn_b = qkv.k_norm[0].data_ptr(), qkv.k_norm[1].data_ptr()
+    e.qk_eps = float(qkv.qk_eps)
+    e.rope = int(qkv.rope_cos is not None)
+    if qkv.rope_cos is not None:
+        cos, sin, pos = qkv.rope_cos, qkv.rope_sin, qkv.pos
+        if not (cos.is_cuda and cos.dtype == torch.float32 and cos.is_contiguous() and cos.shape == sin.shape
+                and cos.dim() == 2 and cos.shape[1] == qkv.head_dim // 4):
+            raise ValueError("sailrecon_b200: rope tables must be fp32 [max_pos, head_dim/4]")
+        if not (pos.is_cuda and pos.dtype == torch.int32 and pos.is_contiguous() and pos.shape == (M, 2)):
+            raise ValueError("sailrecon_b200: rope positions must be int32 [M, 2]")
+        e.rope_cos, e.rope_sin, e.rope_max_pos, e.pos = cos.data_ptr(), sin.data_ptr(), cos.shape[0], pos.data_ptr()
+        keep += [cos, sin, pos]
+    return keep
+
+
 def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor, kind: int = SR_EPI_BIAS,
          gamma: Optional[torch.Tensor] = None, resid: Optional[torch.Tensor] = None,
          qkv: Optional[QkvEpilogue] = None) -> torch.Tensor:
@@ -153,24 +177,7 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: to
     if kind == SR_EPI_QKV:
         if qkv is None:
             raise ValueError("sailrecon_b200: QKV epilogue arguments missing")
-        e.qkv_dim, e.col_offset, e.head_dim = qkv.qkv_dim, qkv.col_offset, qkv.head_dim
-        e.qk_norm = int(qkv.q_norm is not None)
-        if qkv.q_norm is not None:
-            for t in (*qkv.q_norm, *qkv.k_norm):
-                _vec(t, qkv.head_dim, "q/k norm parameter")
-            e.qn_w, e.qn_b = qkv.q_norm[0].data_ptr(), qkv.q_norm[1].data_ptr()
-            e.kn_w, e.kn_b = qkv.k_norm[0].data_ptr(), qkv.k_norm[1].data_ptr()
-        e.qk_eps = float(qkv.qk_eps)
-        e.rope = int(qkv.rope_cos is not None)
-        if qkv.rope_cos is not None:
-            cos, sin, pos = qkv.rope_cos, qkv.rope_sin, qkv.pos
-            if not (cos.is_cuda and cos.dtype == torch.float32 and cos.is_contiguous() and cos.shape == sin.shape
-                    and cos.dim() == 2 and cos.shape[1] == qkv.head_dim // 4):
-                raise ValueError("sailrecon_b200: rope tables must be fp32 [max_pos, head_dim/4]")
-            if not (pos.is_cuda and pos.dtype == torch.int32 and pos.is_contiguous() and pos.shape == (M, 2)):
-                raise ValueError("sailrecon_b200: rope positions must be int32 [M, 2]")
-            e.rope_cos, e.rope_sin, e.rope_max_pos, e.pos = cos.data_ptr(), sin.data_ptr(), cos.shape[0], pos.data_ptr()
-            keep += [cos, sin, pos]
+        keep = _fill_qkv(e, qkv, M)
     lib = _lib.load()
     fn = lib.sr_gemm_bf16 if a.dtype == torch.bfloat16 else lib.sr_gemm_f32
     t = _Timed("gemm_tc" if a.dtype == torch.bfloat16 else "gemm_f32", 2.0 * M * N * K,
@@ -285,6 +292,120 @@ def attention_bwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.
                (4 * batch * q_len + 4 * batch * kv_len + 4 * prefix_len) * hd * 2)
     _lib.check(_lib.load().sr_attn_bwd_bf16(C.byref(a), _stream()), "attention_bwd")
     t.done()
+
+
+# ------------------------------------------------------------------------------------------------ training-step row kernels
+def transpose_bf16(src: torch.Tensor, r_pad: Optional[int] = None) -> torch.Tensor:
+    """[R, C] bf16 -> [C, R_pad] bf16 (R_pad = R rounded up to 64, padding zero): transposed operand of dgrad / wgrad."""
+    _rows2d(src, torch.bfloat16, "src")
+    R, Cc = src.shape
+    rp = r_pad or (R + 63) // 64 * 64
+    dst = torch.empty(Cc, rp, dtype=torch.bfloat16, device=src.device)
+    _lib.check(_lib.load().sr_transpose_bf16(src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0), R, Cc, rp, _stream()),
+               "transpose_bf16")
+    return dst
+
+
+def colsum(a: torch.Tensor, b: Optional[torch.Tensor], out: torch.Tensor, accumulate: bool = False) -> torch.Tensor:
+    """out[c] (+)= sum_r a[r, c] * b[r, c] (b None = 1)."""
+    if a.dtype not in (torch.float32, torch.bfloat16):
+        raise TypeError("sailrecon_b200: colsum input must be fp32 or bf16")
+    _rows2d(a, a.dtype, "a")
+    if b is not None:
+        _rows2d(b, torch.bfloat16, "b")
+        if b.shape != a.shape:
+            raise ValueError("sailrecon_b200: colsum shape mismatch")
+    _vec(out, a.shape[1], "out")
+    _lib.check(_lib.load().sr_colsum(a.data_ptr(), int(a.dtype == torch.bfloat16), a.stride(0), _ptr(b), 0 if b is None else b.stride(0),
+                                     out.data_ptr(), a.shape[0], a.shape[1], int(accumulate), _stream()), "colsum")
+    return out
+
+
+def scale_cast_bf16(x: torch.Tensor, gamma: Optional[torch.Tensor], out: torch.Tensor) -> torch.Tensor:
+    _rows2d(x, torch.float32, "x")
+    _rows2d(out, torch.bfloat16, "out")
+    _vec(gamma, x.shape[1], "gamma")
+    if out.shape != x.shape:
+        raise ValueError("sailrecon_b200: scale_cast shape mismatch")
+    _lib.check(_lib.load().sr_scale_cast_bf16(x.data_ptr(), x.stride(0), _ptr(gamma), out.data_ptr(), out.stride(0), x.shape[0],
+                                              x.shape[1], _stream()), "scale_cast_bf16")
+    return out
+
+
+def ls_residual(resid: torch.Tensor, z: torch.Tensor, gamma: Optional[torch.Tensor], out: torch.Tensor) -> torch.Tensor:
+    _rows2d(resid, torch.float32, "resid")
+    _rows2d(z, torch.bfloat16, "z")
+    _rows2d(out, torch.float32, "out")
+    if not (resid.is_contiguous() and z.is_contiguous() and out.is_contiguous() and resid.shape == z.shape == out.shape):
+        raise ValueError("sailrecon_b200: ls_residual needs contiguous tensors of one shape")
+    _vec(gamma, resid.shape[1], "gamma")
+    _lib.check(_lib.load().sr_ls_residual_f32(resid.data_ptr(), z.data_ptr(), _ptr(gamma), out.data_ptr(), resid.shape[0],
+                                              resid.shape[1], _stream()), "ls_residual")
+    return out
+
+
+def gelu_fwd(u: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    if not (u.is_cuda and u.dtype == out.dtype == torch.bfloat16 and u.is_contiguous() and out.is_contiguous() and u.shape == out.shape):
+        raise ValueError("sailrecon_b200: gelu_fwd needs contiguous bf16 CUDA tensors of one shape")
+    _lib.check(_lib.load().sr_gelu_fwd_bf16(u.data_ptr(), out.data_ptr(), u.numel(), _stream()), "gelu_fwd")
+    return out
+
+
+def gelu_bwd(u: torch.Tensor, dg: torch.Tensor, du: torch.Tensor) -> torch.Tensor:
+    for t in (u, dg, du):
+        if not (t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and t.shape == u.shape):
+            raise ValueError("sailrecon_b200: gelu_bwd needs contiguous bf16 CUDA tensors of one shape")
+    _lib.check(_lib.load().sr_gelu_bwd_bf16(u.data_ptr(), dg.data_ptr(), du.data_ptr(), u.numel(), _stream()), "gelu_bwd")
+    return du
+
+
+def layernorm_bwd(x: torch.Tensor, weight: Optional[torch.Tensor], dy: torch.Tensor, dx: torch.Tensor,
+                  dweight: Optional[torch.Tensor], dbias: Optional[torch.Tensor], eps: float) -> torch.Tensor:
+    """dx += dLN(dy); dweight / dbias accumulate (fp32 [C])."""
+    _rows2d(x, torch.float32, "x")
+    _rows2d(dy, torch.bfloat16, "dy")
+    _rows2d(dx, torch.float32, "dx")
+    if not (x.shape == dy.shape == dx.shape):
+        raise ValueError("sailrecon_b200: layernorm_bwd shape mismatch")
+    for n, t in (("weight", weight), ("dweight", dweight), ("dbias", dbias)):
+        _vec(t, x.shape[1], n)
+    _lib.check(_lib.load().sr_layernorm_bwd(x.data_ptr(), x.stride(0), _ptr(weight), dy.data_ptr(), dy.stride(0), dx.data_ptr(),
+                                            dx.stride(0), _ptr(dweight), _ptr(dbias), x.shape[0], x.shape[1], float(eps), _stream()),
+               "layernorm_bwd")
+    return dx
+
+
+def qknorm_rope_fwd(raw: torch.Tensor, out: torch.Tensor, qkv: QkvEpilogue) -> torch.Tensor:
+    _rows2d(raw, torch.bfloat16, "raw")
+    _rows2d(out, torch.bfloat16, "out")
+    if raw.shape != out.shape or raw.shape[1] != 3 * qkv.qkv_dim:
+        raise ValueError("sailrecon_b200: qknorm_rope needs [M, 3C] buffers")
+    e = SrEpilogue()
+    keep = _fill_qkv(e, qkv, raw.shape[0])
+    _lib.check(_lib.load().sr_qknorm_rope_fwd(raw.data_ptr(), raw.stride(0), out.data_ptr(), out.stride(0), C.byref(e), raw.shape[0],
+                                              _stream()), "qknorm_rope_fwd")
+    del keep
+    return out
+
+
+def qknorm_rope_bwd(raw: torch.Tensor, dqkv: torch.Tensor, qkv: QkvEpilogue, dq_norm=None, dk_norm=None) -> torch.Tensor:
+    """In place on dqkv (gradient w.r.t. normalised / rotated q, k -> gradient w.r.t. raw); dq_norm / dk_norm are
+    (dweight, dbias) fp32 [64] accumulators or None."""
+    _rows2d(raw, torch.bfloat16, "raw")
+    _rows2d(dqkv, torch.bfloat16, "dqkv")
+    if raw.shape != dqkv.shape or raw.shape[1] != 3 * qkv.qkv_dim:
+        raise ValueError("sailrecon_b200: qknorm_rope needs [M, 3C] buffers")
+    e = SrEpilogue()
+    keep = _fill_qkv(e, qkv, raw.shape[0])
+    g = [None, None, None, None]
+    if dq_norm is not None:
+        g = [dq_norm[0], dq_norm[1], dk_norm[0], dk_norm[1]]
+        for t in g:
+            _vec(t, qkv.head_dim, "q/k norm gradient")
+    _lib.check(_lib.load().sr_qknorm_rope_bwd(raw.data_ptr(), raw.stride(0), dqkv.data_ptr(), dqkv.stride(0), C.byref(e), _ptr(g[0]),
+                                              _ptr(g[1]), _ptr(g[2]), _ptr(g[3]), raw.shape[0], _stream()), "qknorm_rope_bwd")
+    del keep
+    return dqkv
 
 
 # ------------------------------------------------------------------------------------------------ re-layout

@@ -1,0 +1,212 @@
+"""Training step of one transformer Block on the C-ABI kernels: forward that keeps what the backward needs, and the
+backward itself (autograd of sailrecon/layers/block.py:86-112 = attention.py:70-122 + mlp.py:33-40 + layer_scale.py:22,
+as train/train_imc.py:358-380 differentiates it under bf16 autocast).
+
+The reference wraps every aggregator block in torch.utils.checkpoint (models/aggregator.py:654-657,726-729,758-761):
+only the block input survives the forward pass, the block is re-run inside backward.  The same schedule here:
+
+    forward pass      engine.run_block(...)                       (inference kernels, nothing kept but x)
+    backward pass     saved = block_forward_saving(blk, x, ...)   (re-run with un-fused epilogues that keep u, z, raw qkv, lse)
+                      dx = block_backward(blk, saved, dy, grads)
+
+Every contraction runs on the tcgen05 kernels: dX = dY W and dW = dY^T X are sr_gemm_bf16 calls on transposed bf16
+operands (ops.transpose_bf16), attention on sr_attn_bwd_bf16; the rest are the row kernels of csrc/train_rows.cu.
+Parameter gradients are accumulated in fp32 into `grads[param]` (the role of .grad under DDP, train_imc.py:472).
+There is no torch fallback.  Scope: blocks whose attention calls have no external prefix (frame and global blocks).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.nn as nn
+
+from . import engine, ops
+from ._lib import SR_EPI_BIAS
+
+BF = torch.bfloat16
+
+
+@dataclass
+class BlockSaved:
+    x: torch.Tensor                    # block input, fp32 [T, C]
+    h1: torch.Tensor                   # LN1(x) bf16
+    raw: torch.Tensor                  # qkv Linear output before q/k norm and RoPE, bf16 [T, 3C]
+    qkv: torch.Tensor                  # after q/k norm and RoPE (what attention consumed)
+    o: torch.Tensor                    # attention output bf16 [T, C]
+    lse: List[torch.Tensor]            # one per attention call
+    z1: torch.Tensor                   # proj output (rounded) bf16
+    x1: torch.Tensor                   # x + g1 z1, fp32
+    h2: torch.Tensor                   # LN2(x1) bf16
+    u: torch.Tensor                    # fc1 output before GELU, bf16 [T, 4C]
+    g: torch.Tensor                    # gelu(u) bf16
+    z2: torch.Tensor                   # fc2 output (rounded) bf16
+    calls: Sequence[engine.AttnCall] = field(default_factory=list)
+    epi: Optional[ops.QkvEpilogue] = None
+
+
+def _qkv_epilogue(attn: nn.Module, rows_pos: Optional[engine.RowPositions], device, T: int) -> Optional[ops.QkvEpilogue]:
+    C = attn.qkv.weight.shape[1]
+    d = C // attn.num_heads
+    qn = kn = None
+    if isinstance(attn.q_norm, nn.LayerNorm):
+        qn = (attn.q_norm.weight.detach(), attn.q_norm.bias.detach())
+        kn = (attn.k_norm.weight.detach(), attn.k_norm.bias.detach())
+    cos = sin = pos32 = None
+    if attn.rope is not None and rows_pos is not None:
+        cos, sin = attn.rope.tables(device, rows_pos.max_pos, d)
+        pos32 = rows_pos.pos32
+        if pos32.shape[0] != T:
+            raise ValueError("sailrecon_b200: one (y, x) position per token row is required")
+    if qn is None and cos is None:
+        return None
+    if d != 64:
+        raise NotImplementedError("sailrecon_b200: q/k LayerNorm and RoPE are implemented for head_dim 64")
+    return ops.QkvEpilogue(C, 0, d, qn, kn, attn.q_norm.eps if qn is not None else 1e-5, cos, sin, pos32)
+
+
+def _check_calls(calls: Sequence[engine.AttnCall]) -> None:
+    for c in calls:
+        if c.prefix is not None and c.prefix.length > 0 and c.prefix.k is not None:
+            raise NotImplementedError("sailrecon_b200: training blocks with an external K/V prefix are not wired up yet")
+
+
+def block_forward_saving(blk: nn.Module, x: torch.Tensor, calls: Sequence[engine.AttnCall],
+                         rows_pos: Optional[engine.RowPositions]) -> BlockSaved:
+    """Block.forward on rows x [T, C] (fp32, not modified) keeping every intermediate the backward reads.  Same arithmetic
+    as engine.run_block in bf16 mode: each fused epilogue is split at the point where its input has to be kept."""
+    engine.require_cuda_f32(x, "x")
+    _check_calls(calls)
+    T, C = x.shape
+    dev = x.device
+    attn, mlp = blk.attn, blk.mlp
+    H = attn.num_heads
+    d = C // H
+    w1, b1, eps1 = engine.ln_params(blk.norm1)
+    h1 = ops.layernorm(x, w1, b1, eps1, torch.empty(T, C, dtype=BF, device=dev))
+    raw = torch.empty(T, 3 * C, dtype=BF, device=dev)
+    ops.gemm(h1, engine.weight_bf16(attn.qkv), engine.bias_for(attn.qkv, "bf16"), raw, kind=SR_EPI_BIAS)
+    epi = _qkv_epilogue(attn, rows_pos, dev, T)
+    qkv = raw if epi is None else ops.qknorm_rope_fwd(raw, torch.empty_like(raw), epi)
+    o = torch.empty(T, C, dtype=BF, device=dev)
+    lses = []
+    q, k, v = qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:]
+    for c in calls:
+        stride = c.stride or c.seg_len
+        r1 = c.q_row0 + (c.batch - 1) * stride + c.seg_len
+        lse = ops.new_lse(H, c.batch, c.seg_len, dev)
+        pk = pv = None
+        plen = 0
+        if c.prefix is not None and c.prefix.length > 0:
+            pk, pv, plen = k[c.prefix.row0:c.prefix.row0 + c.prefix.length], v[c.prefix.row0:c.prefix.row0 + c.prefix.length], c.prefix.length
+        ops.attention(q[c.q_row0:r1], k[c.q_row0:r1], v[c.q_row0:r1], o[c.q_row0:r1], H, d, c.batch, c.seg_len, c.seg_len, stride,
+                      stride, prefix_k=pk, prefix_v=pv, prefix_len=plen, scale=attn.scale, lse=lse)
+        lses.append(lse)
+    z1 = torch.empty(T, C, dtype=BF, device=dev)
+    ops.gemm(o, engine.weight_bf16(attn.proj), engine.bias_for(attn.proj, "bf16"), z1, kind=SR_EPI_BIAS)
+    x1 = ops.ls_residual(x, z1, engine.gamma_of(blk.ls1), torch.empty_like(x))
+    w2, b2, eps2 = engine.ln_params(blk.norm2)
+    h2 = ops.layernorm(x1, w2, b2, eps2, torch.empty(T, C, dtype=BF, device=dev))
+    hid = mlp.fc1.weight.shape[0]
+    u = torch.empty(T, hid, dtype=BF, device=dev)
+    ops.gemm(h2, engine.weight_bf16(mlp.fc1), engine.bias_for(mlp.fc1, "bf16"), u, kind=SR_EPI_BIAS)
+    g = ops.gelu_fwd(u, torch.empty_like(u))
+    z2 = torch.empty(T, C, dtype=BF, device=dev)
+    ops.gemm(g, engine.weight_bf16(mlp.fc2), engine.bias_for(mlp.fc2, "bf16"), z2, kind=SR_EPI_BIAS)
+    return BlockSaved(x, h1, raw, qkv, o, lses, z1, x1, h2, u, g, z2, calls, epi)
+
+
+def block_output(blk: nn.Module, s: BlockSaved) -> torch.Tensor:
+    """x1 + g2 z2: the block output of a saving forward (tests; the training schedule takes it from engine.run_block)."""
+    return ops.ls_residual(s.x1, s.z2, engine.gamma_of(blk.ls2), torch.empty_like(s.x1))
+
+
+def _acc(grads: Dict[nn.Parameter, torch.Tensor], p: Optional[nn.Parameter]) -> Optional[torch.Tensor]:
+    if p is None:
+        return None
+    if p not in grads:
+        grads[p] = torch.zeros(p.shape, dtype=torch.float32, device=p.device)
+    return grads[p]
+
+
+def linear_backward(lin: nn.Module, a_in: torch.Tensor, dz: torch.Tensor, grads: Dict[nn.Parameter, torch.Tensor],
+                    need_input_grad: bool = True) -> Optional[torch.Tensor]:
+    """Gradients of z = a_in W^T + b (nn.Linear): dW += dz^T a_in, db += colsum(dz) (fp32 accumulators in `grads`), returns
+    d a_in = dz W (bf16).  a_in [T, K] bf16, dz [T, N] bf16 — both GEMMs on the tcgen05 kernel."""
+    T, K = a_in.shape
+    N = dz.shape[1]
+    dev = a_in.device
+    dzT = ops.transpose_bf16(dz)                                   # [N, T_pad]
+    aT = ops.transpose_bf16(a_in)                                  # [K, T_pad]
+    gw = _acc(grads, lin.weight)
+    if N % 128 == 0 and K % 128 == 0:
+        tmp = torch.empty(N, K, dtype=torch.float32, device=dev)
+        ops.gemm(dzT, aT, None, tmp, kind=SR_EPI_BIAS)             # [N, T_pad] x [K, T_pad]^T
+        gw.view(N, K).add_(tmp)
+    else:
+        raise NotImplementedError("sailrecon_b200: Linear gradients need in / out features that are multiples of 128")
+    if lin.bias is not None:
+        ops.colsum(dz, None, _acc(grads, lin.bias), accumulate=True)
+    if not need_input_grad:
+        return None
+    wT = engine._cached(lin, "wT_bf16", lin.weight, lambda w: ops.transpose_bf16(engine.weight_bf16(lin)))   # [K, N]
+    da = torch.empty(T, K, dtype=BF, device=dev)
+    ops.gemm(dz, wT, None, da, kind=SR_EPI_BIAS)
+    return da
+
+
+def block_backward(blk: nn.Module, s: BlockSaved, dy: torch.Tensor, grads: Dict[nn.Parameter, torch.Tensor]) -> torch.Tensor:
+    """dy = gradient w.r.t. the block output (fp32 [T, C]) -> gradient w.r.t. the block input (fp32, a fresh tensor);
+    parameter gradients accumulate into `grads`."""
+    engine.require_cuda_f32(dy, "dy")
+    T, C = dy.shape
+    dev = dy.device
+    attn, mlp = blk.attn, blk.mlp
+    H = attn.num_heads
+    d = C // H
+    dx1 = dy.clone()                                               # residual path of x2 = x1 + g2 z2
+    # ---- MLP branch
+    g2 = engine.gamma_of(blk.ls2)
+    if g2 is not None:
+        ops.colsum(dy, s.z2, _acc(grads, blk.ls2.gamma), accumulate=True)
+    dz2 = ops.scale_cast_bf16(dy, g2, torch.empty(T, C, dtype=BF, device=dev))
+    dg = linear_backward(mlp.fc2, s.g, dz2, grads)
+    du = ops.gelu_bwd(s.u, dg, dg)                                 # in place over dg
+    dh2 = linear_backward(mlp.fc1, s.h2, du, grads)
+    w2, _, eps2 = engine.ln_params(blk.norm2)
+    ops.layernorm_bwd(s.x1, w2, dh2, dx1, _acc(grads, blk.norm2.weight), _acc(grads, blk.norm2.bias), eps2)
+    # ---- attention branch
+    dx = dx1.clone()                                               # residual path of x1 = x + g1 z1
+    g1 = engine.gamma_of(blk.ls1)
+    if g1 is not None:
+        ops.colsum(dx1, s.z1, _acc(grads, blk.ls1.gamma), accumulate=True)
+    dz1 = ops.scale_cast_bf16(dx1, g1, dz2)                        # dz2 is free again
+    do = linear_backward(attn.proj, s.o, dz1, grads)
+    dqkv = torch.empty(T, 3 * C, dtype=BF, device=dev)
+    q, k, v = s.qkv[:, :C], s.qkv[:, C:2 * C], s.qkv[:, 2 * C:]
+    dq, dk, dv = dqkv[:, :C], dqkv[:, C:2 * C], dqkv[:, 2 * C:]
+    covered = 0
+    for c, lse in zip(s.calls, s.lse):
+        stride = c.stride or c.seg_len
+        r1 = c.q_row0 + (c.batch - 1) * stride + c.seg_len
+        if c.prefix is not None and c.prefix.length > 0:
+            raise NotImplementedError("sailrecon_b200: training blocks with a K/V prefix are not wired up yet")
+        if stride != c.seg_len:
+            raise NotImplementedError("sailrecon_b200: training attention calls must cover their rows densely")
+        sl = slice(c.q_row0, r1)
+        ops.attention_bwd(q[sl], k[sl], v[sl], s.o[sl], do[sl], lse, dq[sl], dk[sl], dv[sl], H, d, c.batch, c.seg_len, c.seg_len,
+                          stride, stride, scale=attn.scale)
+        covered += r1 - c.q_row0
+    if covered != T:
+        raise ValueError("sailrecon_b200: the attention calls of a training block must cover every row exactly once")
+    if s.epi is not None:
+        dqn = dkn = None
+        if s.epi.q_norm is not None:
+            dqn = (_acc(grads, attn.q_norm.weight), _acc(grads, attn.q_norm.bias))
+            dkn = (_acc(grads, attn.k_norm.weight), _acc(grads, attn.k_norm.bias))
+        ops.qknorm_rope_bwd(s.raw, dqkv, s.epi, dqn, dkn)
+    dh1 = linear_backward(attn.qkv, s.h1, dqkv, grads)
+    w1, _, eps1 = engine.ln_params(blk.norm1)
+    ops.layernorm_bwd(s.x, w1, dh1, dx, _acc(grads, blk.norm1.weight), _acc(grads, blk.norm1.bias), eps1)
+    return dx

@@ -1,0 +1,217 @@
+"""GPU parity of the training-step kernels (csrc/train_rows.cu, csrc/attn_bwd.cu via sailrecon_b200.train) against
+plain fp32 PyTorch autograd of the same Block (sailrecon/layers/block.py:86-112 with attention.py:70-122, rope.py:136-207,
+mlp.py:33-40, layer_scale.py:22).  The kernels run the bf16 autocast arithmetic of train/train_imc.py:358-380, the
+reference here is fp32: tolerances are the bf16 ones of north_star (2e-2 relative L2), 3e-2 for parameter gradients.
+"""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from golden_common import rel_l2
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+BF = torch.bfloat16
+
+
+def _g(seed):
+    return torch.Generator(device=DEV).manual_seed(seed)
+
+
+def _randn(*shape, seed=0, scale=1.0):
+    return torch.randn(*shape, device=DEV, generator=_g(seed)) * scale
+
+
+# ------------------------------------------------------------------------------------------------ row kernels
+def test_transpose_colsum_scale_cast_ls_residual():
+    from sailrecon_b200 import ops
+    a = _randn(333, 1024, seed=1).to(BF)
+    t = ops.transpose_bf16(a)
+    assert t.shape == (1024, 384)
+    assert torch.equal(t[:, :333], a.t()) and bool((t[:, 333:] == 0).all())
+    x = _randn(333, 1024, seed=2)
+    out = torch.full((1024,), float("nan"), device=DEV)
+    ops.colsum(x, a, out)
+    ref = (x.double() * a.double()).sum(0)
+    assert rel_l2(out.cpu(), ref.float().cpu()) < 1e-5
+    ops.colsum(a, None, out, accumulate=True)
+    assert rel_l2(out.cpu(), (ref + a.double().sum(0)).float().cpu()) < 1e-5
+    gam = _randn(1024, seed=3)
+    o = ops.scale_cast_bf16(x, gam, torch.empty(333, 1024, dtype=BF, device=DEV))
+    assert torch.equal(o, (x * gam).to(BF))
+    y = ops.ls_residual(x, a, gam, torch.empty_like(x))
+    assert torch.allclose(y, x + gam * a.float(), rtol=1e-6, atol=1e-6)
+
+
+def test_gelu_fwd_bwd():
+    from sailrecon_b200 import ops
+    u = _randn(77, 4096, seed=4, scale=2.0).to(BF)
+    dg = _randn(77, 4096, seed=5).to(BF)
+    g = ops.gelu_fwd(u, torch.empty_like(u))
+    uf = u.float().requires_grad_(True)
+    ref = F.gelu(uf)
+    assert rel_l2(g.float().cpu(), ref.detach().cpu()) < 4e-3
+    ref.backward(dg.float())
+    du = ops.gelu_bwd(u, dg, torch.empty_like(u))
+    assert rel_l2(du.float().cpu(), uf.grad.cpu()) < 4e-3
+
+
+def test_layernorm_bwd():
+    from sailrecon_b200 import ops
+    T, C = 203, 1024
+    x = _randn(T, C, seed=6, scale=1.7) + 0.3
+    w = _randn(C, seed=7) * 0.2 + 1.0
+    b = _randn(C, seed=8) * 0.1
+    dy = _randn(T, C, seed=9).to(BF)
+    base = _randn(T, C, seed=10)
+    xr = x.clone().requires_grad_(True)
+    wr, br = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    F.layer_norm(xr, (C,), wr, br, 1e-5).backward(dy.float())
+    dx = base.clone()
+    dw = torch.zeros(C, device=DEV)
+    db = torch.zeros(C, device=DEV)
+    ops.layernorm_bwd(x, w, dy, dx, dw, db, 1e-5)
+    assert rel_l2((dx - base).cpu(), xr.grad.cpu()) < 1e-4
+    assert rel_l2(dw.cpu(), wr.grad.cpu()) < 1e-4
+    assert rel_l2(db.cpu(), br.grad.cpu()) < 1e-4
+
+
+def _rope_ref(x, pos, freq=100.0):
+    """x [T, H, 64], pos int [T, 2] (y, x): rope.py:136-207 — halves rotate with y / x, pairs (i, i + 16), 16 frequencies."""
+    inv = 1.0 / freq ** (torch.arange(16, device=x.device, dtype=torch.float32) / 16.0)
+    parts = []
+    for half in range(2):
+        ang = pos[:, half].float()[:, None] * inv[None]
+        c, s = ang.cos()[:, None, :], ang.sin()[:, None, :]
+        a, b = x[..., half * 32:half * 32 + 16], x[..., half * 32 + 16:half * 32 + 32]
+        parts += [a * c - b * s, b * c + a * s]
+    return torch.cat(parts, dim=-1)
+
+
+def _positions(frames, P):
+    """5 special tokens at (0, 0), then a patch grid offset by 1 (aggregator.py:319-328)."""
+    side = int(math.ceil(math.sqrt(P - 5)))
+    ys = torch.arange(P - 5) // side + 1
+    xs = torch.arange(P - 5) % side + 1
+    one = torch.cat([torch.zeros(5, 2, dtype=torch.long), torch.stack([ys, xs], -1)])
+    return one.repeat(frames, 1).to(DEV)
+
+
+def test_qknorm_rope_fwd_equals_fused_epilogue_and_bwd_matches_autograd():
+    from sailrecon_b200 import engine, ops
+    from sailrecon_b200.layers import RotaryPositionEmbedding2D
+    T, H, d = 300, 16, 64
+    C = H * d
+    rope = RotaryPositionEmbedding2D(frequency=100.0)
+    pos = _positions(2, 150)
+    rp = engine.RowPositions(pos.to(torch.int32).contiguous(), int(pos.max()) + 1)
+    cos, sin = rope.tables(DEV, rp.max_pos, d)
+    qn = (_randn(d, seed=11) * 0.2 + 1.0, _randn(d, seed=12) * 0.1)
+    kn = (_randn(d, seed=13) * 0.2 + 1.0, _randn(d, seed=14) * 0.1)
+    epi = ops.QkvEpilogue(C, 0, d, qn, kn, 1e-5, cos, sin, rp.pos32)
+    raw = _randn(T, 3 * C, seed=15, scale=1.5).to(BF)
+    out = ops.qknorm_rope_fwd(raw, torch.empty_like(raw), epi)
+
+    def ref_fwd(r):
+        q, k, v = (r[:, i * C:(i + 1) * C].reshape(T, H, d) for i in range(3))
+        q = _rope_ref(F.layer_norm(q, (d,), qw, qb, 1e-5), pos)
+        k = _rope_ref(F.layer_norm(k, (d,), kw, kb, 1e-5), pos)
+        return torch.cat([q.reshape(T, C), k.reshape(T, C), v.reshape(T, C)], dim=1)
+
+    qw, qb, kw, kb = (t.clone().requires_grad_(True) for t in (*qn, *kn))
+    rr = raw.float().requires_grad_(True)
+    ref = ref_fwd(rr)
+    assert rel_l2(out.float().cpu(), ref.detach().cpu()) < 4e-3
+    assert torch.equal(out[:, 2 * C:], raw[:, 2 * C:])
+    dpost = _randn(T, 3 * C, seed=16).to(BF)
+    ref.backward(dpost.float())
+    dq = [torch.zeros(d, device=DEV) for _ in range(4)]
+    draw = ops.qknorm_rope_bwd(raw, dpost.clone(), epi, (dq[0], dq[1]), (dq[2], dq[3]))
+    assert rel_l2(draw.float().cpu(), rr.grad.cpu()) < 6e-3
+    for got, want in zip(dq, (qw, qb, kw, kb)):
+        assert rel_l2(got.cpu(), want.grad.cpu()) < 2e-3
+
+
+def test_linear_backward_on_tensor_cores():
+    import torch.nn as nn
+    from sailrecon_b200 import train
+    T, K, N = 333, 1024, 3072
+    lin = nn.Linear(K, N).to(DEV)
+    a = _randn(T, K, seed=17).to(BF)
+    dz = _randn(T, N, seed=18).to(BF)
+    grads = {}
+    da = train.linear_backward(lin, a, dz, grads)
+    w = lin.weight.detach().to(BF).float()
+    assert rel_l2(da.float().cpu(), (dz.float() @ w).cpu()) < 6e-3
+    assert rel_l2(grads[lin.weight].cpu(), (dz.float().t() @ a.float()).cpu()) < 1e-3
+    assert rel_l2(grads[lin.bias].cpu(), dz.float().sum(0).cpu()) < 1e-4
+    train.linear_backward(lin, a, dz, grads)                                   # accumulates
+    assert rel_l2(grads[lin.weight].cpu(), (2 * dz.float().t() @ a.float()).cpu()) < 1e-3
+
+
+# ------------------------------------------------------------------------------------------------ whole block
+def _block_ref(P, x, pos, batch, L, H):
+    T, C = x.shape
+    d = C // H
+    h1 = F.layer_norm(x, (C,), P["norm1.weight"], P["norm1.bias"], 1e-5)
+    qkv = h1 @ P["attn.qkv.weight"].t() + P["attn.qkv.bias"]
+    q, k, v = (qkv[:, i * C:(i + 1) * C].reshape(T, H, d) for i in range(3))
+    q = _rope_ref(F.layer_norm(q, (d,), P["attn.q_norm.weight"], P["attn.q_norm.bias"], 1e-5), pos)
+    k = _rope_ref(F.layer_norm(k, (d,), P["attn.k_norm.weight"], P["attn.k_norm.bias"], 1e-5), pos)
+    outs = []
+    for b in range(batch):
+        sl = slice(b * L, (b + 1) * L)
+        s = torch.einsum("qhd,khd->hqk", q[sl], k[sl]) * d ** -0.5
+        outs.append(torch.einsum("hqk,khd->qhd", torch.softmax(s, -1), v[sl]).reshape(L, C))
+    o = torch.cat(outs)
+    x1 = x + P["ls1.gamma"] * (o @ P["attn.proj.weight"].t() + P["attn.proj.bias"])
+    h2 = F.layer_norm(x1, (C,), P["norm2.weight"], P["norm2.bias"], 1e-5)
+    g = F.gelu(h2 @ P["mlp.fc1.weight"].t() + P["mlp.fc1.bias"])
+    return x1 + P["ls2.gamma"] * (g @ P["mlp.fc2.weight"].t() + P["mlp.fc2.bias"])
+
+
+@pytest.mark.parametrize("batch,L", [(3, 150), (1, 450)])
+def test_block_forward_backward_matches_fp32_autograd(batch, L):
+    """One aggregator Block (dim 1024, 16 heads, q/k norm, 2D RoPE, LayerScale) as a frame block (3 segments) and as a global
+    block (one segment): saving forward == inference forward, dx and every parameter gradient against fp32 autograd."""
+    from sailrecon_b200 import engine, train
+    from sailrecon_b200.layers import Block, RotaryPositionEmbedding2D
+    C, H = 1024, 16
+    T = batch * L
+    torch.manual_seed(5)
+    blk = Block(C, H, qk_norm=True, rope=RotaryPositionEmbedding2D(frequency=100.0), init_values=0.01).to(DEV)
+    with torch.no_grad():                                   # O(1) LayerScale and non-trivial norms so every path shows up
+        for n, p in blk.named_parameters():
+            if n.endswith("gamma"):
+                p.uniform_(0.3, 0.9)
+            elif "norm" in n and n.endswith("weight"):
+                p.uniform_(0.7, 1.3)
+            elif n.endswith("bias"):
+                p.uniform_(-0.1, 0.1)
+    x = _randn(T, C, seed=20)
+    dy = _randn(T, C, seed=21)
+    pos = _positions(T // 150, 150)
+    rp = engine.RowPositions(pos.to(torch.int32).contiguous(), int(pos.max()) + 1)
+    calls = engine.full_segments(batch, L)
+
+    saved = train.block_forward_saving(blk, x, calls, rp)
+    y = train.block_output(blk, saved)
+    y_inf = engine.run_block(blk, x.clone(), calls, rp, "bf16")
+    assert rel_l2(y.cpu(), y_inf.cpu()) < 2e-3              # fused and un-fused epilogues round at the same places
+    grads = {}
+    dx = train.block_backward(blk, saved, dy, grads)
+    torch.cuda.synchronize()
+
+    P = {n: p.detach().clone().requires_grad_(True) for n, p in blk.named_parameters()}
+    xr = x.clone().requires_grad_(True)
+    y_ref = _block_ref(P, xr, pos, batch, L, H)
+    y_ref.backward(dy)
+    assert rel_l2(y.cpu(), y_ref.detach().cpu()) < 2e-2
+    assert rel_l2(dx.cpu(), xr.grad.cpu()) < 2e-2
+    named = dict(blk.named_parameters())
+    assert set(grads) == set(named.values())
+    for n, p in named.items():
+        e = rel_l2(grads[p].cpu(), P[n].grad.cpu())
+        assert e < 3e-2, (n, e)
