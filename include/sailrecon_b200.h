@@ -182,6 +182,10 @@ int sr_qknorm_rope_fwd(const void* raw, int64_t ldr, void* out, int64_t ldo, con
 int sr_qknorm_rope_bwd(const void* raw, int64_t ldr, void* dqkv, int64_t ldd, const sr_epilogue_t* qkv, float* dqn_w,
                        float* dqn_b, float* dkn_w, float* dkn_b, int64_t M, void* stream);
 
+/* dst[idx[r], :] += src[r, :], idx unique: gradient of the scene-token row gather (aggregator.py:617-625)        */
+int sr_scatter_add_rows_f32(float* dst, int64_t ldd, const int32_t* idx, const float* src, int64_t lds, int64_t n, int64_t C,
+                            void* stream);
+
 /* ---- token re-layout (aggregator.py:355-357,393-399,406-423,603-625) ----------------------------------- */
 /* dst[i, :] = src[idx[i], :] for i < n; fp32 rows of C elements; idx int32 (scene-token selection).       */
 int sr_gather_rows_f32(const float* src, int64_t lds, const int32_t* idx, float* dst, int64_t ldd, int64_t n,

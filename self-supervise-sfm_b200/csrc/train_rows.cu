@@ -292,6 +292,21 @@ qknorm_rope_kernel(const __nv_bfloat16* __restrict__ raw, int64_t ldr, __nv_bflo
   }
 }
 
+// dst[idx[r], :] += src[r, :] for unique idx (the gradient of the scene-token gather, aggregator.py:617-625)
+__global__ void __launch_bounds__(256)
+scatter_add_rows_kernel(float* __restrict__ dst, int64_t ldd, const int32_t* __restrict__ idx, const float* __restrict__ src,
+                        int64_t lds, int64_t n, int C) {
+  const int64_t e = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+  if (e >= n * C) return;
+  const int64_t r = e / C;
+  const int c = static_cast<int>(e % C);
+  const float4 v = *reinterpret_cast<const float4*>(src + r * lds + c);
+  float* o = dst + static_cast<int64_t>(idx[r]) * ldd + c;
+  float4 t = *reinterpret_cast<float4*>(o);
+  t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+  *reinterpret_cast<float4*>(o) = t;
+}
+
 }  // namespace sr
 
 using namespace sr;
@@ -421,4 +436,15 @@ extern "C" int sr_qknorm_rope_fwd(const void* raw, int64_t ldr, void* out, int64
 extern "C" int sr_qknorm_rope_bwd(const void* raw, int64_t ldr, void* dqkv, int64_t ldd, const sr_epilogue_t* qkv, float* dqn_w,
                                   float* dqn_b, float* dkn_w, float* dkn_b, int64_t M, void* stream) {
   return qk_launch(true, raw, ldr, dqkv, ldd, dqn_w, dqn_b, dkn_w, dkn_b, qkv, M, stream);
+}
+
+extern "C" int sr_scatter_add_rows_f32(float* dst, int64_t ldd, const int32_t* idx, const float* src, int64_t lds, int64_t n,
+                                       int64_t C, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(dst && idx && src && n > 0 && C > 0 && C % 4 == 0 && ldd % 4 == 0 && lds % 4 == 0, "sr_scatter_add_rows_f32: bad shape");
+  const int64_t n4 = n * C / 4;
+  scatter_add_rows_kernel<<<static_cast<unsigned>((n4 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      dst, ldd, idx, src, lds, n, static_cast<int>(C));
+  SR_LAUNCHED();
+  return SR_OK;
 }

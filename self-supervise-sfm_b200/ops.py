@@ -375,6 +375,17 @@ def layernorm_bwd(x: torch.Tensor, weight: Optional[torch.Tensor], dy: torch.Ten
     return dx
 
 
+def scatter_add_rows(dst: torch.Tensor, idx: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    """dst[idx[r]] += src[r] (idx unique int32)."""
+    _rows2d(dst, torch.float32, "dst")
+    _rows2d(src, torch.float32, "src")
+    if not (idx.is_cuda and idx.dtype == torch.int32 and idx.is_contiguous() and idx.numel() == src.shape[0]) or dst.shape[1] != src.shape[1]:
+        raise ValueError("sailrecon_b200: scatter_add_rows needs one contiguous int32 index per source row")
+    _lib.check(_lib.load().sr_scatter_add_rows_f32(dst.data_ptr(), dst.stride(0), idx.data_ptr(), src.data_ptr(), src.stride(0),
+                                                   src.shape[0], src.shape[1], _stream()), "scatter_add_rows")
+    return dst
+
+
 def qknorm_rope_fwd(raw: torch.Tensor, out: torch.Tensor, qkv: QkvEpilogue) -> torch.Tensor:
     _rows2d(raw, torch.bfloat16, "raw")
     _rows2d(out, torch.bfloat16, "out")

@@ -12,7 +12,10 @@ only the block input survives the forward pass, the block is re-run inside backw
 Every contraction runs on the tcgen05 kernels: dX = dY W and dW = dY^T X are sr_gemm_bf16 calls on transposed bf16
 operands (ops.transpose_bf16), attention on sr_attn_bwd_bf16; the rest are the row kernels of csrc/train_rows.cu.
 Parameter gradients are accumulated in fp32 into `grads[param]` (the role of .grad under DDP, train_imc.py:472).
-There is no torch fallback.  Scope: blocks whose attention calls have no external prefix (frame and global blocks).
+There is no torch fallback.  Blocks whose attention call reads an external K/V prefix (the reloc blocks: query frames
+against the scene tokens, aggregator.py:672-741) return the prefix gradient in `saved.dprefix`; scene_forward_saving /
+scene_backward carry it through the scene-token path (row gather + norm1 + K|V projection of the reloc block,
+aggregator.py:593-626) back into the anchor stream.
 """
 from __future__ import annotations
 
@@ -44,6 +47,7 @@ class BlockSaved:
     z2: torch.Tensor                   # fc2 output (rounded) bf16
     calls: Sequence[engine.AttnCall] = field(default_factory=list)
     epi: Optional[ops.QkvEpilogue] = None
+    dprefix: Optional[torch.Tensor] = None    # set by block_backward: [prefix rows, 3C] bf16, k / v thirds hold d prefix K / V
 
 
 def _qkv_epilogue(attn: nn.Module, rows_pos: Optional[engine.RowPositions], device, T: int) -> Optional[ops.QkvEpilogue]:
@@ -68,8 +72,11 @@ def _qkv_epilogue(attn: nn.Module, rows_pos: Optional[engine.RowPositions], devi
 
 def _check_calls(calls: Sequence[engine.AttnCall]) -> None:
     for c in calls:
-        if c.prefix is not None and c.prefix.length > 0 and c.prefix.k is not None:
-            raise NotImplementedError("sailrecon_b200: training blocks with an external K/V prefix are not wired up yet")
+        if c.prefix is not None and c.prefix.length > 0:
+            if c.prefix.k is None:
+                raise NotImplementedError("sailrecon_b200: training attention with an in-buffer prefix is not supported")
+            if len(calls) != 1 or c.prefix.row0 != 0:
+                raise NotImplementedError("sailrecon_b200: a training block takes at most one call with an external prefix")
 
 
 def block_forward_saving(blk: nn.Module, x: torch.Tensor, calls: Sequence[engine.AttnCall],
@@ -99,7 +106,7 @@ def block_forward_saving(blk: nn.Module, x: torch.Tensor, calls: Sequence[engine
         pk = pv = None
         plen = 0
         if c.prefix is not None and c.prefix.length > 0:
-            pk, pv, plen = k[c.prefix.row0:c.prefix.row0 + c.prefix.length], v[c.prefix.row0:c.prefix.row0 + c.prefix.length], c.prefix.length
+            pk, pv, plen = c.prefix.k[:c.prefix.length], c.prefix.v[:c.prefix.length], c.prefix.length
         ops.attention(q[c.q_row0:r1], k[c.q_row0:r1], v[c.q_row0:r1], o[c.q_row0:r1], H, d, c.batch, c.seg_len, c.seg_len, stride,
                       stride, prefix_k=pk, prefix_v=pv, prefix_len=plen, scale=attn.scale, lse=lse)
         lses.append(lse)
@@ -190,13 +197,17 @@ def block_backward(blk: nn.Module, s: BlockSaved, dy: torch.Tensor, grads: Dict[
     for c, lse in zip(s.calls, s.lse):
         stride = c.stride or c.seg_len
         r1 = c.q_row0 + (c.batch - 1) * stride + c.seg_len
-        if c.prefix is not None and c.prefix.length > 0:
-            raise NotImplementedError("sailrecon_b200: training blocks with a K/V prefix are not wired up yet")
         if stride != c.seg_len:
             raise NotImplementedError("sailrecon_b200: training attention calls must cover their rows densely")
         sl = slice(c.q_row0, r1)
+        kw = {}
+        if c.prefix is not None and c.prefix.length > 0:
+            n = c.prefix.length
+            s.dprefix = torch.zeros(n, 3 * C, dtype=BF, device=dev)                # q third stays zero (scene rows are K/V only)
+            kw = dict(prefix_k=c.prefix.k[:n], prefix_v=c.prefix.v[:n], prefix_len=n, dprefix_k=s.dprefix[:, C:2 * C],
+                      dprefix_v=s.dprefix[:, 2 * C:])
         ops.attention_bwd(q[sl], k[sl], v[sl], s.o[sl], do[sl], lse, dq[sl], dk[sl], dv[sl], H, d, c.batch, c.seg_len, c.seg_len,
-                          stride, stride, scale=attn.scale)
+                          stride, stride, scale=attn.scale, **kw)
         covered += r1 - c.q_row0
     if covered != T:
         raise ValueError("sailrecon_b200: the attention calls of a training block must cover every row exactly once")
@@ -210,3 +221,115 @@ def block_backward(blk: nn.Module, s: BlockSaved, dy: torch.Tensor, grads: Dict[
     w1, _, eps1 = engine.ln_params(blk.norm1)
     ops.layernorm_bwd(s.x, w1, dh1, dx, _acc(grads, blk.norm1.weight), _acc(grads, blk.norm1.bias), eps1)
     return dx
+
+
+# ------------------------------------------------------------------------------------------------ scene-token path
+@dataclass
+class SceneSaved:
+    idx: torch.Tensor                  # int32 [Ns] rows of the anchor stream
+    a_s: torch.Tensor                  # norm1(X[idx]) bf16 [Ns, C]
+    raw: torch.Tensor                  # qkv Linear on a_s, bf16 [Ns, 3C] (the q third is computed but never attended)
+    post: torch.Tensor                 # after k norm + RoPE; k = post[:, C:2C], v = post[:, 2C:]
+    epi: Optional[ops.QkvEpilogue]
+
+
+def scene_forward_saving(rblk: nn.Module, X: torch.Tensor, idx: torch.Tensor, spos: engine.RowPositions) -> SceneSaved:
+    """Scene tokens of one layer (aggregator.py:351-360,593-626 + block.py:87 + attention.py:73-82 of the reloc block):
+    gather rows idx of the anchor stream X, norm1, qkv projection, k norm + RoPE.  Returns K/V in `post`."""
+    Ns = idx.numel()
+    C = X.shape[1]
+    dev = X.device
+    w1, b1, eps1 = engine.ln_params(rblk.norm1)
+    a_s = ops.layernorm(X, w1, b1, eps1, torch.empty(Ns, C, dtype=BF, device=dev), idx=idx)
+    raw = torch.empty(Ns, 3 * C, dtype=BF, device=dev)
+    ops.gemm(a_s, engine.weight_bf16(rblk.attn.qkv), engine.bias_for(rblk.attn.qkv, "bf16"), raw, kind=SR_EPI_BIAS)
+    epi = _qkv_epilogue(rblk.attn, spos, dev, Ns)
+    post = raw if epi is None else ops.qknorm_rope_fwd(raw, torch.empty_like(raw), epi)
+    return SceneSaved(idx, a_s, raw, post, epi)
+
+
+def scene_backward(rblk: nn.Module, s: SceneSaved, dprefix: torch.Tensor, X: torch.Tensor, dX: torch.Tensor,
+                   grads: Dict[nn.Parameter, torch.Tensor]) -> None:
+    """dprefix [Ns, 3C] bf16 (k / v thirds = gradient of the scene K / V, q third zero) -> dX[idx] += ... (fp32 anchor-stream
+    gradient) and the reloc block's norm1 / qkv / k_norm parameter gradients."""
+    attn = rblk.attn
+    Ns, C = s.a_s.shape
+    if s.epi is not None:
+        dqn = dkn = None
+        if s.epi.q_norm is not None:
+            dqn = (_acc(grads, attn.q_norm.weight), _acc(grads, attn.q_norm.bias))
+            dkn = (_acc(grads, attn.k_norm.weight), _acc(grads, attn.k_norm.bias))
+        ops.qknorm_rope_bwd(s.raw, dprefix, s.epi, dqn, dkn)
+    dh = linear_backward(attn.qkv, s.a_s, dprefix, grads)
+    xg = ops.gather_rows(X, s.idx, torch.empty(Ns, C, dtype=torch.float32, device=X.device))
+    tmp = torch.zeros(Ns, C, dtype=torch.float32, device=X.device)
+    w1, _, eps1 = engine.ln_params(rblk.norm1)
+    ops.layernorm_bwd(xg, w1, dh, tmp, _acc(grads, rblk.norm1.weight), _acc(grads, rblk.norm1.bias), eps1)
+    ops.scatter_add_rows(dX, s.idx, tmp)
+
+
+# ------------------------------------------------------------------------------------------------ one aggregator layer
+@dataclass
+class LayerCtx:
+    """Row structure of one scene: Na anchor frames then Nq query frames, P tokens each (aggregator.py:242-433)."""
+    Na: int
+    Nq: int
+    P: int
+    rows_pos: engine.RowPositions      # all (Na + Nq) * P rows
+
+    def __post_init__(self):
+        n = self.Na * self.P
+        self.pos_a = engine.RowPositions(self.rows_pos.pos32[:n], self.rows_pos.max_pos)
+        self.pos_q = engine.RowPositions(self.rows_pos.pos32[n:], self.rows_pos.max_pos)
+        self.frame_calls = engine.full_segments(self.Na + self.Nq, self.P)
+        self.global_calls = engine.full_segments(1, n)
+
+
+def layer_forward(fblk: nn.Module, gblk: nn.Module, rblk: nn.Module, X: torch.Tensor, ctx: LayerCtx, idx: torch.Tensor,
+                  spos: engine.RowPositions) -> torch.Tensor:
+    """One aggregator layer in place on X [(Na + Nq) P, C] with the inference kernels (aggregator.py:343-392): frame block on
+    every frame, scene K|V from rows idx of the anchors, reloc block on the queries, global block on the anchors.
+    Returns the copy of X after the frame block (the checkpoint the backward re-runs the reloc / global blocks from)."""
+    n = ctx.Na * ctx.P
+    C = X.shape[1]
+    engine.run_block(fblk, X, ctx.frame_calls, ctx.rows_pos, "bf16", tag="train.")
+    X_mid = X.clone()
+    Xa, Xq = X[:n], X[n:]
+    if ctx.Nq > 0:
+        Ns = idx.numel()
+        w1, b1, eps1 = engine.ln_params(rblk.norm1)
+        a_s = ops.layernorm(X, w1, b1, eps1, torch.empty(Ns, C, dtype=BF, device=X.device), idx=idx)
+        skv = torch.empty(Ns, 2 * C, dtype=BF, device=X.device)
+        engine.qkv_rows(rblk.attn, a_s, skv, "bf16", spos, col_offset=C)
+        pre = engine.Prefix(skv[:, :C], skv[:, C:], 0, Ns)
+        engine.run_block(rblk, Xq, [engine.AttnCall(0, ctx.Nq, ctx.P, ctx.P, pre)], ctx.pos_q, "bf16", tag="train.")
+    engine.run_block(gblk, Xa, ctx.global_calls, ctx.pos_a, "bf16", tag="train.")
+    return X_mid
+
+
+def layer_backward(fblk: nn.Module, gblk: nn.Module, rblk: nn.Module, X_in: torch.Tensor, X_mid: torch.Tensor, dX: torch.Tensor,
+                   ctx: LayerCtx, idx: torch.Tensor, spos: engine.RowPositions, grads: Dict[nn.Parameter, torch.Tensor],
+                   d_mid: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dX = gradient w.r.t. the layer output -> gradient w.r.t. the layer input.  X_in / X_mid are the checkpoints (layer
+    input, state after the frame block); d_mid is an extra gradient on the state after the frame block (the first half of
+    the [frame | global] concat the heads read, aggregator.py:403-413)."""
+    n = ctx.Na * ctx.P
+    Xa_mid, Xq_mid = X_mid[:n], X_mid[n:]
+    sg = block_forward_saving(gblk, Xa_mid, ctx.global_calls, ctx.pos_a)
+    dXa = block_backward(gblk, sg, dX[:n].contiguous(), grads)
+    del sg
+    if ctx.Nq > 0:
+        scene = scene_forward_saving(rblk, Xa_mid, idx, spos)
+        C = X_in.shape[1]
+        pre = engine.Prefix(scene.post[:, C:2 * C], scene.post[:, 2 * C:], 0, idx.numel())
+        sr = block_forward_saving(rblk, Xq_mid, [engine.AttnCall(0, ctx.Nq, ctx.P, ctx.P, pre)], ctx.pos_q)
+        dXq = block_backward(rblk, sr, dX[n:].contiguous(), grads)
+        scene_backward(rblk, scene, sr.dprefix, Xa_mid, dXa, grads)
+        del sr, scene
+        d_all = torch.cat([dXa, dXq])
+    else:
+        d_all = dXa
+    if d_mid is not None:
+        d_all += d_mid
+    sf = block_forward_saving(fblk, X_in, ctx.frame_calls, ctx.rows_pos)
+    return block_backward(fblk, sf, d_all, grads)

@@ -152,19 +152,28 @@ def test_linear_backward_on_tensor_cores():
 
 
 # ------------------------------------------------------------------------------------------------ whole block
-def _block_ref(P, x, pos, batch, L, H):
-    T, C = x.shape
+def _qkv_ref(P, h1, pos, H):
+    T, C = h1.shape
     d = C // H
-    h1 = F.layer_norm(x, (C,), P["norm1.weight"], P["norm1.bias"], 1e-5)
     qkv = h1 @ P["attn.qkv.weight"].t() + P["attn.qkv.bias"]
     q, k, v = (qkv[:, i * C:(i + 1) * C].reshape(T, H, d) for i in range(3))
     q = _rope_ref(F.layer_norm(q, (d,), P["attn.q_norm.weight"], P["attn.q_norm.bias"], 1e-5), pos)
     k = _rope_ref(F.layer_norm(k, (d,), P["attn.k_norm.weight"], P["attn.k_norm.bias"], 1e-5), pos)
+    return q, k, v
+
+
+def _block_ref(P, x, pos, batch, L, H, prefix=None):
+    """prefix = (k, v) [Ns, H, d] every segment also attends to (the scene tokens of the reloc block)."""
+    T, C = x.shape
+    d = C // H
+    h1 = F.layer_norm(x, (C,), P["norm1.weight"], P["norm1.bias"], 1e-5)
+    q, k, v = _qkv_ref(P, h1, pos, H)
     outs = []
     for b in range(batch):
         sl = slice(b * L, (b + 1) * L)
-        s = torch.einsum("qhd,khd->hqk", q[sl], k[sl]) * d ** -0.5
-        outs.append(torch.einsum("hqk,khd->qhd", torch.softmax(s, -1), v[sl]).reshape(L, C))
+        kk, vv = (k[sl], v[sl]) if prefix is None else (torch.cat([prefix[0], k[sl]]), torch.cat([prefix[1], v[sl]]))
+        s = torch.einsum("qhd,khd->hqk", q[sl], kk) * d ** -0.5
+        outs.append(torch.einsum("hqk,khd->qhd", torch.softmax(s, -1), vv).reshape(L, C))
     o = torch.cat(outs)
     x1 = x + P["ls1.gamma"] * (o @ P["attn.proj.weight"].t() + P["attn.proj.bias"])
     h2 = F.layer_norm(x1, (C,), P["norm2.weight"], P["norm2.bias"], 1e-5)
@@ -215,3 +224,60 @@ def test_block_forward_backward_matches_fp32_autograd(batch, L):
     for n, p in named.items():
         e = rel_l2(grads[p].cpu(), P[n].grad.cpu())
         assert e < 3e-2, (n, e)
+
+
+def _rand_block(seed):
+    from sailrecon_b200.layers import Block, RotaryPositionEmbedding2D
+    torch.manual_seed(seed)
+    blk = Block(1024, 16, qk_norm=True, rope=RotaryPositionEmbedding2D(frequency=100.0), init_values=0.01).to(DEV)
+    with torch.no_grad():
+        for n, p in blk.named_parameters():
+            if n.endswith("gamma"):
+                p.uniform_(0.3, 0.9)
+            elif "norm" in n and n.endswith("weight"):
+                p.uniform_(0.7, 1.3)
+            elif n.endswith("bias"):
+                p.uniform_(-0.1, 0.1)
+    return blk
+
+
+def test_aggregator_layer_forward_backward_matches_fp32_autograd():
+    """One aggregator layer (aggregator.py:343-392): frame block on 2 anchors + 2 queries, scene tokens gathered from the
+    anchors (35 rows each) -> K|V prefix of the reloc block on the queries, global block on the anchors; gradients w.r.t.
+    the layer input and all three blocks' parameters, incl. the path scene K/V -> k_norm / RoPE -> qkv -> norm1 -> gather."""
+    from sailrecon_b200 import engine, train
+    Na, Nq, Pn, H, C = 2, 2, 150, 16, 1024
+    S, n = Na + Nq, Na * Pn
+    fblk, gblk, rblk = _rand_block(31), _rand_block(32), _rand_block(33)
+    pos = _positions(S, Pn)
+    ctx = train.LayerCtx(Na, Nq, Pn, engine.RowPositions(pos.to(torch.int32).contiguous(), int(pos.max()) + 1))
+    gidx = torch.Generator().manual_seed(3)
+    idx = torch.cat([a * Pn + torch.cat([torch.arange(5), 5 + torch.randperm(Pn - 5, generator=gidx)[:30]]) for a in range(Na)])
+    idx_d = idx.to(torch.int32).to(DEV)
+    spos = engine.RowPositions(ctx.rows_pos.pos32[idx_d.long()].contiguous(), ctx.rows_pos.max_pos)
+    X0 = _randn(S * Pn, C, seed=34)
+    dY = _randn(S * Pn, C, seed=35)
+    d_mid = _randn(S * Pn, C, seed=36) * 0.5
+
+    X = X0.clone()
+    X_mid = train.layer_forward(fblk, gblk, rblk, X, ctx, idx_d, spos)
+    grads = {}
+    dX0 = train.layer_backward(fblk, gblk, rblk, X0, X_mid, dY, ctx, idx_d, spos, grads, d_mid=d_mid)
+    torch.cuda.synchronize()
+
+    Pf, Pg, Pr = ({k: p.detach().clone().requires_grad_(True) for k, p in b.named_parameters()} for b in (fblk, gblk, rblk))
+    xr = X0.clone().requires_grad_(True)
+    mid = _block_ref(Pf, xr, pos, S, Pn, H)
+    ya = _block_ref(Pg, mid[:n], pos[:n], 1, n, H)
+    hs = F.layer_norm(mid[idx.to(DEV)], (C,), Pr["norm1.weight"], Pr["norm1.bias"], 1e-5)
+    _, sk, sv = _qkv_ref(Pr, hs, pos[idx.to(DEV)], H)
+    yq = _block_ref(Pr, mid[n:], pos[n:], Nq, Pn, H, prefix=(sk, sv))
+    y_ref = torch.cat([ya, yq])
+    ((y_ref * dY).sum() + (mid * d_mid).sum()).backward()
+    assert rel_l2(X.cpu(), y_ref.detach().cpu()) < 2e-2
+    assert rel_l2(X_mid.cpu(), mid.detach().cpu()) < 2e-2
+    assert rel_l2(dX0.cpu(), xr.grad.cpu()) < 2e-2
+    for blk, Pref, tag in ((fblk, Pf, "frame"), (gblk, Pg, "global"), (rblk, Pr, "reloc")):
+        for name, p in blk.named_parameters():
+            e = rel_l2(grads[p].cpu(), Pref[name].grad.cpu())
+            assert e < 3e-2, (tag, name, e)
