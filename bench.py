@@ -17,6 +17,9 @@ need 170 GB here; the structured prefix + own-frame attention does not build it)
 Workload "scene": ONE scene of 256 + 256 frames (N = 512) sharded by frame over the ranks, full aggregator + camera head
 (parallel.sharded_scene_forward); strong scaling.
 Workload "ring" (BASELINE.json configs[3]): the sequence-sharded global-attention stack, see parallel.py.
+Workload "train" (BASELINE.json configs[4]): one training step of the 3 x 24 aggregator blocks on a 24-frame scene
+(12 anchors + 12 queries, train_imc.py shape): zero_grad, checkpointed forward, backward, per-layer NCCL gradient
+all-reduce across the ranks (one scene per rank, DDP's decomposition), Adam — see sailrecon_b200/train.py.
 
 --impl reference: the reference's CPU path restated by the oracle (oracle/sailrecon_oracle.py; the Python reference
 itself cannot travel to the GPU box) timed on the host cores on a bounded sample of the same workload.
@@ -230,13 +233,166 @@ def ncu_traffic(kernel, S, H):
     return rec["bytes_per_launch_mean"]
 
 
+# ------------------------------------------------------------------------------------------------ training step (configs[4])
+def bench_train(args, rank: int, world: int, local: int) -> None:
+    """BASELINE.json configs[4]: forward + backward of the aggregator blocks at 24 frames, bf16 autocast arithmetic, one
+    scene per rank, gradients all-reduced over NCCL (DDP semantics of train_imc.py:472), Adam (train_imc.py:475).
+    The loss is linear in the outputs the heads read: L = sum_i <output_dict[i], G_i> for i in {4, 11, 17, 23} (both
+    halves of the [frame | global] concat, aggregator.py:403-413) plus the anchors' camera tokens of the last layer, with
+    fixed random G_i — so the gradient entering the stack is dense on exactly the rows the reference's heads touch.
+    value: token rows of the scene resident in HBM (DINOv2 patch embed run once, outside the timed region).
+    e2e:   host images -> H2D -> DINOv2 patch embed (inference kernels, no gradient) -> the same step -> loss read back."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a B200: sailrecon_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from sailrecon_b200 import engine, ops, train
+    from sailrecon_b200.engine import RowPositions
+
+    S = args.frames if args.frames != 32 else 24
+    Na = Nq = S // 2
+    H = W = args.size
+    agg, _ = build_models(dev)
+    psi = agg.patch_start_idx
+    h, w = H // PATCH, W // PATCH
+    hw, P = h * w, psi + h * w
+    T = S * P
+    l_prime = min(300, hw)
+    state = train.TrainState(agg, lr=1e-5)
+    rows_pos, frame_pos_cpu = agg._positions(S, h, w, dev)
+    ctx = train.LayerCtx(Na, Nq, P, rows_pos)
+    host_images = torch.rand(1, S, 3, H, W, generator=torch.Generator().manual_seed(1 + rank)).pin_memory()
+
+    def tokens_from(images):
+        """aggregator.py:267-299: patch embed + special tokens -> the fp32 token rows the block stacks start from."""
+        X = torch.empty(T, C, dtype=torch.float32, device=dev)
+        with torch.no_grad():
+            agg._embed(images[0].contiguous(), "bf16", X, S, P, C)
+            X.view(S, P, C)[:, :psi] = agg._special_rows(list(range(S)), set(range(Na, S)), False)
+        return X
+
+    def draw_scene():
+        idx, spos, _ = agg._scene_rows(Na, P, hw, l_prime, frame_pos_cpu, dev)
+        return idx, RowPositions(spos, rows_pos.max_pos)
+
+    g = torch.Generator(device=dev).manual_seed(7 + rank)
+    d_out = {}
+    for i in agg.intermediate_layer_idx:
+        a = torch.randn(T, C, device=dev, generator=g) * 1e-3
+        b = torch.randn(T, C, device=dev, generator=g) * 1e-3
+        a[:Na * P] = 0                                                  # the heads read query rows only (aggregator.py:404-413)
+        b[:Na * P] = 0
+        if i == agg.depth - 1:                                          # ... and the anchors' camera token of the last layer (:414-423)
+            a.view(S, P, C)[:Na, 0] = torch.randn(Na, C, device=dev, generator=g) * 1e-3
+            b.view(S, P, C)[:Na, 0] = torch.randn(Na, C, device=dev, generator=g) * 1e-3
+        d_out[i] = (a, b)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    X0 = tokens_from(host_images.to(dev))
+    for _ in range(args.warmup):
+        agg.generator.manual_seed(1234)
+        train.training_step(agg, state, X0, ctx, draw_scene, d_out, world)
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    ops.PROFILE = []
+    launches0 = ops.num_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        agg.generator.manual_seed(1234)
+        dX0 = train.training_step(agg, state, X0, ctx, draw_scene, d_out, world)
+    e1.record()
+    barrier()
+    launches = ops.num_kernel_launches() - launches0
+    records, ops.PROFILE = ops.PROFILE, None
+    clk = clocks.stop()
+    ms = e0.elapsed_time(e1)
+    finite = bool(torch.isfinite(dX0).all()) and all(bool(torch.isfinite(p).all()) for p in state.param)
+
+    barrier()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(args.steps):
+        agg.generator.manual_seed(1234)
+        Xs = tokens_from(host_images.to(dev, non_blocking=True))
+        dX0 = train.training_step(agg, state, Xs, ctx, draw_scene, d_out, world)
+        host_loss = dX0.view(-1)[:1024].sum().cpu()                    # the step's scalar read-back (stands in for loss.item())
+    t1.record()
+    barrier()
+    ms_e2e = t0.elapsed_time(t1)
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(tt[0]), float(tt[1])
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        peak_tf = peaks.get("bf16_tflops_sustained", 1400.0)
+        peak_src = "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if peaks else "fallback (B200_PROFILING.md sustained ~1.4 PF)"
+        prof = summarize_profile(records)
+        top = max((k for k in prof if prof[k]["flops"] > 0), key=lambda k: prof[k]["ms"])
+        d = prof[top]
+        achieved = d["flops"] / (d["ms"] * 1e-3) / 1e12
+        kern = {k: {"launches_per_step": v["launches"] // args.steps, "ms_per_step": v["ms"] / args.steps,
+                    "tflops": (v["flops"] / (v["ms"] * 1e-3) / 1e12) if v["flops"] else None,
+                    "gbs": v["bytes"] / (v["ms"] * 1e-3) / 1e9} for k, v in prof.items()}
+        fl = algorithmic_flops(Na, Nq, H, W)
+        Pp = psi + l_prime
+        lin = DEPTH * (S * P * 24 * C * C + Nq * P * 24 * C * C + Na * P * 24 * C * C + Na * Pp * 2 * C * 2 * C)
+        att = DEPTH * (S * 4 * P * P * C + 4 * (Na * P) ** 2 * C + Nq * 4 * P * (Na * Pp + P) * C)
+        # forward + backward without the recompute: Linear 3x (y, dX, dW), attention 1 + 2.5 (QK^T, PV | S, dP, dV, dK, dQ)
+        alg = 3.0 * lin + 3.5 * att
+        executed = 4.0 * lin + 4.5 * att                               # + the checkpoint re-run inside the backward
+        step_s = ms * 1e-3 / args.steps
+        nparam = sum(int(x.numel()) for x in state.param)
+        line = {
+            "metric": f"aggregator-blocks training step (forward+backward+Adam) frames/s at N={S} ({H}px)",
+            "value": world * S / step_s, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic",
+            "config": {"workload": f"train{S}: {Na} anchors + {Nq} queries, {H}x{W}, fix_rank 300, 24x(frame, global, reloc) blocks "
+                                   "forward (per-block checkpoints as aggregator.py:654-657) + backward + Adam, fp32 master "
+                                   "weights and gradients, one scene per GPU, per-layer gradient all-reduce (NCCL sum) overlapped "
+                                   "with the backward; linear synthetic loss on output_dict[4,11,17,23] + last-layer camera tokens",
+                       "l2": "activations per block (135 MB residual + 203 MB qkv + 2 x 270 MB MLP hidden) exceed the 126 MB L2; no flush needed",
+                       "trainable_params": nparam, "allreduce_bytes_per_step": 4 * nparam if world > 1 else 0},
+            "e2e": {"value": world * S / (ms_e2e * 1e-3 / args.steps), "unit": UNIT,
+                    "h2d_bytes_per_step": host_images.numel() * 4, "d2h_bytes_per_step": 4,
+                    "includes": "H2D of the images, DINOv2 patch embed forward (no gradient), the training step, scalar read-back"},
+            "gpu_launches": launches, "clocks": clk,
+            "roofline": {"bound": "tensor", "kernel": top, "achieved": achieved, "peak": peak_tf, "unit": "TFLOP/s",
+                         "frac": achieved / peak_tf, "traffic": None, "peak_source": peak_src,
+                         "launches_per_step": d["launches"] // args.steps},
+            "kernels": kern,
+            "algorithmic_tflop_per_step": alg / 1e12, "executed_tflop_per_step_with_recompute": executed / 1e12,
+            "tensor_frac_whole_step": alg / step_s / 1e12 / peak_tf,
+            "tensor_frac_whole_step_with_recompute": executed / step_s / 1e12 / peak_tf,
+            "outputs_finite": finite,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="agg32", choices=["agg32", "imc", "ring", "scene"])
+    ap.add_argument("--workload", default="agg32", choices=["agg32", "imc", "ring", "scene", "train"])
     ap.add_argument("--anchors", type=int, default=100, help="workload imc: anchor frames (build the scene tokens)")
     ap.add_argument("--queries", type=int, default=200, help="workload imc: query frames localised against the anchors")
     ap.add_argument("--frames", type=int, default=32)
@@ -260,6 +416,9 @@ def main():
         if args.anchors == 100 and args.queries == 200:      # defaults of --workload imc; scene defaults to N = 512
             args.anchors = args.queries = 256
         parallel.bench_scene(args, rank, world, local)
+        return
+    if args.workload == "train":
+        bench_train(args, rank, world, local)
         return
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a B200: sailrecon_b200 has no CPU fallback (use --impl reference for the CPU arm)")

@@ -186,6 +186,12 @@ int sr_qknorm_rope_bwd(const void* raw, int64_t ldr, void* dqkv, int64_t ldd, co
 int sr_scatter_add_rows_f32(float* dst, int64_t ldd, const int32_t* idx, const float* src, int64_t lds, int64_t n, int64_t C,
                             void* stream);
 
+/* torch.optim.Adam(betas, eps) as train/train_imc.py:475 configures it (no weight decay, no amsgrad), one step on a flat
+ * fp32 bucket of n parameters (n % 4 == 0, 16-byte aligned): g *= grad_scale; m = b1 m + (1 - b1) g; v = b2 v + (1 - b2) g^2;
+ * p -= lr / (1 - b1^step) * m / (sqrt(v) / sqrt(1 - b2^step) + eps).  step counts from 1.                         */
+int sr_adam_step_f32(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                     float beta2, float eps, int64_t step, float grad_scale, void* stream);
+
 /* ---- token re-layout (aggregator.py:355-357,393-399,406-423,603-625) ----------------------------------- */
 /* dst[i, :] = src[idx[i], :] for i < n; fp32 rows of C elements; idx int32 (scene-token selection).       */
 int sr_gather_rows_f32(const float* src, int64_t lds, const int32_t* idx, float* dst, int64_t ldd, int64_t n,

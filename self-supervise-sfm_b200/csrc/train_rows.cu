@@ -8,6 +8,7 @@
 //   sr_layernorm_bwd       dx += LN'(dy), dw += ..., db += ...           (block.py:87-91 norm1 / norm2)
 //   sr_qknorm_rope_fwd/bwd per-head LayerNorm(64) + 2D RoPE on the q, k thirds of a [M, 3C] bf16 buffer
 //                          (attention.py:78-82) and its gradient, in place
+//   sr_adam_step_f32       torch.optim.Adam update (train/train_imc.py:475,381) on one flat fp32 parameter bucket
 #include "common.cuh"
 #include "sr_internal.h"
 
@@ -307,6 +308,35 @@ scatter_add_rows_kernel(float* __restrict__ dst, int64_t ldd, const int32_t* __r
   *reinterpret_cast<float4*>(o) = t;
 }
 
+
+// ------------------------------------------------------------------------------------------------ Adam
+// torch.optim.Adam (betas, eps, no weight decay, no amsgrad; train_imc.py:475) on a flat bucket: 16 B read + 12 B written
+// per parameter, float4 lanes, grid-stride over a grid of 148 x 8 CTAs.  g is multiplied by grad_scale first (1 / world
+// after a sum all-reduce, or the GradScaler's 1 / scale, train_imc.py:380-381).
+__global__ void __launch_bounds__(256)
+adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n4,
+                 float step_size, float beta1, float beta2, float eps, float inv_sqrt_bc2, float grad_scale) {
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    float4 pp = reinterpret_cast<float4*>(p)[i];
+    const float4 gg = reinterpret_cast<const float4*>(g)[i];
+    float4 mm = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    auto upd = [&](float& pe, float ge, float& me, float& ve) {
+      ge *= grad_scale;
+      me = beta1 * me + (1.f - beta1) * ge;
+      ve = beta2 * ve + (1.f - beta2) * ge * ge;
+      pe -= step_size * me / (sqrtf(ve) * inv_sqrt_bc2 + eps);
+    };
+    upd(pp.x, gg.x, mm.x, vv.x);
+    upd(pp.y, gg.y, mm.y, vv.y);
+    upd(pp.z, gg.z, mm.z, vv.z);
+    upd(pp.w, gg.w, mm.w, vv.w);
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+}
+
 }  // namespace sr
 
 using namespace sr;
@@ -445,6 +475,24 @@ extern "C" int sr_scatter_add_rows_f32(float* dst, int64_t ldd, const int32_t* i
   const int64_t n4 = n * C / 4;
   scatter_add_rows_kernel<<<static_cast<unsigned>((n4 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       dst, ldd, idx, src, lds, n, static_cast<int>(C));
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_adam_step_f32(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                                float beta2, float eps, int64_t step, float grad_scale, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(param && grad && exp_avg && exp_avg_sq && n > 0 && n % 4 == 0 && step >= 1, "sr_adam_step_f32: bad arguments (n % 4 == 0, step >= 1)");
+  SR_REQUIRE(((reinterpret_cast<uintptr_t>(param) | reinterpret_cast<uintptr_t>(grad) | reinterpret_cast<uintptr_t>(exp_avg) |
+               reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15) == 0, "sr_adam_step_f32: buffers must be 16-byte aligned");
+  const double bc1 = 1.0 - pow(static_cast<double>(beta1), static_cast<double>(step));
+  const double bc2 = 1.0 - pow(static_cast<double>(beta2), static_cast<double>(step));
+  const int64_t n4 = n / 4;
+  const int64_t want = (n4 + 255) / 256;
+  const unsigned grid = static_cast<unsigned>(want < 148 * 8 ? want : 148 * 8);
+  adam_step_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(param, grad, exp_avg, exp_avg_sq, n4,
+                                                                             static_cast<float>(lr / bc1), beta1, beta2, eps,
+                                                                             static_cast<float>(1.0 / sqrt(bc2)), grad_scale);
   SR_LAUNCHED();
   return SR_OK;
 }

@@ -386,6 +386,19 @@ def scatter_add_rows(dst: torch.Tensor, idx: torch.Tensor, src: torch.Tensor) ->
     return dst
 
 
+def adam_step(param: torch.Tensor, grad: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor, lr: float, step: int,
+              betas=(0.9, 0.999), eps: float = 1e-8, grad_scale: float = 1.0) -> None:
+    """torch.optim.Adam step (train/train_imc.py:475) in place on flat contiguous fp32 buffers of equal length."""
+    n = param.numel()
+    for t, name in ((param, "param"), (grad, "grad"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq")):
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == n):
+            raise ValueError(f"sailrecon_b200: adam_step {name} must be a contiguous fp32 CUDA buffer of {n} elements")
+    t = _Timed("adam", 0.0, 28.0 * n)
+    _lib.check(_lib.load().sr_adam_step_f32(param.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), n, lr,
+                                            betas[0], betas[1], eps, step, grad_scale, _stream()), "adam_step")
+    t.done()
+
+
 def qknorm_rope_fwd(raw: torch.Tensor, out: torch.Tensor, qkv: QkvEpilogue) -> torch.Tensor:
     _rows2d(raw, torch.bfloat16, "raw")
     _rows2d(out, torch.bfloat16, "out")

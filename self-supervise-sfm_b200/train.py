@@ -333,3 +333,119 @@ def layer_backward(fblk: nn.Module, gblk: nn.Module, rblk: nn.Module, X_in: torc
         d_all += d_mid
     sf = block_forward_saving(fblk, X_in, ctx.frame_calls, ctx.rows_pos)
     return block_backward(fblk, sf, d_all, grads)
+
+
+# ------------------------------------------------------------------------------------------------ the 3 x depth block stack
+class TrainState:
+    """Optimizer-side state of the aggregator's block stacks (frame / global / global_reloc, aggregator.py:99-149), one flat
+    fp32 bucket per layer index i holding the parameters of frame_blocks[i], global_blocks[i] and global_reloc_blocks[i]:
+
+        param  the modules' parameters are re-pointed into it (p.data = view), so the Adam kernel updates them in place
+        grad   what DDP's bucket is in the reference (train_imc.py:472): block_backward accumulates into views of it and
+               ONE all-reduce per layer runs on it while the backward of the next (lower) layer computes
+        m, v   Adam moments (train_imc.py:475: Adam(lr, betas=(0.9, 0.999), eps=1e-8))
+
+    ~37.8 M parameters per layer, 4 x 151 MB; 14.5 GB for the 24 layers."""
+
+    def __init__(self, agg: nn.Module, lr: float = 1e-5, betas=(0.9, 0.999), eps: float = 1e-8):
+        self.lr, self.betas, self.eps, self.step = lr, betas, eps, 0
+        self.param: List[torch.Tensor] = []
+        self.grad: List[torch.Tensor] = []
+        self.m: List[torch.Tensor] = []
+        self.v: List[torch.Tensor] = []
+        self.grads: Dict[nn.Parameter, torch.Tensor] = {}
+        self.params_of_layer: List[List[nn.Parameter]] = []
+        for i in range(agg.depth):
+            ps = [p for blk in (agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i]) for p in blk.parameters()]
+            offs, n = [], 0
+            for p in ps:
+                offs.append(n)
+                n += (p.numel() + 63) // 64 * 64                                       # 256-byte aligned views
+            dev = ps[0].device
+            flat = torch.zeros(n, dtype=torch.float32, device=dev)
+            g = torch.zeros(n, dtype=torch.float32, device=dev)
+            with torch.no_grad():
+                for p, o in zip(ps, offs):
+                    view = flat[o:o + p.numel()].view(p.shape)
+                    view.copy_(p.detach())
+                    p.data = view
+                    self.grads[p] = g[o:o + p.numel()].view(p.shape)
+            self.param.append(flat)
+            self.grad.append(g)
+            self.m.append(torch.zeros_like(flat))
+            self.v.append(torch.zeros_like(flat))
+            self.params_of_layer.append(ps)
+
+    def zero_grad(self) -> None:
+        for g in self.grad:
+            g.zero_()
+
+    def adam_step(self, grad_scale: float = 1.0) -> None:
+        self.step += 1
+        for i in range(len(self.param)):
+            ops.adam_step(self.param[i], self.grad[i], self.m[i], self.v[i], self.lr, self.step, self.betas, self.eps, grad_scale)
+            for p in self.params_of_layer[i]:
+                torch.autograd.graph.increment_version(p)                             # engine's bf16 weight copies are stale now
+
+
+def stack_forward(agg: nn.Module, X: torch.Tensor, ctx: LayerCtx, draw_scene) -> list:
+    """The 24 aggregator layers (aggregator.py:339-423) in place on X with the inference kernels, keeping per layer what
+    torch.utils.checkpoint keeps in the reference (the block inputs: layer input and the state after the frame block) plus
+    that layer's scene-token draw.  draw_scene() -> (idx int32 [Na P'], RowPositions) is called once per layer, in order."""
+    ck = []
+    for i in range(agg.depth):
+        X_in = X.clone()
+        idx, spos = draw_scene()
+        X_mid = layer_forward(agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i], X, ctx, idx, spos)
+        ck.append((X_in, X_mid, idx, spos))
+    return ck
+
+
+def stack_backward(agg: nn.Module, ck: list, d_out: Dict[int, tuple], ctx: LayerCtx, grads: Dict[nn.Parameter, torch.Tensor],
+                   on_layer_done=None) -> torch.Tensor:
+    """Backward through the 24 layers.  d_out[i] = (d_frame_half, d_global_half), each fp32 [T, C] or None: the loss gradient
+    on the state after layer i's frame block and after the whole layer (the two halves of output_dict[i],
+    aggregator.py:403-413; the last layer's anchor rows carry the camera-token gradient, :414-423).  Checkpoints are
+    released layer by layer; on_layer_done(i) runs when layer i's parameter gradients are complete."""
+    dX = None
+    for i in reversed(range(agg.depth)):
+        X_in, X_mid, idx, spos = ck[i]
+        d_mid, d_post = d_out.get(i, (None, None))
+        if dX is None:
+            dX = torch.zeros_like(X_in) if d_post is None else d_post.clone()
+        elif d_post is not None:
+            dX += d_post
+        dX = layer_backward(agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i], X_in, X_mid, dX, ctx, idx, spos,
+                            grads, d_mid=d_mid)
+        ck[i] = None
+        if on_layer_done is not None:
+            on_layer_done(i)
+    return dX
+
+
+def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: LayerCtx, draw_scene, d_out: Dict[int, tuple],
+                  world: int = 1, fwd_bwd=None, optimizer_step=None) -> torch.Tensor:
+    """zero_grad + forward + backward + gradient all-reduce + Adam for the block stacks on one scene per rank
+    (train_imc.py:361-381 with DDP, :472).  The all-reduce of layer i's bucket (sum; the 1 / world of DDP's mean is
+    folded into the Adam kernel) is issued as soon as layer i's backward is enqueued and overlaps the layers below it.
+    Returns the gradient w.r.t. X0 (what would flow on into the patch embed).
+    fwd_bwd(on_layer_done) -> dX0 and optimizer_step(grad_scale) replace the CUDA kernels in the CPU (gloo) tests of this
+    schedule; the product path leaves them None."""
+    import torch.distributed as dist
+    state.zero_grad()
+    works = []
+
+    def reduce_layer(i):
+        if world > 1:
+            works.append(dist.all_reduce(state.grad[i], op=dist.ReduceOp.SUM, async_op=True))
+
+    if fwd_bwd is None:
+        X = X0.clone()
+        ck = stack_forward(agg, X, ctx, draw_scene)
+        dX0 = stack_backward(agg, ck, d_out, ctx, state.grads, reduce_layer)
+    else:
+        dX0 = fwd_bwd(reduce_layer)
+    for w in works:
+        w.wait()
+    (optimizer_step or state.adam_step)(grad_scale=1.0 / world)
+    return dX0
