@@ -169,10 +169,12 @@ int sr_ls_residual_f32(const float* resid, const void* z, const float* gamma, fl
 /* mlp.py:36 on the saved pre-activation u (bf16): g = gelu_erf(u);  du = dg * gelu'(u)                         */
 int sr_gelu_fwd_bf16(const void* u, void* out, int64_t n, void* stream);
 int sr_gelu_bwd_bf16(const void* u, const void* dg, void* du, int64_t n, void* stream);
-/* LayerNorm gradient (block.py norm1 / norm2, C = 1024): dx += dLN(dy) (dx fp32 holds the residual-path gradient
- * already), dweight / dbias (fp32 [C], accumulated with atomics; NULL = skip).  x fp32, dy bf16.                */
-int sr_layernorm_bwd(const float* x, int64_t ldx, const float* weight, const void* dy, int64_t lddy, float* dx, int64_t lddx,
-                     float* dweight, float* dbias, int64_t rows, int64_t C, float eps, void* stream);
+/* LayerNorm gradient (block.py norm1 / norm2, C = 1024): dx = dres + dLN(dy), where dres (fp32) is the gradient arriving
+ * over the residual connection (NULL = dx itself, i.e. dx += dLN(dy); dres may alias dx); dweight / dbias (fp32 [C],
+ * accumulated with atomics; NULL = skip).  x fp32, dy bf16.                                                         */
+int sr_layernorm_bwd(const float* x, int64_t ldx, const float* weight, const void* dy, int64_t lddy, const float* dres,
+                     int64_t lddres, float* dx, int64_t lddx, float* dweight, float* dbias, int64_t rows, int64_t C, float eps,
+                     void* stream);
 /* attention.py:78-82 on a saved raw qkv buffer (bf16 [M, 3C], the qkv Linear's rounded output): per-head
  * LayerNorm(64) + 2D RoPE on q and k, v copied — the un-fused form of SR_EPI_QKV (fields qkv_dim, head_dim,
  * qk_norm, q/k norm parameters, qk_eps, rope tables, pos of `qkv` are read).  _bwd turns the gradient w.r.t. the
@@ -189,8 +191,8 @@ int sr_scatter_add_rows_f32(float* dst, int64_t ldd, const int32_t* idx, const f
 /* torch.optim.Adam(betas, eps) as train/train_imc.py:475 configures it (no weight decay, no amsgrad), one step on a flat
  * fp32 bucket of n parameters (n % 4 == 0, 16-byte aligned): g *= grad_scale; m = b1 m + (1 - b1) g; v = b2 v + (1 - b2) g^2;
  * p -= lr / (1 - b1^step) * m / (sqrt(v) / sqrt(1 - b2^step) + eps).  step counts from 1.                         */
-int sr_adam_step_f32(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
-                     float beta2, float eps, int64_t step, float grad_scale, void* stream);
+int sr_adam_step_f32(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr, double beta1,
+                     double beta2, double eps, int64_t step, double grad_scale, void* stream);
 
 /* ---- token re-layout (aggregator.py:355-357,393-399,406-423,603-625) ----------------------------------- */
 /* dst[i, :] = src[idx[i], :] for i < n; fp32 rows of C elements; idx int32 (scene-token selection).       */

@@ -84,11 +84,11 @@ SIGNATURES = {
     "sr_ls_residual_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _vp]),
     "sr_gelu_fwd_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
     "sr_gelu_bwd_bf16": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
-    "sr_layernorm_bwd": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _f32, _vp]),
+    "sr_layernorm_bwd": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _f32, _vp]),
     "sr_qknorm_rope_fwd": (C.c_int, [_vp, _i64, _vp, _i64, C.POINTER(SrEpilogue), _i64, _vp]),
     "sr_qknorm_rope_bwd": (C.c_int, [_vp, _i64, _vp, _i64, C.POINTER(SrEpilogue), _vp, _vp, _vp, _vp, _i64, _vp]),
     "sr_scatter_add_rows_f32": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _vp]),
-    "sr_adam_step_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _i64, _f32, _vp]),
+    "sr_adam_step_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, C.c_double, C.c_double, C.c_double, C.c_double, _i64, C.c_double, _vp]),
     "sr_gather_rows_f32": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _vp]),
     "sr_copy_cols_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp]),
     "sr_cast_f32_to_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _vp]),

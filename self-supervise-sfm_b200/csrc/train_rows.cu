@@ -121,13 +121,13 @@ gelu_kernel(const __nv_bfloat16* __restrict__ u, const __nv_bfloat16* __restrict
 }
 
 // ------------------------------------------------------------------------------------------------ LayerNorm backward
-// One warp per row, lane holds columns {128 i + 4 lane .. +3}, i < NCH (C = 128 NCH).  dx += rstd * (g - mean(g) -
+// One warp per row, lane holds columns {128 i + 4 lane .. +3}, i < NCH (C = 128 NCH).  dx = dres + rstd * (g - mean(g) -
 // xhat * mean(g * xhat)) with g = dy * w; per-block partial dw / db reduced through shared memory, then atomics.
 template <int NCH>
 __global__ void __launch_bounds__(256)
 layernorm_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, const __nv_bfloat16* __restrict__ dy,
-                     int64_t lddy, float* __restrict__ dx, int64_t lddx, float* __restrict__ dw, float* __restrict__ db, int rows,
-                     int rows_per_block, float eps) {
+                     int64_t lddy, const float* dres, int64_t lddres, float* dx, int64_t lddx, float* __restrict__ dw,
+                     float* __restrict__ db, int rows, int rows_per_block, float eps) {
   constexpr int C = NCH * 128;
   __shared__ float red[8][C];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -172,7 +172,7 @@ layernorm_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __re
 #pragma unroll
     for (int i = 0; i < NCH; ++i) {
       float* o = dx + static_cast<int64_t>(r) * lddx + i * 128 + lane * 4;
-      float4 v = *reinterpret_cast<float4*>(o);
+      float4 v = *reinterpret_cast<const float4*>(dres + static_cast<int64_t>(r) * lddres + i * 128 + lane * 4);   // may alias o
       v.x += rstd * (gv[4 * i] - mg - xv[4 * i] * mgx);
       v.y += rstd * (gv[4 * i + 1] - mg - xv[4 * i + 1] * mgx);
       v.z += rstd * (gv[4 * i + 2] - mg - xv[4 * i + 2] * mgx);
@@ -315,7 +315,7 @@ scatter_add_rows_kernel(float* __restrict__ dst, int64_t ldd, const int32_t* __r
 // after a sum all-reduce, or the GradScaler's 1 / scale, train_imc.py:380-381).
 __global__ void __launch_bounds__(256)
 adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, int64_t n4,
-                 float step_size, float beta1, float beta2, float eps, float inv_sqrt_bc2, float grad_scale) {
+                 float step_size, float beta1, float beta2, float omb1, float omb2, float eps, float inv_sqrt_bc2, float grad_scale) {
   for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
     float4 pp = reinterpret_cast<float4*>(p)[i];
     const float4 gg = reinterpret_cast<const float4*>(g)[i];
@@ -323,8 +323,8 @@ adam_step_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
     float4 vv = reinterpret_cast<float4*>(v)[i];
     auto upd = [&](float& pe, float ge, float& me, float& ve) {
       ge *= grad_scale;
-      me = beta1 * me + (1.f - beta1) * ge;
-      ve = beta2 * ve + (1.f - beta2) * ge * ge;
+      me = beta1 * me + omb1 * ge;                     // omb = 1 - beta evaluated in double on the host, as torch does
+      ve = beta2 * ve + omb2 * ge * ge;
       pe -= step_size * me / (sqrtf(ve) * inv_sqrt_bc2 + eps);
     };
     upd(pp.x, gg.x, mm.x, vv.x);
@@ -416,16 +416,18 @@ extern "C" int sr_gelu_bwd_bf16(const void* u, const void* dg, void* du, int64_t
   return SR_OK;
 }
 
-extern "C" int sr_layernorm_bwd(const float* x, int64_t ldx, const float* weight, const void* dy, int64_t lddy, float* dx,
-                                int64_t lddx, float* dweight, float* dbias, int64_t rows, int64_t C, float eps, void* stream) {
+extern "C" int sr_layernorm_bwd(const float* x, int64_t ldx, const float* weight, const void* dy, int64_t lddy, const float* dres,
+                                int64_t lddres, float* dx, int64_t lddx, float* dweight, float* dbias, int64_t rows, int64_t C,
+                                float eps, void* stream) {
   if (int rc = require_sm100()) return rc;
   SR_REQUIRE(x && dy && dx && rows > 0, "sr_layernorm_bwd: null pointer / empty");
   SR_REQUIRE(C == 1024, "sr_layernorm_bwd: C must be 1024 (got %lld)", static_cast<long long>(C));
-  SR_REQUIRE(ldx % 4 == 0 && lddy % 4 == 0 && lddx % 4 == 0, "sr_layernorm_bwd: row strides must be multiples of 4");
+  if (dres == nullptr) { dres = dx; lddres = lddx; }
+  SR_REQUIRE(ldx % 4 == 0 && lddy % 4 == 0 && lddx % 4 == 0 && lddres % 4 == 0, "sr_layernorm_bwd: row strides must be multiples of 4");
   const int rows_per_block = 64;
   layernorm_bwd_kernel<8><<<static_cast<unsigned>((rows + rows_per_block - 1) / rows_per_block), 256, 0,
                             reinterpret_cast<cudaStream_t>(stream)>>>(x, ldx, weight, reinterpret_cast<const __nv_bfloat16*>(dy), lddy,
-                                                                      dx, lddx, dweight, dbias, static_cast<int>(rows),
+                                                                      dres, lddres, dx, lddx, dweight, dbias, static_cast<int>(rows),
                                                                       rows_per_block, eps);
   SR_LAUNCHED();
   return SR_OK;
@@ -479,20 +481,23 @@ extern "C" int sr_scatter_add_rows_f32(float* dst, int64_t ldd, const int32_t* i
   return SR_OK;
 }
 
-extern "C" int sr_adam_step_f32(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
-                                float beta2, float eps, int64_t step, float grad_scale, void* stream) {
+extern "C" int sr_adam_step_f32(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, double lr, double beta1,
+                                double beta2, double eps, int64_t step, double grad_scale, void* stream) {
   if (int rc = require_sm100()) return rc;
   SR_REQUIRE(param && grad && exp_avg && exp_avg_sq && n > 0 && n % 4 == 0 && step >= 1, "sr_adam_step_f32: bad arguments (n % 4 == 0, step >= 1)");
   SR_REQUIRE(((reinterpret_cast<uintptr_t>(param) | reinterpret_cast<uintptr_t>(grad) | reinterpret_cast<uintptr_t>(exp_avg) |
                reinterpret_cast<uintptr_t>(exp_avg_sq)) & 15) == 0, "sr_adam_step_f32: buffers must be 16-byte aligned");
-  const double bc1 = 1.0 - pow(static_cast<double>(beta1), static_cast<double>(step));
-  const double bc2 = 1.0 - pow(static_cast<double>(beta2), static_cast<double>(step));
+  const double bc1 = 1.0 - pow(beta1, static_cast<double>(step));
+  const double bc2 = 1.0 - pow(beta2, static_cast<double>(step));
   const int64_t n4 = n / 4;
   const int64_t want = (n4 + 255) / 256;
   const unsigned grid = static_cast<unsigned>(want < 148 * 8 ? want : 148 * 8);
   adam_step_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(param, grad, exp_avg, exp_avg_sq, n4,
-                                                                             static_cast<float>(lr / bc1), beta1, beta2, eps,
-                                                                             static_cast<float>(1.0 / sqrt(bc2)), grad_scale);
+                                                                             static_cast<float>(lr / bc1), static_cast<float>(beta1),
+                                                                             static_cast<float>(beta2), static_cast<float>(1.0 - beta1),
+                                                                             static_cast<float>(1.0 - beta2), static_cast<float>(eps),
+                                                                             static_cast<float>(1.0 / sqrt(bc2)),
+                                                                             static_cast<float>(grad_scale));
   SR_LAUNCHED();
   return SR_OK;
 }

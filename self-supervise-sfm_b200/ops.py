@@ -301,8 +301,10 @@ def transpose_bf16(src: torch.Tensor, r_pad: Optional[int] = None) -> torch.Tens
     R, Cc = src.shape
     rp = r_pad or (R + 63) // 64 * 64
     dst = torch.empty(Cc, rp, dtype=torch.bfloat16, device=src.device)
+    tm = _Timed("transpose", 0.0, 4.0 * R * Cc)
     _lib.check(_lib.load().sr_transpose_bf16(src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0), R, Cc, rp, _stream()),
                "transpose_bf16")
+    tm.done()
     return dst
 
 
@@ -316,8 +318,10 @@ def colsum(a: torch.Tensor, b: Optional[torch.Tensor], out: torch.Tensor, accumu
         if b.shape != a.shape:
             raise ValueError("sailrecon_b200: colsum shape mismatch")
     _vec(out, a.shape[1], "out")
+    tm = _Timed("colsum", 0.0, a.numel() * (a.element_size() + (0 if b is None else 2)))
     _lib.check(_lib.load().sr_colsum(a.data_ptr(), int(a.dtype == torch.bfloat16), a.stride(0), _ptr(b), 0 if b is None else b.stride(0),
                                      out.data_ptr(), a.shape[0], a.shape[1], int(accumulate), _stream()), "colsum")
+    tm.done()
     return out
 
 
@@ -327,8 +331,10 @@ def scale_cast_bf16(x: torch.Tensor, gamma: Optional[torch.Tensor], out: torch.T
     _vec(gamma, x.shape[1], "gamma")
     if out.shape != x.shape:
         raise ValueError("sailrecon_b200: scale_cast shape mismatch")
+    tm = _Timed("scale_cast", 0.0, 6.0 * x.numel())
     _lib.check(_lib.load().sr_scale_cast_bf16(x.data_ptr(), x.stride(0), _ptr(gamma), out.data_ptr(), out.stride(0), x.shape[0],
                                               x.shape[1], _stream()), "scale_cast_bf16")
+    tm.done()
     return out
 
 
@@ -339,15 +345,19 @@ def ls_residual(resid: torch.Tensor, z: torch.Tensor, gamma: Optional[torch.Tens
     if not (resid.is_contiguous() and z.is_contiguous() and out.is_contiguous() and resid.shape == z.shape == out.shape):
         raise ValueError("sailrecon_b200: ls_residual needs contiguous tensors of one shape")
     _vec(gamma, resid.shape[1], "gamma")
+    tm = _Timed("ls_residual", 0.0, 10.0 * resid.numel())
     _lib.check(_lib.load().sr_ls_residual_f32(resid.data_ptr(), z.data_ptr(), _ptr(gamma), out.data_ptr(), resid.shape[0],
                                               resid.shape[1], _stream()), "ls_residual")
+    tm.done()
     return out
 
 
 def gelu_fwd(u: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
     if not (u.is_cuda and u.dtype == out.dtype == torch.bfloat16 and u.is_contiguous() and out.is_contiguous() and u.shape == out.shape):
         raise ValueError("sailrecon_b200: gelu_fwd needs contiguous bf16 CUDA tensors of one shape")
+    tm = _Timed("gelu_fwd", 0.0, 4.0 * u.numel())
     _lib.check(_lib.load().sr_gelu_fwd_bf16(u.data_ptr(), out.data_ptr(), u.numel(), _stream()), "gelu_fwd")
+    tm.done()
     return out
 
 
@@ -355,23 +365,30 @@ def gelu_bwd(u: torch.Tensor, dg: torch.Tensor, du: torch.Tensor) -> torch.Tenso
     for t in (u, dg, du):
         if not (t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and t.shape == u.shape):
             raise ValueError("sailrecon_b200: gelu_bwd needs contiguous bf16 CUDA tensors of one shape")
+    tm = _Timed("gelu_bwd", 0.0, 6.0 * u.numel())
     _lib.check(_lib.load().sr_gelu_bwd_bf16(u.data_ptr(), dg.data_ptr(), du.data_ptr(), u.numel(), _stream()), "gelu_bwd")
+    tm.done()
     return du
 
 
 def layernorm_bwd(x: torch.Tensor, weight: Optional[torch.Tensor], dy: torch.Tensor, dx: torch.Tensor,
-                  dweight: Optional[torch.Tensor], dbias: Optional[torch.Tensor], eps: float) -> torch.Tensor:
-    """dx += dLN(dy); dweight / dbias accumulate (fp32 [C])."""
+                  dweight: Optional[torch.Tensor], dbias: Optional[torch.Tensor], eps: float,
+                  dres: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dx = dres + dLN(dy) (dres None: dx += dLN(dy)); dweight / dbias accumulate (fp32 [C])."""
     _rows2d(x, torch.float32, "x")
     _rows2d(dy, torch.bfloat16, "dy")
     _rows2d(dx, torch.float32, "dx")
-    if not (x.shape == dy.shape == dx.shape):
+    if dres is not None:
+        _rows2d(dres, torch.float32, "dres")
+    if not (x.shape == dy.shape == dx.shape) or (dres is not None and dres.shape != dx.shape):
         raise ValueError("sailrecon_b200: layernorm_bwd shape mismatch")
     for n, t in (("weight", weight), ("dweight", dweight), ("dbias", dbias)):
         _vec(t, x.shape[1], n)
-    _lib.check(_lib.load().sr_layernorm_bwd(x.data_ptr(), x.stride(0), _ptr(weight), dy.data_ptr(), dy.stride(0), dx.data_ptr(),
-                                            dx.stride(0), _ptr(dweight), _ptr(dbias), x.shape[0], x.shape[1], float(eps), _stream()),
-               "layernorm_bwd")
+    tm = _Timed("layernorm_bwd", 0.0, 14.0 * x.numel())
+    _lib.check(_lib.load().sr_layernorm_bwd(x.data_ptr(), x.stride(0), _ptr(weight), dy.data_ptr(), dy.stride(0), _ptr(dres),
+                                            0 if dres is None else dres.stride(0), dx.data_ptr(), dx.stride(0), _ptr(dweight),
+                                            _ptr(dbias), x.shape[0], x.shape[1], float(eps), _stream()), "layernorm_bwd")
+    tm.done()
     return dx
 
 
@@ -406,8 +423,10 @@ def qknorm_rope_fwd(raw: torch.Tensor, out: torch.Tensor, qkv: QkvEpilogue) -> t
         raise ValueError("sailrecon_b200: qknorm_rope needs [M, 3C] buffers")
     e = SrEpilogue()
     keep = _fill_qkv(e, qkv, raw.shape[0])
+    tm = _Timed("qknorm_rope_fwd", 0.0, 4.0 * raw.numel())
     _lib.check(_lib.load().sr_qknorm_rope_fwd(raw.data_ptr(), raw.stride(0), out.data_ptr(), out.stride(0), C.byref(e), raw.shape[0],
                                               _stream()), "qknorm_rope_fwd")
+    tm.done()
     del keep
     return out
 
@@ -426,8 +445,10 @@ def qknorm_rope_bwd(raw: torch.Tensor, dqkv: torch.Tensor, qkv: QkvEpilogue, dq_
         g = [dq_norm[0], dq_norm[1], dk_norm[0], dk_norm[1]]
         for t in g:
             _vec(t, qkv.head_dim, "q/k norm gradient")
+    tm = _Timed("qknorm_rope_bwd", 0.0, 6.0 * raw.numel())
     _lib.check(_lib.load().sr_qknorm_rope_bwd(raw.data_ptr(), raw.stride(0), dqkv.data_ptr(), dqkv.stride(0), C.byref(e), _ptr(g[0]),
                                               _ptr(g[1]), _ptr(g[2]), _ptr(g[3]), raw.shape[0], _stream()), "qknorm_rope_bwd")
+    tm.done()
     del keep
     return dqkv
 

@@ -163,16 +163,17 @@ def linear_backward(lin: nn.Module, a_in: torch.Tensor, dz: torch.Tensor, grads:
     return da
 
 
-def block_backward(blk: nn.Module, s: BlockSaved, dy: torch.Tensor, grads: Dict[nn.Parameter, torch.Tensor]) -> torch.Tensor:
-    """dy = gradient w.r.t. the block output (fp32 [T, C]) -> gradient w.r.t. the block input (fp32, a fresh tensor);
-    parameter gradients accumulate into `grads`."""
+def block_backward(blk: nn.Module, s: BlockSaved, dy: torch.Tensor, grads: Dict[nn.Parameter, torch.Tensor],
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dy = gradient w.r.t. the block output (fp32 [T, C], not modified) -> gradient w.r.t. the block input (fp32, written to
+    `out` or a fresh tensor); parameter gradients accumulate into `grads`."""
     engine.require_cuda_f32(dy, "dy")
     T, C = dy.shape
     dev = dy.device
     attn, mlp = blk.attn, blk.mlp
     H = attn.num_heads
     d = C // H
-    dx1 = dy.clone()                                               # residual path of x2 = x1 + g2 z2
+    dx1 = torch.empty_like(dy)                                     # = dy (residual path of x2 = x1 + g2 z2) + MLP branch
     # ---- MLP branch
     g2 = engine.gamma_of(blk.ls2)
     if g2 is not None:
@@ -182,9 +183,9 @@ def block_backward(blk: nn.Module, s: BlockSaved, dy: torch.Tensor, grads: Dict[
     du = ops.gelu_bwd(s.u, dg, dg)                                 # in place over dg
     dh2 = linear_backward(mlp.fc1, s.h2, du, grads)
     w2, _, eps2 = engine.ln_params(blk.norm2)
-    ops.layernorm_bwd(s.x1, w2, dh2, dx1, _acc(grads, blk.norm2.weight), _acc(grads, blk.norm2.bias), eps2)
+    ops.layernorm_bwd(s.x1, w2, dh2, dx1, _acc(grads, blk.norm2.weight), _acc(grads, blk.norm2.bias), eps2, dres=dy)
     # ---- attention branch
-    dx = dx1.clone()                                               # residual path of x1 = x + g1 z1
+    dx = out if out is not None else torch.empty_like(dy)          # = dx1 (residual path of x1 = x + g1 z1) + attention branch
     g1 = engine.gamma_of(blk.ls1)
     if g1 is not None:
         ops.colsum(dx1, s.z1, _acc(grads, blk.ls1.gamma), accumulate=True)
@@ -219,7 +220,7 @@ def block_backward(blk: nn.Module, s: BlockSaved, dy: torch.Tensor, grads: Dict[
         ops.qknorm_rope_bwd(s.raw, dqkv, s.epi, dqn, dkn)
     dh1 = linear_backward(attn.qkv, s.h1, dqkv, grads)
     w1, _, eps1 = engine.ln_params(blk.norm1)
-    ops.layernorm_bwd(s.x, w1, dh1, dx, _acc(grads, blk.norm1.weight), _acc(grads, blk.norm1.bias), eps1)
+    ops.layernorm_bwd(s.x, w1, dh1, dx, _acc(grads, blk.norm1.weight), _acc(grads, blk.norm1.bias), eps1, dres=dx1)
     return dx
 
 
@@ -315,20 +316,18 @@ def layer_backward(fblk: nn.Module, gblk: nn.Module, rblk: nn.Module, X_in: torc
     the [frame | global] concat the heads read, aggregator.py:403-413)."""
     n = ctx.Na * ctx.P
     Xa_mid, Xq_mid = X_mid[:n], X_mid[n:]
+    d_all = torch.empty_like(dX)
     sg = block_forward_saving(gblk, Xa_mid, ctx.global_calls, ctx.pos_a)
-    dXa = block_backward(gblk, sg, dX[:n].contiguous(), grads)
+    dXa = block_backward(gblk, sg, dX[:n], grads, out=d_all[:n])
     del sg
     if ctx.Nq > 0:
         scene = scene_forward_saving(rblk, Xa_mid, idx, spos)
         C = X_in.shape[1]
         pre = engine.Prefix(scene.post[:, C:2 * C], scene.post[:, 2 * C:], 0, idx.numel())
         sr = block_forward_saving(rblk, Xq_mid, [engine.AttnCall(0, ctx.Nq, ctx.P, ctx.P, pre)], ctx.pos_q)
-        dXq = block_backward(rblk, sr, dX[n:].contiguous(), grads)
+        block_backward(rblk, sr, dX[n:], grads, out=d_all[n:])
         scene_backward(rblk, scene, sr.dprefix, Xa_mid, dXa, grads)
         del sr, scene
-        d_all = torch.cat([dXa, dXq])
-    else:
-        d_all = dXa
     if d_mid is not None:
         d_all += d_mid
     sf = block_forward_saving(fblk, X_in, ctx.frame_calls, ctx.rows_pos)
