@@ -156,8 +156,11 @@ int sr_attn_bwd_bf16(const sr_attn_bwd_t* p, void* stream);
 /* ---- Training-step row kernels (autograd of block.py:86-112; csrc/train_rows.cu) -------------------------
  * The Linear gradients run on sr_gemm_bf16 itself: dX = dY W is sr_gemm_bf16(dY, W^T), dW = dY^T X is
  * sr_gemm_bf16(dY^T, X^T) with fp32 output; sr_transpose_bf16 makes the transposed bf16 operands
- * (dst [C, ldd >= R_pad], columns [R, R_pad) zero-filled so that the contraction length is a multiple of 64).  */
-int sr_transpose_bf16(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t R, int64_t C, int64_t R_pad, void* stream);
+ * (dst [C, ldd >= R_pad], columns [R, R_pad) zero-filled so that the contraction length is a multiple of 64).
+ * colsum (fp32 [C], NULL = skip): colsum[c] += sum_r src[r, c] in the same pass — the bias gradient of the Linear whose
+ * dY is being transposed (needs the 16-byte aligned layout: R_pad % 64 == 0; C, lds, ldd multiples of 8).        */
+int sr_transpose_bf16(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t R, int64_t C, int64_t R_pad, float* colsum,
+                      void* stream);
 /* out[c] (+)= sum_r a[r,c] * b[r,c]   (a fp32 or bf16, b bf16 or NULL = 1): bias and LayerScale gamma gradients */
 int sr_colsum(const void* a, int a_bf16, int64_t lda, const void* b, int64_t ldb, float* out, int64_t R, int64_t C,
               int accumulate, void* stream);

@@ -78,7 +78,7 @@ SIGNATURES = {
     "sr_attn_fwd_bf16": (C.c_int, [C.POINTER(SrAttn), _vp]),
     "sr_attn_fwd_f32": (C.c_int, [C.POINTER(SrAttn), _vp]),
     "sr_attn_bwd_bf16": (C.c_int, [C.POINTER(SrAttnBwd), _vp]),
-    "sr_transpose_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp]),
+    "sr_transpose_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _vp]),
     "sr_colsum": (C.c_int, [_vp, C.c_int, _i64, _vp, _i64, _vp, _i64, _i64, C.c_int, _vp]),
     "sr_scale_cast_bf16": (C.c_int, [_vp, _i64, _vp, _vp, _i64, _i64, _i64, _vp]),
     "sr_ls_residual_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _vp]),

@@ -39,6 +39,48 @@ transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, int64_t lds, __nv_b
   }
 }
 
+// Vector form (16-byte global accesses both ways): 64 x 64 tile, thread t loads chunks (row t/8 [+32], 8 columns), the
+// write side gives every group of 8 lanes one output row (128 contiguous bytes, rows r0 + 8k .. + 7 of source column c).
+// The 8 values a thread gathers for its chunk are 8 rows of ONE source column, so the column sums of src (the bias
+// gradient of the Linear whose dY this is) come for free: 3 shuffles + one atomic per (column, tile).
+__global__ void __launch_bounds__(256)
+transpose_bf16_vec_kernel(const __nv_bfloat16* __restrict__ src, int64_t lds, __nv_bfloat16* __restrict__ dst, int64_t ldd,
+                          int R, int C, float* __restrict__ colsum) {
+  __shared__ __align__(16) uint32_t tile[64 * 33];                 // 64 rows x 64 bf16, row stride 33 words
+  const int r0 = blockIdx.x * 64, c0 = blockIdx.y * 64;
+  const int t = threadIdx.x;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int r = (t >> 3) + 32 * h, c8 = t & 7;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (r0 + r < R && c0 + c8 * 8 < C) v = *reinterpret_cast<const uint4*>(src + static_cast<int64_t>(r0 + r) * lds + c0 + c8 * 8);
+    uint32_t* w = tile + r * 33 + c8 * 4;
+    w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+  }
+  __syncthreads();
+  const int warp = t >> 5, lane = t & 31, k = lane & 7;
+  const __nv_bfloat16* tb = reinterpret_cast<const __nv_bfloat16*>(tile);
+#pragma unroll
+  for (int i = 0; i < 2; ++i) {
+    const int c = warp * 8 + i * 4 + (lane >> 3);
+    uint32_t o[4];
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const __nv_bfloat16 a = tb[(8 * k + 2 * j) * 66 + c], b = tb[(8 * k + 2 * j + 1) * 66 + c];
+      o[j] = static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
+      sum += __bfloat162float(a) + __bfloat162float(b);
+    }
+    if (c0 + c < C) *reinterpret_cast<uint4*>(dst + static_cast<int64_t>(c0 + c) * ldd + r0 + 8 * k) = make_uint4(o[0], o[1], o[2], o[3]);
+    if (colsum != nullptr) {
+      sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+      sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+      sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+      if (k == 0 && c0 + c < C) atomicAdd(colsum + c0 + c, sum);
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ column sums
 // One thread per column, 128 columns x 128 rows per block, atomics into out (zeroed by the launcher unless accumulate).
 template <bool A_BF16>
@@ -122,20 +164,26 @@ gelu_kernel(const __nv_bfloat16* __restrict__ u, const __nv_bfloat16* __restrict
 
 // ------------------------------------------------------------------------------------------------ LayerNorm backward
 // One warp per row, lane holds columns {128 i + 4 lane .. +3}, i < NCH (C = 128 NCH).  dx = dres + rstd * (g - mean(g) -
-// xhat * mean(g * xhat)) with g = dy * w; per-block partial dw / db reduced through shared memory, then atomics.
+// xhat * mean(g * xhat)) with g = dy * w.  The per-column dw / db partials live in shared memory (each lane owns its own
+// 4 NCH addresses of its warp's slice, so no synchronisation inside the row loop) instead of 2 x 4 NCH registers: 4 warps
+// per CTA at <= 128 registers -> 4 CTAs = 16 warps per SM (the register-resident version ran 8); one atomic per column
+// and CTA at the end.
 template <int NCH>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128, 4)
 layernorm_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ w, const __nv_bfloat16* __restrict__ dy,
                      int64_t lddy, const float* dres, int64_t lddres, float* dx, int64_t lddx, float* __restrict__ dw,
                      float* __restrict__ db, int rows, int rows_per_block, float eps) {
   constexpr int C = NCH * 128;
-  __shared__ float red[8][C];
+  __shared__ __align__(16) float red_w[4][C];
+  __shared__ __align__(16) float red_b[4][C];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float pw[NCH * 4], pb[NCH * 4];
 #pragma unroll
-  for (int i = 0; i < NCH * 4; ++i) pw[i] = pb[i] = 0.f;
+  for (int i = 0; i < NCH; ++i) {
+    *reinterpret_cast<float4*>(&red_w[warp][i * 128 + lane * 4]) = make_float4(0.f, 0.f, 0.f, 0.f);
+    *reinterpret_cast<float4*>(&red_b[warp][i * 128 + lane * 4]) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   const int r_begin = blockIdx.x * rows_per_block, r_end = min(rows, r_begin + rows_per_block);
-  for (int r = r_begin + warp; r < r_end; r += 8) {
+  for (int r = r_begin + warp; r < r_end; r += 4) {
     float xv[NCH * 4], gv[NCH * 4];
     float s = 0.f;
 #pragma unroll
@@ -156,17 +204,23 @@ layernorm_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __re
       const float4 wv = w ? __ldg(reinterpret_cast<const float4*>(w + i * 128 + lane * 4)) : make_float4(1.f, 1.f, 1.f, 1.f);
       const float dyv[4] = {bf16_lo(d.x), bf16_hi(d.x), bf16_lo(d.y), bf16_hi(d.y)};
       const float wq[4] = {wv.x, wv.y, wv.z, wv.w};
+      float4 aw = *reinterpret_cast<float4*>(&red_w[warp][i * 128 + lane * 4]);
+      float4 ab = *reinterpret_cast<float4*>(&red_b[warp][i * 128 + lane * 4]);
+      float* awp = &aw.x;
+      float* abp = &ab.x;
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const float xh = xv[4 * i + u] * rstd;
         xv[4 * i + u] = xh;
-        pw[4 * i + u] += dyv[u] * xh;
-        pb[4 * i + u] += dyv[u];
+        awp[u] += dyv[u] * xh;
+        abp[u] += dyv[u];
         const float g = dyv[u] * wq[u];
         gv[4 * i + u] = g;
         sg += g;
         sgx += g * xh;
       }
+      *reinterpret_cast<float4*>(&red_w[warp][i * 128 + lane * 4]) = aw;
+      *reinterpret_cast<float4*>(&red_b[warp][i * 128 + lane * 4]) = ab;
     }
     const float mg = warp_sum(sg) * (1.0f / C), mgx = warp_sum(sgx) * (1.0f / C);
 #pragma unroll
@@ -180,30 +234,18 @@ layernorm_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __re
       *reinterpret_cast<float4*>(o) = v;
     }
   }
-  // block reduction of the dw / db partials (two passes through the same buffer)
-#pragma unroll
-  for (int pass = 0; pass < 2; ++pass) {
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < NCH; ++i)
-#pragma unroll
-      for (int u = 0; u < 4; ++u) red[warp][i * 128 + lane * 4 + u] = pass == 0 ? pw[4 * i + u] : pb[4 * i + u];
-    __syncthreads();
-    float* dst = pass == 0 ? dw : db;
-    if (dst != nullptr) {
-      for (int c = threadIdx.x; c < C; c += 256) {
-        float t = 0.f;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) t += red[k][c];
-        atomicAdd(dst + c, t);
-      }
-    }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += 128) {
+    if (dw != nullptr) atomicAdd(dw + c, red_w[0][c] + red_w[1][c] + red_w[2][c] + red_w[3][c]);
+    if (db != nullptr) atomicAdd(db + c, red_b[0][c] + red_b[1][c] + red_b[2][c] + red_b[3][c]);
   }
 }
 
 // ------------------------------------------------------------------------------------------------ QK-norm + RoPE
-// One warp per (row, head): lane holds features `lane` (y half) and `lane + 32` (x half); the rotate-half partner of
-// feature j inside a half is j ^ 16 -> one shuffle.  blockIdx.x = head slot in [0, 3H): q heads, k heads, v heads.
+// One warp per (row, head): lane holds the ADJACENT features 2 lane, 2 lane + 1 (one 4-byte load per row; lanes 0-15 the y
+// half, 16-31 the x half); the rotate-half partner of feature j inside a half is j ^ 16 -> lane ^ 8, one shuffle each.
+// Four rows are in flight per iteration (loads first, then the shuffle reductions, then stores) to hide the latency
+// of the strided 128-byte row segments.  blockIdx.x = head slot in [0, 3H): q heads, k heads, v heads.
 struct QkRopeParams {
   const float* qn_w; const float* qn_b; const float* kn_w; const float* kn_b;
   float eps;
@@ -217,20 +259,26 @@ struct QkRopeParams {
 
 template <bool BWD>
 __global__ void __launch_bounds__(256)
-qknorm_rope_kernel(const __nv_bfloat16* __restrict__ raw, int64_t ldr, __nv_bfloat16* __restrict__ io, int64_t ldio,
+qknorm_rope_kernel(const __nv_bfloat16* __restrict__ raw, int64_t ldr, __nv_bfloat16* io, int64_t ldio,
                    float* __restrict__ dqn_w, float* __restrict__ dqn_b, float* __restrict__ dkn_w, float* __restrict__ dkn_b,
                    const QkRopeParams p) {
+  constexpr int U = 4;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slot = blockIdx.x;                        // head slot
   const int which = slot / p.H;                       // 0 q, 1 k, 2 v
-  const int col = slot * 64;
+  const int col = slot * 64 + 2 * lane;
   const int64_t r_begin = (static_cast<int64_t>(blockIdx.y) * 8 + warp) * p.rows_per_warp;
   const int64_t r_end = min(p.M, r_begin + p.rows_per_warp);
   if (which == 2) {
     if (!BWD) {
-      for (int64_t r = r_begin; r < r_end; ++r) {
-        io[r * ldio + col + lane] = raw[r * ldr + col + lane];
-        io[r * ldio + col + 32 + lane] = raw[r * ldr + col + 32 + lane];
+      for (int64_t r = r_begin; r < r_end; r += U) {
+        uint32_t v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (r + u < r_end) v[u] = *reinterpret_cast<const uint32_t*>(raw + (r + u) * ldr + col);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (r + u < r_end) *reinterpret_cast<uint32_t*>(io + (r + u) * ldio + col) = v[u];
       }
     }
     return;
@@ -238,58 +286,72 @@ qknorm_rope_kernel(const __nv_bfloat16* __restrict__ raw, int64_t ldr, __nv_bflo
   const float* nw = which == 0 ? p.qn_w : p.kn_w;
   const float* nb = which == 0 ? p.qn_b : p.kn_b;
   float w0 = 1.f, w1 = 1.f, b0 = 0.f, b1 = 0.f;
-  if (p.qk_norm) { w0 = nw[lane]; w1 = nw[lane + 32]; b0 = nb[lane]; b1 = nb[lane + 32]; }
+  if (p.qk_norm) { w0 = nw[2 * lane]; w1 = nw[2 * lane + 1]; b0 = nb[2 * lane]; b1 = nb[2 * lane + 1]; }
   float aw0 = 0.f, aw1 = 0.f, ab0 = 0.f, ab1 = 0.f;
-  const int f = lane & 15;
-  const bool is_a = lane < 16;                        // first member of the (i, i + 16) pair
-  for (int64_t r = r_begin; r < r_end; ++r) {
-    float x0 = __bfloat162float(raw[r * ldr + col + lane]);
-    float x1 = __bfloat162float(raw[r * ldr + col + 32 + lane]);
-    float rstd = 1.f;
-    if (p.qk_norm) {
-      const float mean = warp_sum(x0 + x1) * (1.0f / 64.0f);
-      x0 -= mean; x1 -= mean;
-      rstd = rsqrtf(warp_sum(x0 * x0 + x1 * x1) * (1.0f / 64.0f) + p.eps);
-      x0 *= rstd; x1 *= rstd;                         // xhat
-    }
-    float c0 = 1.f, s0 = 0.f, c1 = 1.f, s1 = 0.f;
-    if (p.rope) {
-      const int2 yx = __ldg(reinterpret_cast<const int2*>(p.pos) + r);
-      c0 = __ldg(p.rope_cos + static_cast<int64_t>(yx.x) * 16 + f); s0 = __ldg(p.rope_sin + static_cast<int64_t>(yx.x) * 16 + f);
-      c1 = __ldg(p.rope_cos + static_cast<int64_t>(yx.y) * 16 + f); s1 = __ldg(p.rope_sin + static_cast<int64_t>(yx.y) * 16 + f);
-    }
-    if (!BWD) {
-      float y0 = p.qk_norm ? x0 * w0 + b0 : x0, y1 = p.qk_norm ? x1 * w1 + b1 : x1;
-      const float o0 = __shfl_xor_sync(0xffffffffu, y0, 16), o1 = __shfl_xor_sync(0xffffffffu, y1, 16);
-      // pair (a, b) = (i, i + 16): a' = a c - b s ; b' = b c + a s
-      y0 = is_a ? y0 * c0 - o0 * s0 : y0 * c0 + o0 * s0;
-      y1 = is_a ? y1 * c1 - o1 * s1 : y1 * c1 + o1 * s1;
-      io[r * ldio + col + lane] = __float2bfloat16_rn(y0);
-      io[r * ldio + col + 32 + lane] = __float2bfloat16_rn(y1);
-    } else {
-      float d0 = __bfloat162float(io[r * ldio + col + lane]);
-      float d1 = __bfloat162float(io[r * ldio + col + 32 + lane]);
-      const float o0 = __shfl_xor_sync(0xffffffffu, d0, 16), o1 = __shfl_xor_sync(0xffffffffu, d1, 16);
-      // da = da' c + db' s ; db = db' c - da' s
-      d0 = is_a ? d0 * c0 + o0 * s0 : d0 * c0 - o0 * s0;
-      d1 = is_a ? d1 * c1 + o1 * s1 : d1 * c1 - o1 * s1;
-      if (p.qk_norm) {
-        aw0 += d0 * x0; aw1 += d1 * x1; ab0 += d0; ab1 += d1;
-        const float g0 = d0 * w0, g1 = d1 * w1;
-        const float mg = warp_sum(g0 + g1) * (1.0f / 64.0f);
-        const float mgx = warp_sum(g0 * x0 + g1 * x1) * (1.0f / 64.0f);
-        d0 = rstd * (g0 - mg - x0 * mgx);
-        d1 = rstd * (g1 - mg - x1 * mgx);
+  const int f = 2 * (lane & 7);                       // table column of the first feature (j & 15)
+  const bool is_a = (lane & 8) == 0;                  // first member of the (i, i + 16) pair
+  const bool x_half = lane >= 16;
+  for (int64_t r = r_begin; r < r_end; r += U) {
+    uint32_t xr[U], dr[U];
+    float2 cs[U], sn[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const bool ok = r + u < r_end;
+      xr[u] = ok ? *reinterpret_cast<const uint32_t*>(raw + (r + u) * ldr + col) : 0u;
+      if (BWD) dr[u] = ok ? *reinterpret_cast<const uint32_t*>(io + (r + u) * ldio + col) : 0u;
+      cs[u] = make_float2(1.f, 1.f);
+      sn[u] = make_float2(0.f, 0.f);
+      if (p.rope && ok) {
+        const int2 yx = __ldg(reinterpret_cast<const int2*>(p.pos) + (r + u));
+        const int64_t t = static_cast<int64_t>(x_half ? yx.y : yx.x) * 16 + f;
+        cs[u] = __ldg(reinterpret_cast<const float2*>(p.rope_cos + t));
+        sn[u] = __ldg(reinterpret_cast<const float2*>(p.rope_sin + t));
       }
-      io[r * ldio + col + lane] = __float2bfloat16_rn(d0);
-      io[r * ldio + col + 32 + lane] = __float2bfloat16_rn(d1);
     }
+    uint32_t out[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float x0 = bf16_lo(xr[u]), x1 = bf16_hi(xr[u]);
+      float rstd = 1.f;
+      if (p.qk_norm) {
+        const float mean = warp_sum(x0 + x1) * (1.0f / 64.0f);
+        x0 -= mean; x1 -= mean;
+        rstd = rsqrtf(warp_sum(x0 * x0 + x1 * x1) * (1.0f / 64.0f) + p.eps);
+        x0 *= rstd; x1 *= rstd;                       // xhat
+      }
+      if (!BWD) {
+        float y0 = p.qk_norm ? x0 * w0 + b0 : x0, y1 = p.qk_norm ? x1 * w1 + b1 : x1;
+        const float o0 = __shfl_xor_sync(0xffffffffu, y0, 8), o1 = __shfl_xor_sync(0xffffffffu, y1, 8);
+        // pair (a, b) = (i, i + 16): a' = a c - b s ; b' = b c + a s
+        y0 = is_a ? y0 * cs[u].x - o0 * sn[u].x : y0 * cs[u].x + o0 * sn[u].x;
+        y1 = is_a ? y1 * cs[u].y - o1 * sn[u].y : y1 * cs[u].y + o1 * sn[u].y;
+        out[u] = pack_bf16x2(y0, y1);
+      } else {
+        float d0 = bf16_lo(dr[u]), d1 = bf16_hi(dr[u]);
+        const float o0 = __shfl_xor_sync(0xffffffffu, d0, 8), o1 = __shfl_xor_sync(0xffffffffu, d1, 8);
+        // da = da' c + db' s ; db = db' c - da' s
+        d0 = is_a ? d0 * cs[u].x + o0 * sn[u].x : d0 * cs[u].x - o0 * sn[u].x;
+        d1 = is_a ? d1 * cs[u].y + o1 * sn[u].y : d1 * cs[u].y - o1 * sn[u].y;
+        if (p.qk_norm) {
+          aw0 += d0 * x0; aw1 += d1 * x1; ab0 += d0; ab1 += d1;
+          const float g0 = d0 * w0, g1 = d1 * w1;
+          const float mg = warp_sum(g0 + g1) * (1.0f / 64.0f);
+          const float mgx = warp_sum(g0 * x0 + g1 * x1) * (1.0f / 64.0f);
+          d0 = rstd * (g0 - mg - x0 * mgx);
+          d1 = rstd * (g1 - mg - x1 * mgx);
+        }
+        out[u] = pack_bf16x2(d0, d1);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (r + u < r_end) *reinterpret_cast<uint32_t*>(io + (r + u) * ldio + col) = out[u];
   }
   if (BWD && p.qk_norm) {
     float* gw = which == 0 ? dqn_w : dkn_w;
     float* gb = which == 0 ? dqn_b : dkn_b;
-    if (gw) { atomicAdd(gw + lane, aw0); atomicAdd(gw + lane + 32, aw1); }
-    if (gb) { atomicAdd(gb + lane, ab0); atomicAdd(gb + lane + 32, ab1); }
+    if (gw) { atomicAdd(gw + 2 * lane, aw0); atomicAdd(gw + 2 * lane + 1, aw1); }
+    if (gb) { atomicAdd(gb + 2 * lane, ab0); atomicAdd(gb + 2 * lane + 1, ab1); }
   }
 }
 
@@ -348,13 +410,23 @@ using namespace sr;
   } while (0)
 
 extern "C" int sr_transpose_bf16(const void* src, int64_t lds, void* dst, int64_t ldd, int64_t R, int64_t C, int64_t R_pad,
-                                 void* stream) {
+                                 float* colsum, void* stream) {
   if (int rc = require_sm100()) return rc;
   SR_REQUIRE(src && dst && R > 0 && C > 0 && R_pad >= R && ldd >= R_pad && lds >= C, "sr_transpose_bf16: bad shape");
   dim3 grid(static_cast<unsigned>((R_pad + 63) / 64), static_cast<unsigned>((C + 63) / 64));
-  transpose_bf16_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(src), lds, reinterpret_cast<__nv_bfloat16*>(dst), ldd, static_cast<int>(R),
-      static_cast<int>(C), static_cast<int>(R_pad));
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool vec = R_pad % 64 == 0 && C % 8 == 0 && lds % 8 == 0 && ldd % 8 == 0 &&
+                   ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+  SR_REQUIRE(vec || colsum == nullptr, "sr_transpose_bf16: the fused column sum needs the 16-byte aligned layout "
+                                       "(R_pad % 64 == 0, C, lds, ldd multiples of 8)");
+  if (vec)
+    transpose_bf16_vec_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(src), lds,
+                                                    reinterpret_cast<__nv_bfloat16*>(dst), ldd, static_cast<int>(R),
+                                                    static_cast<int>(C), colsum);
+  else
+    transpose_bf16_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(src), lds,
+                                                reinterpret_cast<__nv_bfloat16*>(dst), ldd, static_cast<int>(R), static_cast<int>(C),
+                                                static_cast<int>(R_pad));
   SR_LAUNCHED();
   return SR_OK;
 }
@@ -424,8 +496,8 @@ extern "C" int sr_layernorm_bwd(const float* x, int64_t ldx, const float* weight
   SR_REQUIRE(C == 1024, "sr_layernorm_bwd: C must be 1024 (got %lld)", static_cast<long long>(C));
   if (dres == nullptr) { dres = dx; lddres = lddx; }
   SR_REQUIRE(ldx % 4 == 0 && lddy % 4 == 0 && lddx % 4 == 0 && lddres % 4 == 0, "sr_layernorm_bwd: row strides must be multiples of 4");
-  const int rows_per_block = 64;
-  layernorm_bwd_kernel<8><<<static_cast<unsigned>((rows + rows_per_block - 1) / rows_per_block), 256, 0,
+  const int rows_per_block = 32;
+  layernorm_bwd_kernel<8><<<static_cast<unsigned>((rows + rows_per_block - 1) / rows_per_block), 128, 0,
                             reinterpret_cast<cudaStream_t>(stream)>>>(x, ldx, weight, reinterpret_cast<const __nv_bfloat16*>(dy), lddy,
                                                                       dres, lddres, dx, lddx, dweight, dbias, static_cast<int>(rows),
                                                                       rows_per_block, eps);
@@ -438,6 +510,8 @@ static int qk_launch(bool bwd, const void* raw, int64_t ldr, void* io, int64_t l
   if (int rc = require_sm100()) return rc;
   SR_REQUIRE(raw && io && e && M > 0, "sr_qknorm_rope: null pointer / empty");
   SR_REQUIRE(e->head_dim == 64 && e->qkv_dim > 0 && e->qkv_dim % 64 == 0, "sr_qknorm_rope: head_dim must be 64");
+  SR_REQUIRE(ldr % 2 == 0 && ldio % 2 == 0 && ((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(io)) & 3) == 0,
+             "sr_qknorm_rope: buffers must be 4-byte aligned with even row strides");
   if (e->qk_norm) SR_REQUIRE(e->qn_w && e->qn_b && e->kn_w && e->kn_b, "sr_qknorm_rope: q/k norm parameters missing");
   if (e->rope) SR_REQUIRE(e->rope_cos && e->rope_sin && e->pos, "sr_qknorm_rope: RoPE tables / positions missing");
   QkRopeParams p;

@@ -295,15 +295,17 @@ def attention_bwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.
 
 
 # ------------------------------------------------------------------------------------------------ training-step row kernels
-def transpose_bf16(src: torch.Tensor, r_pad: Optional[int] = None) -> torch.Tensor:
-    """[R, C] bf16 -> [C, R_pad] bf16 (R_pad = R rounded up to 64, padding zero): transposed operand of dgrad / wgrad."""
+def transpose_bf16(src: torch.Tensor, r_pad: Optional[int] = None, colsum: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """[R, C] bf16 -> [C, R_pad] bf16 (R_pad = R rounded up to 64, padding zero): transposed operand of dgrad / wgrad.
+    colsum (fp32 [C]) += column sums of src in the same pass (the bias gradient when src is a Linear's dY)."""
     _rows2d(src, torch.bfloat16, "src")
     R, Cc = src.shape
     rp = r_pad or (R + 63) // 64 * 64
+    _vec(colsum, Cc, "colsum")
     dst = torch.empty(Cc, rp, dtype=torch.bfloat16, device=src.device)
     tm = _Timed("transpose", 0.0, 4.0 * R * Cc)
-    _lib.check(_lib.load().sr_transpose_bf16(src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0), R, Cc, rp, _stream()),
-               "transpose_bf16")
+    _lib.check(_lib.load().sr_transpose_bf16(src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0), R, Cc, rp, _ptr(colsum),
+                                             _stream()), "transpose_bf16")
     tm.done()
     return dst
 

@@ -124,9 +124,9 @@ def block_forward_saving(blk: nn.Module, x: torch.Tensor, calls: Sequence[engine
     return BlockSaved(x, h1, raw, qkv, o, lses, z1, x1, h2, u, g, z2, calls, epi)
 
 
-def block_output(blk: nn.Module, s: BlockSaved) -> torch.Tensor:
-    """x1 + g2 z2: the block output of a saving forward (tests; the training schedule takes it from engine.run_block)."""
-    return ops.ls_residual(s.x1, s.z2, engine.gamma_of(blk.ls2), torch.empty_like(s.x1))
+def block_output(blk: nn.Module, s: BlockSaved, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x1 + g2 z2: the block output of a saving forward, into `out` (contiguous rows) or a fresh tensor."""
+    return ops.ls_residual(s.x1, s.z2, engine.gamma_of(blk.ls2), torch.empty_like(s.x1) if out is None else out)
 
 
 def _acc(grads: Dict[nn.Parameter, torch.Tensor], p: Optional[nn.Parameter]) -> Optional[torch.Tensor]:
@@ -144,7 +144,8 @@ def linear_backward(lin: nn.Module, a_in: torch.Tensor, dz: torch.Tensor, grads:
     T, K = a_in.shape
     N = dz.shape[1]
     dev = a_in.device
-    dzT = ops.transpose_bf16(dz)                                   # [N, T_pad]
+    gb = _acc(grads, lin.bias) if lin.bias is not None else None
+    dzT = ops.transpose_bf16(dz, colsum=gb)                        # [N, T_pad]; db += colsum(dz) in the same pass
     aT = ops.transpose_bf16(a_in)                                  # [K, T_pad]
     gw = _acc(grads, lin.weight)
     if N % 128 == 0 and K % 128 == 0:
@@ -153,8 +154,6 @@ def linear_backward(lin: nn.Module, a_in: torch.Tensor, dz: torch.Tensor, grads:
         gw.view(N, K).add_(tmp)
     else:
         raise NotImplementedError("sailrecon_b200: Linear gradients need in / out features that are multiples of 128")
-    if lin.bias is not None:
-        ops.colsum(dz, None, _acc(grads, lin.bias), accumulate=True)
     if not need_input_grad:
         return None
     wT = engine._cached(lin, "wT_bf16", lin.weight, lambda w: ops.transpose_bf16(engine.weight_bf16(lin)))   # [K, N]
@@ -387,16 +386,59 @@ class TrainState:
                 torch.autograd.graph.increment_version(p)                             # engine's bf16 weight copies are stale now
 
 
-def stack_forward(agg: nn.Module, X: torch.Tensor, ctx: LayerCtx, draw_scene) -> list:
-    """The 24 aggregator layers (aggregator.py:339-423) in place on X with the inference kernels, keeping per layer what
-    torch.utils.checkpoint keeps in the reference (the block inputs: layer input and the state after the frame block) plus
-    that layer's scene-token draw.  draw_scene() -> (idx int32 [Na P'], RowPositions) is called once per layer, in order."""
+def layer_forward_saving(fblk: nn.Module, gblk: nn.Module, rblk: nn.Module, X: torch.Tensor, ctx: LayerCtx, idx: torch.Tensor,
+                         spos: engine.RowPositions):
+    """One aggregator layer keeping every activation its backward reads (no re-run in the backward): X is not modified,
+    returns (layer output, saved).  ~2.8 GB per layer at 24 frames of 518 px, 68 GB for the 24 layers — the schedule the
+    180 GB of a B200 allow; layer_forward / layer_backward are the reference's checkpointed schedule."""
+    n = ctx.Na * ctx.P
+    C = X.shape[1]
+    sf = block_forward_saving(fblk, X, ctx.frame_calls, ctx.rows_pos)
+    X_mid = block_output(fblk, sf)
+    Y = torch.empty_like(X_mid)
+    sg = block_forward_saving(gblk, X_mid[:n], ctx.global_calls, ctx.pos_a)
+    block_output(gblk, sg, out=Y[:n])
+    scene = sr = None
+    if ctx.Nq > 0:
+        scene = scene_forward_saving(rblk, X_mid[:n], idx, spos)
+        pre = engine.Prefix(scene.post[:, C:2 * C], scene.post[:, 2 * C:], 0, idx.numel())
+        sr = block_forward_saving(rblk, X_mid[n:], [engine.AttnCall(0, ctx.Nq, ctx.P, ctx.P, pre)], ctx.pos_q)
+        block_output(rblk, sr, out=Y[n:])
+    return Y, (sf, sg, scene, sr, X_mid)
+
+
+def layer_backward_saved(fblk: nn.Module, gblk: nn.Module, rblk: nn.Module, saved, dX: torch.Tensor, ctx: LayerCtx,
+                         grads: Dict[nn.Parameter, torch.Tensor], d_mid: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """layer_backward on the activations layer_forward_saving kept."""
+    sf, sg, scene, sr, X_mid = saved
+    n = ctx.Na * ctx.P
+    d_all = torch.empty_like(dX)
+    dXa = block_backward(gblk, sg, dX[:n], grads, out=d_all[:n])
+    if sr is not None:
+        block_backward(rblk, sr, dX[n:], grads, out=d_all[n:])
+        scene_backward(rblk, scene, sr.dprefix, X_mid[:n], dXa, grads)
+    if d_mid is not None:
+        d_all += d_mid
+    return block_backward(fblk, sf, d_all, grads)
+
+
+def stack_forward(agg: nn.Module, X: torch.Tensor, ctx: LayerCtx, draw_scene, keep_activations: bool = False) -> list:
+    """The 24 aggregator layers (aggregator.py:339-423) on X.  draw_scene() -> (idx int32 [Na P'], RowPositions) is called
+    once per layer, in order (the per-layer scene-token draw, :351-360).
+    keep_activations False: the reference's schedule — inference kernels in place on X, per layer only what
+    torch.utils.checkpoint keeps (the block inputs: layer input and the state after the frame block, :654-657,726-729,
+    758-761); the backward re-runs each block.  True: every block runs its saving forward once and nothing is re-run."""
     ck = []
     for i in range(agg.depth):
-        X_in = X.clone()
         idx, spos = draw_scene()
-        X_mid = layer_forward(agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i], X, ctx, idx, spos)
-        ck.append((X_in, X_mid, idx, spos))
+        blocks = (agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i])
+        if keep_activations:
+            X, saved = layer_forward_saving(*blocks, X, ctx, idx, spos)
+            ck.append((saved,))
+        else:
+            X_in = X.clone()
+            X_mid = layer_forward(*blocks, X, ctx, idx, spos)
+            ck.append((X_in, X_mid, idx, spos))
     return ck
 
 
@@ -404,18 +446,22 @@ def stack_backward(agg: nn.Module, ck: list, d_out: Dict[int, tuple], ctx: Layer
                    on_layer_done=None) -> torch.Tensor:
     """Backward through the 24 layers.  d_out[i] = (d_frame_half, d_global_half), each fp32 [T, C] or None: the loss gradient
     on the state after layer i's frame block and after the whole layer (the two halves of output_dict[i],
-    aggregator.py:403-413; the last layer's anchor rows carry the camera-token gradient, :414-423).  Checkpoints are
-    released layer by layer; on_layer_done(i) runs when layer i's parameter gradients are complete."""
+    aggregator.py:403-413; the last layer's anchor rows carry the camera-token gradient, :414-423).  Checkpoints /
+    activations are released layer by layer; on_layer_done(i) runs when layer i's parameter gradients are complete."""
     dX = None
     for i in reversed(range(agg.depth)):
-        X_in, X_mid, idx, spos = ck[i]
         d_mid, d_post = d_out.get(i, (None, None))
+        ref = ck[i][0][4] if len(ck[i]) == 1 else ck[i][0]
         if dX is None:
-            dX = torch.zeros_like(X_in) if d_post is None else d_post.clone()
+            dX = torch.zeros_like(ref) if d_post is None else d_post.clone()
         elif d_post is not None:
             dX += d_post
-        dX = layer_backward(agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i], X_in, X_mid, dX, ctx, idx, spos,
-                            grads, d_mid=d_mid)
+        blocks = (agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i])
+        if len(ck[i]) == 1:
+            dX = layer_backward_saved(*blocks, ck[i][0], dX, ctx, grads, d_mid=d_mid)
+        else:
+            X_in, X_mid, idx, spos = ck[i]
+            dX = layer_backward(*blocks, X_in, X_mid, dX, ctx, idx, spos, grads, d_mid=d_mid)
         ck[i] = None
         if on_layer_done is not None:
             on_layer_done(i)
@@ -423,11 +469,13 @@ def stack_backward(agg: nn.Module, ck: list, d_out: Dict[int, tuple], ctx: Layer
 
 
 def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: LayerCtx, draw_scene, d_out: Dict[int, tuple],
-                  world: int = 1, fwd_bwd=None, optimizer_step=None) -> torch.Tensor:
+                  world: int = 1, fwd_bwd=None, optimizer_step=None, keep_activations: bool = True) -> torch.Tensor:
     """zero_grad + forward + backward + gradient all-reduce + Adam for the block stacks on one scene per rank
     (train_imc.py:361-381 with DDP, :472).  The all-reduce of layer i's bucket (sum; the 1 / world of DDP's mean is
     folded into the Adam kernel) is issued as soon as layer i's backward is enqueued and overlaps the layers below it.
     Returns the gradient w.r.t. X0 (what would flow on into the patch embed).
+    keep_activations: True keeps every block's activations from the forward (68 GB at 24 frames — fits a B200, no re-run);
+    False is the reference's torch.utils.checkpoint schedule (block inputs only, each block re-run inside the backward).
     fwd_bwd(on_layer_done) -> dX0 and optimizer_step(grad_scale) replace the CUDA kernels in the CPU (gloo) tests of this
     schedule; the product path leaves them None."""
     import torch.distributed as dist
@@ -439,8 +487,8 @@ def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: Laye
             works.append(dist.all_reduce(state.grad[i], op=dist.ReduceOp.SUM, async_op=True))
 
     if fwd_bwd is None:
-        X = X0.clone()
-        ck = stack_forward(agg, X, ctx, draw_scene)
+        X = X0 if keep_activations else X0.clone()                 # the checkpointed forward works in place
+        ck = stack_forward(agg, X, ctx, draw_scene, keep_activations)
         dX0 = stack_backward(agg, ck, d_out, ctx, state.grads, reduce_layer)
     else:
         dX0 = fwd_bwd(reduce_layer)

@@ -31,6 +31,20 @@ def test_transpose_colsum_scale_cast_ls_residual():
     t = ops.transpose_bf16(a)
     assert t.shape == (1024, 384)
     assert torch.equal(t[:, :333], a.t()) and bool((t[:, 333:] == 0).all())
+    cs = torch.ones(1024, device=DEV)
+    t2 = ops.transpose_bf16(a, colsum=cs)                                    # fused column sum (bias gradient), accumulating
+    assert torch.equal(t2, t) and rel_l2(cs.cpu(), (1.0 + a.double().sum(0)).float().cpu()) < 1e-5
+    wide = _randn(200, 3072, seed=4).to(BF)
+    for view in (wide[:, 1024:2048], wide[:, 8:72], wide[3:131, :1000]):     # strided, narrow and row-offset sources
+        cs = torch.zeros(view.shape[1], device=DEV)
+        tv = ops.transpose_bf16(view, colsum=cs)
+        rp = (view.shape[0] + 63) // 64 * 64
+        assert tv.shape == (view.shape[1], rp) and torch.equal(tv[:, :view.shape[0]], view.t()) and bool((tv[:, view.shape[0]:] == 0).all())
+        assert rel_l2(cs.cpu(), view.double().sum(0).float().cpu()) < 1e-5
+    odd = wide[:, 3:67]                                                      # not 16-byte aligned: scalar kernel, no fused sum
+    assert torch.equal(ops.transpose_bf16(odd)[:, :200], odd.t())
+    with pytest.raises(ValueError):
+        ops.transpose_bf16(odd, colsum=torch.zeros(64, device=DEV))
     x = _randn(333, 1024, seed=2)
     out = torch.full((1024,), float("nan"), device=DEV)
     ops.colsum(x, a, out)
@@ -316,7 +330,8 @@ class _Stacks(torch.nn.Module):
         self.global_reloc_blocks = torch.nn.ModuleList([_rand_block(seed + 3 * i + 2) for i in range(depth)])
 
 
-def test_training_step_two_layers_matches_fp32_autograd_and_adam():
+@pytest.mark.parametrize("keep_activations", [True, False])
+def test_training_step_two_layers_matches_fp32_autograd_and_adam(keep_activations):
     """train.training_step over a 2-layer stack (checkpointed forward, backward through both layers with gradients on both
     halves of the layer-0 output and on the final state, flat per-layer buckets, Adam): input gradient and every parameter
     gradient against fp32 autograd; updated parameters against torch.optim.Adam fed with the reference gradients."""
@@ -345,8 +360,10 @@ def test_training_step_two_layers_matches_fp32_autograd_and_adam():
     X0 = _randn(S * Pn, C, seed=72)
     d_out = {0: (_randn(S * Pn, C, seed=73) * 0.5, _randn(S * Pn, C, seed=74) * 0.5),
              1: (None, _randn(S * Pn, C, seed=75))}
-    dX0 = train.training_step(agg, state, X0, ctx, draw_scene, d_out)
+    X0_in = X0.clone()
+    dX0 = train.training_step(agg, state, X0, ctx, draw_scene, d_out, keep_activations=keep_activations)
     torch.cuda.synchronize()
+    assert torch.equal(X0, X0_in)                                                  # the step does not touch its input
 
     P = {k: v.clone().requires_grad_(True) for k, v in before.items()}
     sub = lambda stack, i: {k[len(f"{stack}.{i}."):]: v for k, v in P.items() if k.startswith(f"{stack}.{i}.")}
