@@ -318,6 +318,12 @@ def bench_train(args, rank: int, world: int, local: int) -> None:
     finite = bool(torch.isfinite(dX0).all()) and all(bool(torch.isfinite(p).all()) for p in state.param)
     # per-kernel-class CUDA-event times: the same K steps again with an event pair around every C-ABI launch (~7000 pairs
     # per step cost a few per cent, so they are kept out of the region `value` is timed on)
+    if args.only_timed:
+        if rank == 0:
+            print(json.dumps({"only_timed": True, "ms_per_step": ms / args.steps, "gpu_launches": launches}), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     ops.PROFILE = []
     for _ in range(args.steps):
         agg.generator.manual_seed(1234)
@@ -410,6 +416,7 @@ def main():
     ap.add_argument("--checkpoint", action="store_true",
                     help="workload train: the reference's torch.utils.checkpoint schedule (re-run every block inside the backward) "
                          "instead of keeping the activations in HBM")
+    ap.add_argument("--only-timed", action="store_true", help="workload train: skip the per-kernel profile and e2e passes (ncu runs)")
     ap.add_argument("--ring-frames", type=int, default=512)
     ap.add_argument("--ring-depth", type=int, default=24)
     args = ap.parse_args()

@@ -16,6 +16,8 @@
 // TMEM per CTA: S 64 | dP 64 | acc0 64 | acc1 64 = 256 columns, 80 KB of smem: two CTAs per SM, whose MMA and softmax
 // phases interleave (inside one CTA the tile loop is serial: SS -> softmax -> TS).
 //   warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4-7 one thread per TMEM lane.
+#include <cstdlib>
+
 #include "attn_math.cuh"
 #include "common.cuh"
 #include "sr_internal.h"
@@ -28,7 +30,7 @@ constexpr int kBwXTile = 128 * 64 * 2;                // 16 KB stationary operan
 constexpr int kBwSTile = 64 * 64 * 2;                 //  8 KB streamed operand
 constexpr int kBwStat = 64 * 4;                       // 64 fp32 row statistics of a streamed query tile
 constexpr int kBwStageBytes = 2 * kBwSTile;           // A tile | B tile (1024-byte aligned: SWIZZLE_128B)
-constexpr int kBwThreads = 256;
+constexpr int kBwThreads = 384;                     // 4 control warps + 8 softmax-gradient warps (two per TMEM lane quarter)
 constexpr int kBwSmem = 2 * kBwXTile + kBwStages * (kBwStageBytes + 2 * kBwStat) + 1024;
 
 struct BwdParams {
@@ -45,6 +47,7 @@ struct BwdParams {
   int own_len, n_own_tiles;         // streamed rows / 64-row tiles per segment
   int over_prefix;               // mode 1: stream over all segments
   float scale_log2, scale;
+  int dbg;                       // timing experiments only (SR_ATTN_BWD_DBG): 1 = skip the exp / dS arithmetic, 2 = also skip TMEM loads
 };
 
 __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
@@ -85,7 +88,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
   if (warp == 1 && lane == 0) {
     mbar_init(&x_full, 1);
     mbar_init(&s_full, 1);
-    mbar_init(&p_ready, 4);
+    mbar_init(&p_ready, 8);
     mbar_init(&acc_done, 1);
     for (int s = 0; s < kBwStages; ++s) {
       mbar_init(&full[s], 1);
@@ -169,14 +172,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
           if (kMode == 0) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)       // dQ += dS K_j
-              umma_ts(tmem_acc0, tmem_dP + k * 8, umma_desc_sw128(a_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
+              umma_ts(tmem_acc0, tmem_dP + (k >> 1) * 32 + (k & 1) * 8, umma_desc_sw128(a_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
           } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k)       // dV += P^T dO_i
-              umma_ts(tmem_acc0, tmem_S + k * 8, umma_desc_sw128(b_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
+              umma_ts(tmem_acc0, tmem_S + (k >> 1) * 32 + (k & 1) * 8, umma_desc_sw128(b_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
 #pragma unroll
             for (int k = 0; k < 4; ++k)       // dK += dS^T Q_i
-              umma_ts(tmem_acc1, tmem_dP + k * 8, umma_desc_sw128(a_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
+              umma_ts(tmem_acc1, tmem_dP + (k >> 1) * 32 + (k & 1) * 8, umma_desc_sw128(a_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
           }
           umma_commit(&empty[s]);
           if (t == n_tiles - 1) umma_commit(&acc_done);
@@ -185,14 +188,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
       }
     }
   } else {
-    // ------------------------------------------------------------------ softmax-gradient warps: one thread per TMEM lane
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 200;");
+    // ------------------------------------------------------------------ softmax-gradient warps: TWO threads per TMEM lane
+    // (warps 4-7 own score columns 0-31 of every tile, warps 8-11 columns 32-63).  Each half writes its bf16 P / dS back
+    // into the first 16 columns of ITS OWN 32-column range, so the two warps of a lane quarter never touch each other's
+    // columns: the A operand of the TS MMAs is read at column offsets 0, 8, 32, 40 (see the issuer).
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 88;");
     const int quarter = warp & 3;
+    const int hlf = (warp - 4) >> 2;
     const int r_tile = quarter * 32 + lane;                 // stationary row inside the tile == TMEM lane
     const int x_row = x0 + r_tile;                          // row inside the segment (or the prefix)
     const bool row_ok = x_row < p.x_len;
     const uint32_t lane_off = static_cast<uint32_t>(quarter * 32) << 16;
-    const uint32_t tS = tmem_S + lane_off, tDP = tmem_dP + lane_off;
+    const uint32_t tS = tmem_S + lane_off + hlf * 32, tDP = tmem_dP + lane_off + hlf * 32;
 
     float lse_r = INFINITY, delta_r = 0.f;                  // mode 0: statistics of this thread's query row
     if (kMode == 0 && row_ok) {
@@ -212,19 +219,26 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
       if (kMode == 1) mbar_wait(&full[s], (t / kBwStages) & 1);   // the bulk-copied statistics are visible to this thread
       mbar_wait(&s_full, t & 1);
       tc_fence_after();
-      uint32_t pkp[32], pkd[32];
+      uint32_t pkp[16], pkd[16];
+      if (p.dbg != 0) {
 #pragma unroll
-      for (int hlf = 0; hlf < 2; ++hlf) {
-        uint32_t sv[32], dv[32];
-        tmem_ld32(tS + hlf * 32, sv);
-        tmem_ld32(tDP + hlf * 32, dv);
+        for (int i = 0; i < 16; ++i) pkp[i] = pkd[i] = 0u;
+      }
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {                         // two chunks of 16 score columns
+        if (p.dbg & 2) continue;
+        uint32_t sv[16], dv[16];
+        tmem_ld16(tS + c * 16, sv);
+        tmem_ld16(tDP + c * 16, dv);
         tmem_ld_wait();
+        if (p.dbg & 1) { pkp[c] ^= sv[0] ^ dv[15]; continue; }
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) {
+        for (int i = 0; i < 16; i += 4) {
+          const int col = hlf * 32 + c * 16 + i;            // column inside the 64-wide tile
           float ls[4], dl[4];
           if (kMode == 1) {
-            const float4 a = lds128(stat + (hlf * 32 + i) * 4);
-            const float4 d = lds128(stat + kBwStat + (hlf * 32 + i) * 4);
+            const float4 a = lds128(stat + col * 4);
+            const float4 d = lds128(stat + kBwStat + col * 4);
             ls[0] = a.x; ls[1] = a.y; ls[2] = a.z; ls[3] = a.w;
             dl[0] = d.x; dl[1] = d.y; dl[2] = d.z; dl[3] = d.w;
           } else {
@@ -235,18 +249,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
             float e = ex2_approx(fmaf(__uint_as_float(sv[i + u]), p.scale_log2, -ls[u]));
-            if (kMode == 0 && hlf * 32 + i + u >= valid) e = 0.f;
+            if (kMode == 0 && col + u >= valid) e = 0.f;
             pv[u] = e;
             ds[u] = e * (__uint_as_float(dv[i + u]) - dl[u]) * p.scale;
           }
-          pkp[hlf * 16 + (i >> 1)] = cvt_bf16x2(pv[0], pv[1]);
-          pkp[hlf * 16 + (i >> 1) + 1] = cvt_bf16x2(pv[2], pv[3]);
-          pkd[hlf * 16 + (i >> 1)] = cvt_bf16x2(ds[0], ds[1]);
-          pkd[hlf * 16 + (i >> 1) + 1] = cvt_bf16x2(ds[2], ds[3]);
+          pkp[c * 8 + (i >> 1)] = cvt_bf16x2(pv[0], pv[1]);
+          pkp[c * 8 + (i >> 1) + 1] = cvt_bf16x2(pv[2], pv[3]);
+          pkd[c * 8 + (i >> 1)] = cvt_bf16x2(ds[0], ds[1]);
+          pkd[c * 8 + (i >> 1) + 1] = cvt_bf16x2(ds[2], ds[3]);
         }
       }
-      if (kMode == 1) tmem_st32(tS, pkp);                   // P^T over S^T (both halves of S^T are in registers by now)
-      tmem_st32(tDP, pkd);                                  // dS over dP
+      if (kMode == 1) tmem_st16(tS, pkp);                   // P^T over the first half of this warp's own S^T columns
+      tmem_st16(tDP, pkd);                                  // dS likewise over dP
       tmem_st_wait();
       tc_fence_before();
       if (elect_one()) mbar_arrive(&p_ready);
@@ -259,22 +273,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
 #pragma unroll
     for (int which = 0; which < (kMode == 0 ? 1 : 2); ++which) {
       __nv_bfloat16* base = which == 0 ? p.d0 : p.d1;
+      uint32_t o[32];
+      tmem_ld32((which == 0 ? tmem_acc0 : tmem_acc1) + lane_off + hlf * 32, o);
+      tmem_ld_wait();
+      if (row_ok) {
+        __nv_bfloat16* dst = base + g_row * p.ldd + head * 64 + hlf * 32;
 #pragma unroll
-      for (int hlf = 0; hlf < 2; ++hlf) {
-        uint32_t o[32];
-        tmem_ld32((which == 0 ? tmem_acc0 : tmem_acc1) + lane_off + hlf * 32, o);
-        tmem_ld_wait();
-        if (row_ok) {
-          __nv_bfloat16* dst = base + g_row * p.ldd + head * 64 + hlf * 32;
-#pragma unroll
-          for (int i = 0; i < 32; i += 8) {
-            uint4 w;
-            w.x = pack_bf16x2(__uint_as_float(o[i + 0]), __uint_as_float(o[i + 1]));
-            w.y = pack_bf16x2(__uint_as_float(o[i + 2]), __uint_as_float(o[i + 3]));
-            w.z = pack_bf16x2(__uint_as_float(o[i + 4]), __uint_as_float(o[i + 5]));
-            w.w = pack_bf16x2(__uint_as_float(o[i + 6]), __uint_as_float(o[i + 7]));
-            *reinterpret_cast<uint4*>(dst + i) = w;
-          }
+        for (int i = 0; i < 32; i += 8) {
+          uint4 w;
+          w.x = pack_bf16x2(__uint_as_float(o[i + 0]), __uint_as_float(o[i + 1]));
+          w.y = pack_bf16x2(__uint_as_float(o[i + 2]), __uint_as_float(o[i + 3]));
+          w.z = pack_bf16x2(__uint_as_float(o[i + 4]), __uint_as_float(o[i + 5]));
+          w.w = pack_bf16x2(__uint_as_float(o[i + 6]), __uint_as_float(o[i + 7]));
+          *reinterpret_cast<uint4*>(dst + i) = w;
         }
       }
     }
@@ -414,6 +425,10 @@ extern "C" int sr_attn_bwd_bf16(const sr_attn_bwd_t* a, void* stream) {
   p.batch = a->batch;
   p.scale = a->scale;
   p.scale_log2 = a->scale * 1.4426950408889634f;
+  {
+    static const int dbg = [] { const char* e = getenv("SR_ATTN_BWD_DBG"); return e ? atoi(e) : 0; }();
+    p.dbg = dbg;
+  }
 
   // 2. dq: query-stationary pass over [prefix | own] K/V tiles
   p.d0 = reinterpret_cast<__nv_bfloat16*>(a->dq);

@@ -242,10 +242,10 @@ layernorm_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __re
 }
 
 // ------------------------------------------------------------------------------------------------ QK-norm + RoPE
-// One warp per (row, head): lane holds the ADJACENT features 2 lane, 2 lane + 1 (one 4-byte load per row; lanes 0-15 the y
-// half, 16-31 the x half); the rotate-half partner of feature j inside a half is j ^ 16 -> lane ^ 8, one shuffle each.
-// Four rows are in flight per iteration (loads first, then the shuffle reductions, then stores) to hide the latency
-// of the strided 128-byte row segments.  blockIdx.x = head slot in [0, 3H): q heads, k heads, v heads.
+// One warp = FOUR adjacent heads of a row (512 contiguous bytes): lane = 8 g + q holds features 8 q .. 8 q + 7 of head g as
+// one 16-byte load.  LayerNorm(64) reduces over the 8 lanes of a head (3 shuffles); the rotate-half partner of feature j
+// inside a half is j ^ 16 -> lane ^ 2.  Two rows per iteration, the next two rows' loads are issued before the current
+// ones are computed.  blockIdx.x = group of 4 head slots in [0, 3H / 4): q heads, k heads, v heads (H % 4 == 0).
 struct QkRopeParams {
   const float* qn_w; const float* qn_b; const float* kn_w; const float* kn_b;
   float eps;
@@ -257,101 +257,171 @@ struct QkRopeParams {
   int rows_per_warp;
 };
 
+__device__ __forceinline__ float sum8(float v) {      // over the 8 lanes of one head
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  return v;
+}
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  f[0] = bf16_lo(v.x); f[1] = bf16_hi(v.x); f[2] = bf16_lo(v.y); f[3] = bf16_hi(v.y);
+  f[4] = bf16_lo(v.z); f[5] = bf16_hi(v.z); f[6] = bf16_lo(v.w); f[7] = bf16_hi(v.w);
+}
+
 template <bool BWD>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 qknorm_rope_kernel(const __nv_bfloat16* __restrict__ raw, int64_t ldr, __nv_bfloat16* io, int64_t ldio,
                    float* __restrict__ dqn_w, float* __restrict__ dqn_b, float* __restrict__ dkn_w, float* __restrict__ dkn_b,
                    const QkRopeParams p) {
-  constexpr int U = 4;
+  constexpr int U = 2;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int slot = blockIdx.x;                        // head slot
-  const int which = slot / p.H;                       // 0 q, 1 k, 2 v
-  const int col = slot * 64 + 2 * lane;
+  const int which = (blockIdx.x * 4) / p.H;           // 0 q, 1 k, 2 v
+  const int col = blockIdx.x * 256 + lane * 8;
+  const int q = lane & 7;
   const int64_t r_begin = (static_cast<int64_t>(blockIdx.y) * 8 + warp) * p.rows_per_warp;
   const int64_t r_end = min(p.M, r_begin + p.rows_per_warp);
   if (which == 2) {
     if (!BWD) {
-      for (int64_t r = r_begin; r < r_end; r += U) {
-        uint32_t v[U];
+      for (int64_t r = r_begin; r < r_end; r += 4) {
+        uint4 v[4];
 #pragma unroll
-        for (int u = 0; u < U; ++u)
-          if (r + u < r_end) v[u] = *reinterpret_cast<const uint32_t*>(raw + (r + u) * ldr + col);
+        for (int u = 0; u < 4; ++u)
+          if (r + u < r_end) v[u] = *reinterpret_cast<const uint4*>(raw + (r + u) * ldr + col);
 #pragma unroll
-        for (int u = 0; u < U; ++u)
-          if (r + u < r_end) *reinterpret_cast<uint32_t*>(io + (r + u) * ldio + col) = v[u];
+        for (int u = 0; u < 4; ++u)
+          if (r + u < r_end) *reinterpret_cast<uint4*>(io + (r + u) * ldio + col) = v[u];
       }
     }
     return;
   }
   const float* nw = which == 0 ? p.qn_w : p.kn_w;
   const float* nb = which == 0 ? p.qn_b : p.kn_b;
-  float w0 = 1.f, w1 = 1.f, b0 = 0.f, b1 = 0.f;
-  if (p.qk_norm) { w0 = nw[2 * lane]; w1 = nw[2 * lane + 1]; b0 = nb[2 * lane]; b1 = nb[2 * lane + 1]; }
-  float aw0 = 0.f, aw1 = 0.f, ab0 = 0.f, ab1 = 0.f;
-  const int f = 2 * (lane & 7);                       // table column of the first feature (j & 15)
-  const bool is_a = (lane & 8) == 0;                  // first member of the (i, i + 16) pair
-  const bool x_half = lane >= 16;
+  float w[8], bb[8], aw[8], ab[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    w[e] = p.qk_norm ? nw[8 * q + e] : 1.f;
+    bb[e] = p.qk_norm ? nb[8 * q + e] : 0.f;
+    aw[e] = ab[e] = 0.f;
+  }
+  const int f = 8 * (q & 1);                          // table column of the lane's first feature (j & 15)
+  const bool is_a = (q & 2) == 0;                     // first member of the (i, i + 16) pair
+  const bool x_half = q >= 4;
+  const uint4 zero4 = make_uint4(0, 0, 0, 0);
+  uint4 nx[U], nd[U];                                 // prefetched rows
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const bool ok = r_begin + u < r_end;
+    nx[u] = ok ? *reinterpret_cast<const uint4*>(raw + (r_begin + u) * ldr + col) : zero4;
+    nd[u] = (BWD && ok) ? *reinterpret_cast<const uint4*>(io + (r_begin + u) * ldio + col) : zero4;
+  }
   for (int64_t r = r_begin; r < r_end; r += U) {
-    uint32_t xr[U], dr[U];
-    float2 cs[U], sn[U];
+    uint4 cx[U], cd[U];
+    float cs[U][8], sn[U][8];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
+      cx[u] = nx[u];
+      cd[u] = nd[u];
       const bool ok = r + u < r_end;
-      xr[u] = ok ? *reinterpret_cast<const uint32_t*>(raw + (r + u) * ldr + col) : 0u;
-      if (BWD) dr[u] = ok ? *reinterpret_cast<const uint32_t*>(io + (r + u) * ldio + col) : 0u;
-      cs[u] = make_float2(1.f, 1.f);
-      sn[u] = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { cs[u][e] = 1.f; sn[u][e] = 0.f; }
       if (p.rope && ok) {
         const int2 yx = __ldg(reinterpret_cast<const int2*>(p.pos) + (r + u));
         const int64_t t = static_cast<int64_t>(x_half ? yx.y : yx.x) * 16 + f;
-        cs[u] = __ldg(reinterpret_cast<const float2*>(p.rope_cos + t));
-        sn[u] = __ldg(reinterpret_cast<const float2*>(p.rope_sin + t));
+        const float4 c0 = __ldg(reinterpret_cast<const float4*>(p.rope_cos + t)), c1 = __ldg(reinterpret_cast<const float4*>(p.rope_cos + t + 4));
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.rope_sin + t)), s1 = __ldg(reinterpret_cast<const float4*>(p.rope_sin + t + 4));
+        cs[u][0] = c0.x; cs[u][1] = c0.y; cs[u][2] = c0.z; cs[u][3] = c0.w; cs[u][4] = c1.x; cs[u][5] = c1.y; cs[u][6] = c1.z; cs[u][7] = c1.w;
+        sn[u][0] = s0.x; sn[u][1] = s0.y; sn[u][2] = s0.z; sn[u][3] = s0.w; sn[u][4] = s1.x; sn[u][5] = s1.y; sn[u][6] = s1.z; sn[u][7] = s1.w;
       }
     }
-    uint32_t out[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {                     // next iteration's rows: in flight under the arithmetic below
+      const bool ok = r + U + u < r_end;
+      nx[u] = ok ? *reinterpret_cast<const uint4*>(raw + (r + U + u) * ldr + col) : zero4;
+      nd[u] = (BWD && ok) ? *reinterpret_cast<const uint4*>(io + (r + U + u) * ldio + col) : zero4;
+    }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      float x0 = bf16_lo(xr[u]), x1 = bf16_hi(xr[u]);
+      float x[8];
+      unpack8(cx[u], x);
       float rstd = 1.f;
       if (p.qk_norm) {
-        const float mean = warp_sum(x0 + x1) * (1.0f / 64.0f);
-        x0 -= mean; x1 -= mean;
-        rstd = rsqrtf(warp_sum(x0 * x0 + x1 * x1) * (1.0f / 64.0f) + p.eps);
-        x0 *= rstd; x1 *= rstd;                       // xhat
-      }
-      if (!BWD) {
-        float y0 = p.qk_norm ? x0 * w0 + b0 : x0, y1 = p.qk_norm ? x1 * w1 + b1 : x1;
-        const float o0 = __shfl_xor_sync(0xffffffffu, y0, 8), o1 = __shfl_xor_sync(0xffffffffu, y1, 8);
-        // pair (a, b) = (i, i + 16): a' = a c - b s ; b' = b c + a s
-        y0 = is_a ? y0 * cs[u].x - o0 * sn[u].x : y0 * cs[u].x + o0 * sn[u].x;
-        y1 = is_a ? y1 * cs[u].y - o1 * sn[u].y : y1 * cs[u].y + o1 * sn[u].y;
-        out[u] = pack_bf16x2(y0, y1);
-      } else {
-        float d0 = bf16_lo(dr[u]), d1 = bf16_hi(dr[u]);
-        const float o0 = __shfl_xor_sync(0xffffffffu, d0, 8), o1 = __shfl_xor_sync(0xffffffffu, d1, 8);
-        // da = da' c + db' s ; db = db' c - da' s
-        d0 = is_a ? d0 * cs[u].x + o0 * sn[u].x : d0 * cs[u].x - o0 * sn[u].x;
-        d1 = is_a ? d1 * cs[u].y + o1 * sn[u].y : d1 * cs[u].y - o1 * sn[u].y;
-        if (p.qk_norm) {
-          aw0 += d0 * x0; aw1 += d1 * x1; ab0 += d0; ab1 += d1;
-          const float g0 = d0 * w0, g1 = d1 * w1;
-          const float mg = warp_sum(g0 + g1) * (1.0f / 64.0f);
-          const float mgx = warp_sum(g0 * x0 + g1 * x1) * (1.0f / 64.0f);
-          d0 = rstd * (g0 - mg - x0 * mgx);
-          d1 = rstd * (g1 - mg - x1 * mgx);
-        }
-        out[u] = pack_bf16x2(d0, d1);
-      }
-    }
+        float sm = 0.f;
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-      if (r + u < r_end) *reinterpret_cast<uint32_t*>(io + (r + u) * ldio + col) = out[u];
+        for (int e = 0; e < 8; ++e) sm += x[e];
+        const float mean = sum8(sm) * (1.0f / 64.0f);
+        float sq = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { x[e] -= mean; sq += x[e] * x[e]; }
+        rstd = rsqrtf(sum8(sq) * (1.0f / 64.0f) + p.eps);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) x[e] *= rstd;      // xhat
+      }
+      float o[8];
+      if (!BWD) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float y = p.qk_norm ? x[e] * w[e] + bb[e] : x[e];
+          const float oth = __shfl_xor_sync(0xffffffffu, y, 2);
+          // pair (a, b) = (i, i + 16): a' = a c - b s ; b' = b c + a s
+          o[e] = is_a ? y * cs[u][e] - oth * sn[u][e] : y * cs[u][e] + oth * sn[u][e];
+        }
+      } else {
+        float d[8];
+        unpack8(cd[u], d);
+        float sg = 0.f, sgx = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float oth = __shfl_xor_sync(0xffffffffu, d[e], 2);
+          // da = da' c + db' s ; db = db' c - da' s
+          d[e] = is_a ? d[e] * cs[u][e] + oth * sn[u][e] : d[e] * cs[u][e] - oth * sn[u][e];
+          if (p.qk_norm) {
+            aw[e] += d[e] * x[e];
+            ab[e] += d[e];
+            d[e] *= w[e];                              // g
+            sg += d[e];
+            sgx += d[e] * x[e];
+          }
+        }
+        if (p.qk_norm) {
+          const float mg = sum8(sg) * (1.0f / 64.0f), mgx = sum8(sgx) * (1.0f / 64.0f);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) d[e] = rstd * (d[e] - mg - x[e] * mgx);
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = d[e];
+      }
+      if (r + u < r_end)
+        *reinterpret_cast<uint4*>(io + (r + u) * ldio + col) =
+            make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+    }
   }
   if (BWD && p.qk_norm) {
-    float* gw = which == 0 ? dqn_w : dkn_w;
-    float* gb = which == 0 ? dqn_b : dkn_b;
-    if (gw) { atomicAdd(gw + 2 * lane, aw0); atomicAdd(gw + 2 * lane + 1, aw1); }
-    if (gb) { atomicAdd(gb + 2 * lane, ab0); atomicAdd(gb + 2 * lane + 1, ab1); }
+    // the 64 + 64 parameter gradients live in 16 sectors of L2: atomics from every warp serialise there (measured: 2/3 of
+    // the kernel's time), so reduce over the warp's 4 heads (shuffles) and the CTA's 8 warps (shared memory) first
+    __shared__ float red[8][2][64];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      aw[e] += __shfl_xor_sync(0xffffffffu, aw[e], 8);
+      aw[e] += __shfl_xor_sync(0xffffffffu, aw[e], 16);
+      ab[e] += __shfl_xor_sync(0xffffffffu, ab[e], 8);
+      ab[e] += __shfl_xor_sync(0xffffffffu, ab[e], 16);
+    }
+    if (lane < 8) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        red[warp][0][8 * q + e] = aw[e];
+        red[warp][1][8 * q + e] = ab[e];
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < 128) {
+      const int wb = threadIdx.x >> 6, c = threadIdx.x & 63;
+      float t = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) t += red[k][wb][c];
+      float* dst = wb == 0 ? (which == 0 ? dqn_w : dkn_w) : (which == 0 ? dqn_b : dkn_b);
+      if (dst) atomicAdd(dst + c, t);
+    }
   }
 }
 
@@ -510,8 +580,9 @@ static int qk_launch(bool bwd, const void* raw, int64_t ldr, void* io, int64_t l
   if (int rc = require_sm100()) return rc;
   SR_REQUIRE(raw && io && e && M > 0, "sr_qknorm_rope: null pointer / empty");
   SR_REQUIRE(e->head_dim == 64 && e->qkv_dim > 0 && e->qkv_dim % 64 == 0, "sr_qknorm_rope: head_dim must be 64");
-  SR_REQUIRE(ldr % 2 == 0 && ldio % 2 == 0 && ((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(io)) & 3) == 0,
-             "sr_qknorm_rope: buffers must be 4-byte aligned with even row strides");
+  SR_REQUIRE(ldr % 8 == 0 && ldio % 8 == 0 && ((reinterpret_cast<uintptr_t>(raw) | reinterpret_cast<uintptr_t>(io)) & 15) == 0 &&
+                 (e->qkv_dim / 64) % 4 == 0,
+             "sr_qknorm_rope: buffers must be 16-byte aligned, row strides multiples of 8, heads a multiple of 4");
   if (e->qk_norm) SR_REQUIRE(e->qn_w && e->qn_b && e->kn_w && e->kn_b, "sr_qknorm_rope: q/k norm parameters missing");
   if (e->rope) SR_REQUIRE(e->rope_cos && e->rope_sin && e->pos, "sr_qknorm_rope: RoPE tables / positions missing");
   QkRopeParams p;
@@ -522,7 +593,7 @@ static int qk_launch(bool bwd, const void* raw, int64_t ldr, void* io, int64_t l
   p.H = static_cast<int>(e->qkv_dim / 64);
   p.M = M;
   p.rows_per_warp = 32;
-  dim3 grid(static_cast<unsigned>(3 * p.H), static_cast<unsigned>((M + 8 * p.rows_per_warp - 1) / (8 * p.rows_per_warp)));
+  dim3 grid(static_cast<unsigned>(3 * p.H / 4), static_cast<unsigned>((M + 8 * p.rows_per_warp - 1) / (8 * p.rows_per_warp)));
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (bwd)
     qknorm_rope_kernel<true><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(raw), ldr, reinterpret_cast<__nv_bfloat16*>(io),
