@@ -45,34 +45,46 @@ transpose_bf16_kernel(const __nv_bfloat16* __restrict__ src, int64_t lds, __nv_b
 // gradient of the Linear whose dY this is) come for free: 3 shuffles + one atomic per (column, tile).
 __global__ void __launch_bounds__(256)
 transpose_bf16_vec_kernel(const __nv_bfloat16* __restrict__ src, int64_t lds, __nv_bfloat16* __restrict__ dst, int64_t ldd,
-                          int R, int C, float* __restrict__ colsum) {
-  __shared__ __align__(16) uint32_t tile[64 * 33];                 // 64 rows x 64 bf16, row stride 33 words
-  const int r0 = blockIdx.x * 64, c0 = blockIdx.y * 64;
+                          int R, int C, int R_pad, float* __restrict__ colsum) {
+  constexpr int kTilesPerCta = 4;                                  // 256 source rows per CTA: one atomic per column and CTA
+  __shared__ __align__(16) uint32_t tile[2][64 * 33];              // 64 rows x 64 bf16, row stride 33 words, double-buffered
+  const int c0 = blockIdx.y * 64;
   const int t = threadIdx.x;
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int r = (t >> 3) + 32 * h, c8 = t & 7;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if (r0 + r < R && c0 + c8 * 8 < C) v = *reinterpret_cast<const uint4*>(src + static_cast<int64_t>(r0 + r) * lds + c0 + c8 * 8);
-    uint32_t* w = tile + r * 33 + c8 * 4;
-    w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
-  }
-  __syncthreads();
   const int warp = t >> 5, lane = t & 31, k = lane & 7;
-  const __nv_bfloat16* tb = reinterpret_cast<const __nv_bfloat16*>(tile);
+  float sums[2] = {0.f, 0.f};
+#pragma unroll 1
+  for (int it = 0; it < kTilesPerCta; ++it) {
+    const int r0 = (blockIdx.x * kTilesPerCta + it) * 64;
+    if (r0 >= R_pad) break;
+    uint32_t* tl = tile[it & 1];
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int c = warp * 8 + i * 4 + (lane >> 3);
-    uint32_t o[4];
-    float sum = 0.f;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const __nv_bfloat16 a = tb[(8 * k + 2 * j) * 66 + c], b = tb[(8 * k + 2 * j + 1) * 66 + c];
-      o[j] = static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
-      sum += __bfloat162float(a) + __bfloat162float(b);
+    for (int h = 0; h < 2; ++h) {
+      const int r = (t >> 3) + 32 * h, c8 = t & 7;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (r0 + r < R && c0 + c8 * 8 < C) v = *reinterpret_cast<const uint4*>(src + static_cast<int64_t>(r0 + r) * lds + c0 + c8 * 8);
+      uint32_t* w = tl + r * 33 + c8 * 4;
+      w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
     }
-    if (c0 + c < C) *reinterpret_cast<uint4*>(dst + static_cast<int64_t>(c0 + c) * ldd + r0 + 8 * k) = make_uint4(o[0], o[1], o[2], o[3]);
-    if (colsum != nullptr) {
+    __syncthreads();                                               // (the other buffer is free: its readers passed the previous barrier)
+    const __nv_bfloat16* tb = reinterpret_cast<const __nv_bfloat16*>(tl);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int c = warp * 8 + i * 4 + (lane >> 3);
+      uint32_t o[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const __nv_bfloat16 a = tb[(8 * k + 2 * j) * 66 + c], b = tb[(8 * k + 2 * j + 1) * 66 + c];
+        o[j] = static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
+        sums[i] += __bfloat162float(a) + __bfloat162float(b);
+      }
+      if (c0 + c < C) *reinterpret_cast<uint4*>(dst + static_cast<int64_t>(c0 + c) * ldd + r0 + 8 * k) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+  }
+  if (colsum != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int c = warp * 8 + i * 4 + (lane >> 3);
+      float sum = sums[i];
       sum += __shfl_xor_sync(0xffffffffu, sum, 1);
       sum += __shfl_xor_sync(0xffffffffu, sum, 2);
       sum += __shfl_xor_sync(0xffffffffu, sum, 4);
@@ -489,10 +501,12 @@ extern "C" int sr_transpose_bf16(const void* src, int64_t lds, void* dst, int64_
                    ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
   SR_REQUIRE(vec || colsum == nullptr, "sr_transpose_bf16: the fused column sum needs the 16-byte aligned layout "
                                        "(R_pad % 64 == 0, C, lds, ldd multiples of 8)");
-  if (vec)
-    transpose_bf16_vec_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(src), lds,
-                                                    reinterpret_cast<__nv_bfloat16*>(dst), ldd, static_cast<int>(R),
-                                                    static_cast<int>(C), colsum);
+  if (vec) {
+    dim3 vgrid(static_cast<unsigned>((R_pad / 64 + 3) / 4), grid.y);
+    transpose_bf16_vec_kernel<<<vgrid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(src), lds,
+                                                     reinterpret_cast<__nv_bfloat16*>(dst), ldd, static_cast<int>(R),
+                                                     static_cast<int>(C), static_cast<int>(R_pad), colsum);
+  }
   else
     transpose_bf16_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(src), lds,
                                                 reinterpret_cast<__nv_bfloat16*>(dst), ldd, static_cast<int>(R), static_cast<int>(C),
