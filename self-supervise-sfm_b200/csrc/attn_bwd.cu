@@ -15,7 +15,9 @@
 //            tiles of EVERY segment (the prefix gradient is the sum over the segments).
 // TMEM per CTA: S 64 | dP 64 | acc0 64 | acc1 64 = 256 columns, 80 KB of smem: two CTAs per SM, whose MMA and softmax
 // phases interleave (inside one CTA the tile loop is serial: SS -> softmax -> TS).
-//   warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4-7 one thread per TMEM lane.
+//   warp 0 TMA producer, warp 1 MMA issuer, warp 2 TMEM allocator, warps 4-11 softmax gradient: two threads per TMEM lane
+//   (warps 4-7 score columns 0-31, warps 8-11 columns 32-63).  kMode 0 has a spare accumulator: dS is double-buffered there
+//   and S(t+1) / dP(t+1) are issued under the arithmetic of tile t.
 #include <cstdlib>
 
 #include "attn_math.cuh"
@@ -62,7 +64,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
                 const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                 const __grid_constant__ CUtensorMap tm_pa, const __grid_constant__ CUtensorMap tm_pb, const BwdParams p) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t x_full, s_full, p_ready, acc_done;
+  __shared__ __align__(8) uint64_t x_full, s_full, p_ready, acc_done, sdp_free;
   __shared__ __align__(8) uint64_t full[kBwStages], empty[kBwStages];
   __shared__ uint32_t tmem_base_slot;
 
@@ -89,6 +91,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
     mbar_init(&x_full, 1);
     mbar_init(&s_full, 1);
     mbar_init(&p_ready, 8);
+    mbar_init(&sdp_free, 8);
     mbar_init(&acc_done, 1);
     for (int s = 0; s < kBwStages; ++s) {
       mbar_init(&full[s], 1);
@@ -150,15 +153,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
       const uint64_t dx = umma_desc_sw128(smem_u32(sX), 16, 1024);
       const uint64_t dy = umma_desc_sw128(smem_u32(sY), 16, 1024);
       mbar_wait(&x_full, 0);
-      for (int t = 0; t < n_tiles; ++t) {
+      auto issue_ss = [&](int t) {                           // S(t) = X A_t^T, dP(t) = Y B_t^T into the S / dP columns
         const int s = t % kBwStages;
         const uint32_t a_addr = smem_u32(sStage + s * kBwStageBytes);
-        const uint32_t b_addr = a_addr + kBwSTile;
         mbar_wait(&full[s], (t / kBwStages) & 1);
         tc_fence_after();
         if (elect_one()) {
           const uint64_t da = umma_desc_sw128(a_addr, 16, 1024);
-          const uint64_t db = umma_desc_sw128(b_addr, 16, 1024);
+          const uint64_t db = umma_desc_sw128(a_addr + kBwSTile, 16, 1024);
 #pragma unroll
           for (int k = 0; k < 4; ++k) umma_ss(tmem_S, dx + 2 * k, da + 2 * k, idesc_s, k != 0 ? 1u : 0u);
 #pragma unroll
@@ -166,25 +168,53 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
           umma_commit(&s_full);
         }
         __syncwarp();
-        mbar_wait(&p_ready, t & 1);
-        tc_fence_after();
-        if (elect_one()) {
-          if (kMode == 0) {
+      };
+      if (kMode == 0) {
+        // Query-stationary pass: dS(t) goes to its own double-buffered columns (the unused second accumulator), so
+        // S(t+1) / dP(t+1) are issued as soon as the softmax warps have READ S(t) / dP(t) (sdp_free) and run under the
+        // arithmetic of tile t; the in-order tensor pipe then gives  SS(t+1), TS(t), SS(t+2), TS(t+1), ...
+        issue_ss(0);
+        for (int t = 0; t < n_tiles; ++t) {
+          const int s = t % kBwStages;
+          const uint32_t a_addr = smem_u32(sStage + s * kBwStageBytes);
+          if (t + 1 < n_tiles) {
+            mbar_wait(&sdp_free, t & 1);
+            issue_ss(t + 1);
+          }
+          mbar_wait(&p_ready, t & 1);
+          tc_fence_after();
+          if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)       // dQ += dS K_j
-              umma_ts(tmem_acc0, tmem_dP + (k >> 1) * 32 + (k & 1) * 8, umma_desc_sw128(a_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
-          } else {
+              umma_ts(tmem_acc0, tmem_acc1 + (t & 1) * 32 + k * 8, umma_desc_sw128(a_addr + k * 2048, 0, 1024), idesc_t,
+                      (t > 0 || k != 0) ? 1u : 0u);
+            umma_commit(&empty[s]);
+            if (t == n_tiles - 1) umma_commit(&acc_done);
+          }
+          __syncwarp();
+        }
+      } else {
+        for (int t = 0; t < n_tiles; ++t) {
+          const int s = t % kBwStages;
+          const uint32_t a_addr = smem_u32(sStage + s * kBwStageBytes);
+          const uint32_t b_addr = a_addr + kBwSTile;
+          issue_ss(t);
+          mbar_wait(&p_ready, t & 1);
+          tc_fence_after();
+          if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)       // dV += P^T dO_i
-              umma_ts(tmem_acc0, tmem_S + (k >> 1) * 32 + (k & 1) * 8, umma_desc_sw128(b_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
+              umma_ts(tmem_acc0, tmem_S + (k >> 1) * 32 + (k & 1) * 8, umma_desc_sw128(b_addr + k * 2048, 0, 1024), idesc_t,
+                      (t > 0 || k != 0) ? 1u : 0u);
 #pragma unroll
             for (int k = 0; k < 4; ++k)       // dK += dS^T Q_i
-              umma_ts(tmem_acc1, tmem_dP + (k >> 1) * 32 + (k & 1) * 8, umma_desc_sw128(a_addr + k * 2048, 0, 1024), idesc_t, (t > 0 || k != 0) ? 1u : 0u);
+              umma_ts(tmem_acc1, tmem_dP + (k >> 1) * 32 + (k & 1) * 8, umma_desc_sw128(a_addr + k * 2048, 0, 1024), idesc_t,
+                      (t > 0 || k != 0) ? 1u : 0u);
+            umma_commit(&empty[s]);
+            if (t == n_tiles - 1) umma_commit(&acc_done);
           }
-          umma_commit(&empty[s]);
-          if (t == n_tiles - 1) umma_commit(&acc_done);
+          __syncwarp();
         }
-        __syncwarp();
       }
     }
   } else {
@@ -226,11 +256,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
       }
 #pragma unroll
       for (int c = 0; c < 2; ++c) {                         // two chunks of 16 score columns
-        if (p.dbg & 2) continue;
+        if (p.dbg & 2) {
+          if (kMode == 0 && c == 1 && elect_one()) mbar_arrive(&sdp_free);
+          continue;
+        }
         uint32_t sv[16], dv[16];
         tmem_ld16(tS + c * 16, sv);
         tmem_ld16(tDP + c * 16, dv);
         tmem_ld_wait();
+        if (kMode == 0 && c == 1) {                         // S(t) / dP(t) are in registers: the issuer may overwrite them
+          tc_fence_before();
+          if (elect_one()) mbar_arrive(&sdp_free);
+        }
         if (p.dbg & 1) { pkp[c] ^= sv[0] ^ dv[15]; continue; }
 #pragma unroll
         for (int i = 0; i < 16; i += 4) {
@@ -259,8 +296,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
           pkd[c * 8 + (i >> 1) + 1] = cvt_bf16x2(ds[2], ds[3]);
         }
       }
-      if (kMode == 1) tmem_st16(tS, pkp);                   // P^T over the first half of this warp's own S^T columns
-      tmem_st16(tDP, pkd);                                  // dS likewise over dP
+      if (kMode == 1) {
+        tmem_st16(tS, pkp);                                 // P^T over the first half of this warp's own S^T columns
+        tmem_st16(tDP, pkd);                                // dS^T likewise over dP^T
+      } else {
+        tmem_st16(tmem_acc1 + lane_off + (t & 1) * 32 + hlf * 16, pkd);   // dS(t): buffer t & 1 of the spare accumulator columns
+      }
       tmem_st_wait();
       tc_fence_before();
       if (elect_one()) mbar_arrive(&p_ready);
