@@ -282,13 +282,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
 #pragma unroll
             for (int u = 0; u < 4; ++u) { ls[u] = lse_r; dl[u] = delta_r; }
           }
+          // dS' = P (dP - delta): the softmax scale is applied once to the dQ / dK accumulators in the epilogue
           float pv[4], ds[4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            float e = ex2_approx(fmaf(__uint_as_float(sv[i + u]), p.scale_log2, -ls[u]));
-            if (kMode == 0 && col + u >= valid) e = 0.f;
-            pv[u] = e;
-            ds[u] = e * (__uint_as_float(dv[i + u]) - dl[u]) * p.scale;
+            pv[u] = ex2_approx(fmaf(__uint_as_float(sv[i + u]), p.scale_log2, -ls[u]));
+            ds[u] = pv[u] * (__uint_as_float(dv[i + u]) - dl[u]);
+          }
+          if (kMode == 0 && col + 4 > valid) {              // only the last, partial K/V tile of a segment masks
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (col + u >= valid) pv[u] = ds[u] = 0.f;
           }
           pkp[c * 8 + (i >> 1)] = cvt_bf16x2(pv[0], pv[1]);
           pkp[c * 8 + (i >> 1) + 1] = cvt_bf16x2(pv[2], pv[3]);
@@ -317,6 +321,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
       uint32_t o[32];
       tmem_ld32((which == 0 ? tmem_acc0 : tmem_acc1) + lane_off + hlf * 32, o);
       tmem_ld_wait();
+      if (kMode == 0 || which == 1) {                       // dQ / dK were accumulated from the unscaled dS'
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * p.scale);
+      }
       if (row_ok) {
         __nv_bfloat16* dst = base + g_row * p.ldd + head * 64 + hlf * 32;
 #pragma unroll
