@@ -144,6 +144,21 @@ ls_residual_kernel(const float* __restrict__ resid, const __nv_bfloat16* __restr
   *reinterpret_cast<float4*>(out + e) = y;
 }
 
+// erf by Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, the form the GEMM's fused GELU epilogue uses): one rcp, one ex2 and
+// 8 FMAs instead of the ~27 branchy instructions of erff(); the same exponential exp(-x^2 / 2) is the Gaussian density
+// the derivative needs.  erf_abs = erf(|x| / sqrt 2), e = exp(-x^2 / 2).
+__device__ __forceinline__ void erf_gauss(float x, float& erf_abs, float& e) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -1.4426950408889634f));
+  erf_abs = fmaf(-poly * t, e, 1.0f);
+}
+
 // mode 0: out = bf16(gelu_erf(u));  mode 1: out = bf16(dg * gelu'(u)),  gelu'(u) = Phi(u) + u * phi(u)
 template <int kMode>
 __global__ void __launch_bounds__(256)
@@ -161,12 +176,14 @@ gelu_kernel(const __nv_bfloat16* __restrict__ u, const __nv_bfloat16* __restrict
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
       const float x = h ? bf16_hi(uw[i]) : bf16_lo(uw[i]);
+      float erf_abs, e;
+      erf_gauss(x, erf_abs, e);
       if (kMode == 0) {
-        r[h] = gelu_erf(x);
+        const float hx = 0.5f * x;
+        r[h] = fmaf(fabsf(hx), erf_abs, hx);                 // 0.5 x (1 + sign(x) erf_abs)
       } else {
-        const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752440f));
-        const float pdf = 0.39894228040143267794f * __expf(-0.5f * x * x);
-        r[h] = (h ? bf16_hi(gw[i]) : bf16_lo(gw[i])) * (cdf + x * pdf);
+        const float cdf = 0.5f + copysignf(0.5f * erf_abs, x);
+        r[h] = (h ? bf16_hi(gw[i]) : bf16_lo(gw[i])) * fmaf(x, 0.39894228040143267794f * e, cdf);
       }
     }
     ow[i] = pack_bf16x2(r[0], r[1]);
