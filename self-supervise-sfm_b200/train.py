@@ -149,9 +149,14 @@ def linear_backward(lin: nn.Module, a_in: torch.Tensor, dz: torch.Tensor, grads:
     aT = ops.transpose_bf16(a_in)                                  # [K, T_pad]
     gw = _acc(grads, lin.weight)
     if N % 128 == 0 and K % 128 == 0:
-        tmp = torch.empty(N, K, dtype=torch.float32, device=dev)
-        ops.gemm(dzT, aT, None, tmp, kind=SR_EPI_BIAS)             # [N, T_pad] x [K, T_pad]^T
-        gw.view(N, K).add_(tmp)
+        fresh = getattr(grads, "fresh", None)
+        if fresh is not None and lin.weight in fresh:              # first contribution since zero_grad: write, do not add
+            fresh.discard(lin.weight)
+            ops.gemm(dzT, aT, None, gw.view(N, K), kind=SR_EPI_BIAS)   # [N, T_pad] x [K, T_pad]^T
+        else:
+            tmp = torch.empty(N, K, dtype=torch.float32, device=dev)
+            ops.gemm(dzT, aT, None, tmp, kind=SR_EPI_BIAS)
+            gw.view(N, K).add_(tmp)
     else:
         raise NotImplementedError("sailrecon_b200: Linear gradients need in / out features that are multiples of 128")
     if not need_input_grad:
@@ -334,6 +339,13 @@ def layer_backward(fblk: nn.Module, gblk: nn.Module, rblk: nn.Module, X_in: torc
 
 
 # ------------------------------------------------------------------------------------------------ the 3 x depth block stack
+class GradViews(dict):
+    """parameter -> fp32 gradient view.  `fresh` = the 2-D (Linear weight) parameters that have not received a gradient since
+    zero_grad: linear_backward lets the wgrad GEMM write those views directly instead of GEMM -> temporary -> add
+    (the reloc block's qkv weight gets two contributions per step, scene tokens and query frames: the second one adds)."""
+    fresh: set = frozenset()
+
+
 class TrainState:
     """Optimizer-side state of the aggregator's block stacks (frame / global / global_reloc, aggregator.py:99-149), one flat
     fp32 bucket per layer index i holding the parameters of frame_blocks[i], global_blocks[i] and global_reloc_blocks[i]:
@@ -351,7 +363,7 @@ class TrainState:
         self.grad: List[torch.Tensor] = []
         self.m: List[torch.Tensor] = []
         self.v: List[torch.Tensor] = []
-        self.grads: Dict[nn.Parameter, torch.Tensor] = {}
+        self.grads: "GradViews" = GradViews()
         self.params_of_layer: List[List[nn.Parameter]] = []
         for i in range(agg.depth):
             ps = [p for blk in (agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i]) for p in blk.parameters()]
@@ -377,6 +389,7 @@ class TrainState:
     def zero_grad(self) -> None:
         for g in self.grad:
             g.zero_()
+        self.grads.fresh = {p for ps in self.params_of_layer for p in ps if p.dim() == 2}
 
     def adam_step(self, grad_scale: float = 1.0) -> None:
         self.step += 1
