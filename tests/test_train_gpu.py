@@ -4,6 +4,7 @@ mlp.py:33-40, layer_scale.py:22).  The kernels run the bf16 autocast arithmetic 
 reference here is fp32: tolerances are the bf16 ones of north_star (2e-2 relative L2), 3e-2 for parameter gradients.
 """
 import math
+import os
 
 import pytest
 import torch
@@ -397,3 +398,77 @@ def test_training_step_two_layers_matches_fp32_autograd_and_adam(keep_activation
     # the cached bf16 weights follow the update
     w = agg.frame_blocks[0].mlp.fc1
     assert torch.equal(engine.weight_bf16(w), w.weight.detach().to(torch.bfloat16))
+
+
+# ------------------------------------------------------------------------------------------------ data parallel over NCCL
+def _dp_setup(seed_scene):
+    """A 1-layer stack + one small scene (2 anchors + 2 queries of 150 tokens); the scene differs per seed."""
+    from sailrecon_b200 import engine, train
+    Na, Nq, Pn, C = 2, 2, 150, 1024
+    S = Na + Nq
+    agg = _Stacks(1, 91)
+    pos = _positions(S, Pn)
+    ctx = train.LayerCtx(Na, Nq, Pn, engine.RowPositions(pos.to(torch.int32).contiguous(), int(pos.max()) + 1))
+    gidx = torch.Generator().manual_seed(7)
+    idx = torch.cat([a * Pn + torch.cat([torch.arange(5), 5 + torch.randperm(Pn - 5, generator=gidx)[:30]]) for a in range(Na)])
+    idx_d = idx.to(torch.int32).to(DEV)
+    spos = engine.RowPositions(ctx.rows_pos.pos32[idx_d.long()].contiguous(), ctx.rows_pos.max_pos)
+    X0 = _randn(S * Pn, C, seed=100 + seed_scene)
+    d_out = {0: (_randn(S * Pn, C, seed=200 + seed_scene) * 0.5, _randn(S * Pn, C, seed=300 + seed_scene))}
+    return agg, ctx, (lambda: (idx_d, spos)), X0, d_out
+
+
+def _dp_worker(rank, world, port, out_path):
+    import torch.distributed as dist
+    from sailrecon_b200 import train
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        global DEV
+        DEV = f"cuda:{rank}"
+        agg, ctx, draw, X0, d_out = _dp_setup(rank)
+        state = train.TrainState(agg, lr=1e-3)
+        train.training_step(agg, state, X0, ctx, draw, d_out, world=world)
+        torch.cuda.synchronize()
+        torch.save({k: p.detach().cpu() for k, p in agg.named_parameters()}, f"{out_path}.{rank}")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs (gpurun --gpus 2)")
+def test_training_step_two_processes_nccl(tmp_path):
+    """DDP semantics of train_imc.py:472 on real kernels: two ranks, one (different) scene each, per-layer NCCL all-reduce.
+    Both ranks must end with identical parameters, equal to ONE Adam step on the mean of the two scenes' gradients
+    (computed here in a single process with the same kernels)."""
+    import socket
+
+    import torch.multiprocessing as mp
+    from sailrecon_b200 import train
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = str(tmp_path / "dp")
+    mp.spawn(_dp_worker, args=(2, port, out), nprocs=2, join=True)
+    got = [torch.load(f"{out}.{r}") for r in range(2)]
+    for k in got[0]:
+        assert torch.equal(got[0][k], got[1][k]), k                                # replicas stay bit-identical
+    # single-process reference: gradients of both scenes, mean, torch.optim.Adam
+    mean = None
+    for scene in range(2):
+        agg, ctx, draw, X0, d_out = _dp_setup(scene)
+        before = {k: p.detach().clone() for k, p in agg.named_parameters()}
+        state = train.TrainState(agg, lr=1e-3)
+        train.training_step(agg, state, X0, ctx, draw, d_out, optimizer_step=lambda grad_scale: None)
+        g = {k: state.grads[p].clone() for k, p in agg.named_parameters()}
+        mean = g if mean is None else {k: (mean[k] + g[k]) * 0.5 for k in g}
+    worst = 0.0
+    for k, w0 in before.items():
+        ref = torch.nn.Parameter(w0.clone())
+        ref.grad = mean[k]
+        torch.optim.Adam([ref], lr=1e-3, betas=(0.9, 0.999), eps=1e-8).step()
+        # first Adam step = lr * g / (|g| + eps): a gradient that differs in the last bits (atomic summation order) moves the
+        # update by far less than lr
+        worst = max(worst, (got[0][k].to(DEV) - ref.detach()).abs().max().item())
+    assert worst < 2e-4, worst
