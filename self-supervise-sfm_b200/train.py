@@ -481,14 +481,32 @@ def stack_backward(agg: nn.Module, ck: list, d_out: Dict[int, tuple], ctx: Layer
     return dX
 
 
+def activation_bytes(ctx: LayerCtx, depth: int, C: int, scene_rows: int = 0) -> int:
+    """HBM needed to keep every activation the backward reads (layer_forward_saving) for `depth` layers.  Per token row of a
+    block: bf16 h1, raw qkv, qkv, o, z1, h2, u, g, z2 = 19 C elements and fp32 x1 + block output = 2 C elements; every row
+    goes through the frame block and through one of the global / reloc blocks; scene rows keep a_s, raw and post (7 C bf16).
+    The fp32 log-sum-exp rows (H floats per row and block) are included with H = C / 64."""
+    T = (ctx.Na + ctx.Nq) * ctx.P
+    per_row = 19 * C * 2 + 2 * C * 4 + (C // 64) * 4
+    return depth * (2 * T * per_row + scene_rows * 7 * C * 2)
+
+
+def choose_keep_activations(ctx: LayerCtx, depth: int, C: int, scene_rows: int, free_bytes: int, headroom: float = 0.85) -> bool:
+    """True when the kept activations (plus one layer of backward temporaries, ~ the size of one layer's activations) fit in
+    `headroom` of the free HBM; otherwise the reference's checkpointed schedule is used."""
+    need = activation_bytes(ctx, depth + 1, C, scene_rows)
+    return need <= headroom * free_bytes
+
+
 def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: LayerCtx, draw_scene, d_out: Dict[int, tuple],
-                  world: int = 1, fwd_bwd=None, optimizer_step=None, keep_activations: bool = True) -> torch.Tensor:
+                  world: int = 1, fwd_bwd=None, optimizer_step=None, keep_activations: Optional[bool] = None) -> torch.Tensor:
     """zero_grad + forward + backward + gradient all-reduce + Adam for the block stacks on one scene per rank
     (train_imc.py:361-381 with DDP, :472).  The all-reduce of layer i's bucket (sum; the 1 / world of DDP's mean is
     folded into the Adam kernel) is issued as soon as layer i's backward is enqueued and overlaps the layers below it.
     Returns the gradient w.r.t. X0 (what would flow on into the patch embed).
     keep_activations: True keeps every block's activations from the forward (68 GB at 24 frames — fits a B200, no re-run);
-    False is the reference's torch.utils.checkpoint schedule (block inputs only, each block re-run inside the backward).
+    False is the reference's torch.utils.checkpoint schedule (block inputs only, each block re-run inside the backward);
+    None (default) keeps them when activation_bytes() fits the free HBM of X0's device (choose_keep_activations).
     fwd_bwd(on_layer_done) -> dX0 and optimizer_step(grad_scale) replace the CUDA kernels in the CPU (gloo) tests of this
     schedule; the product path leaves them None."""
     import torch.distributed as dist
@@ -500,6 +518,11 @@ def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: Laye
             works.append(dist.all_reduce(state.grad[i], op=dist.ReduceOp.SUM, async_op=True))
 
     if fwd_bwd is None:
+        if keep_activations is None:
+            free, _ = torch.cuda.mem_get_info(X0.device)
+            free += torch.cuda.memory_reserved(X0.device) - torch.cuda.memory_allocated(X0.device)   # cached blocks are reusable
+            scene_rows = ctx.Na * min(ctx.P, 305) if ctx.Nq > 0 else 0        # upper bound at the reference's fix_rank 300
+            keep_activations = choose_keep_activations(ctx, agg.depth, X0.shape[1], scene_rows, free)
         X = X0 if keep_activations else X0.clone()                 # the checkpointed forward works in place
         ck = stack_forward(agg, X, ctx, draw_scene, keep_activations)
         dX0 = stack_backward(agg, ck, d_out, ctx, state.grads, reduce_layer)

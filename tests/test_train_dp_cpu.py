@@ -121,3 +121,18 @@ def test_train_state_bucket_layout():
     assert torch.allclose(agg.frame_blocks[0].w.detach(), before["frame_blocks.0.w"] + 1.0)
     torch.autograd.graph.increment_version(agg.frame_blocks[0].w)
     assert agg.frame_blocks[0].w._version > v0
+
+
+def test_activation_budget_picks_the_schedule():
+    """train.activation_bytes / choose_keep_activations: 24 frames of 518 px keep ~70 GB of activations (fits a 180 GB B200
+    next to 15 GB of optimizer state), 100 + 200 frames do not and fall back to the reference's checkpointed schedule."""
+    class Ctx:
+        pass
+    c = Ctx()
+    c.Na, c.Nq, c.P = 12, 12, 1374
+    need = train.activation_bytes(c, 24, 1024, scene_rows=12 * 305)
+    assert 60e9 < need < 85e9
+    assert train.choose_keep_activations(c, 24, 1024, 12 * 305, free_bytes=int(160e9))
+    assert not train.choose_keep_activations(c, 24, 1024, 12 * 305, free_bytes=int(70e9))       # e.g. an 80 GB part
+    c.Na, c.Nq = 100, 200
+    assert not train.choose_keep_activations(c, 24, 1024, 100 * 305, free_bytes=int(160e9))

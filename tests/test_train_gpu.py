@@ -331,7 +331,7 @@ class _Stacks(torch.nn.Module):
         self.global_reloc_blocks = torch.nn.ModuleList([_rand_block(seed + 3 * i + 2) for i in range(depth)])
 
 
-@pytest.mark.parametrize("keep_activations", [True, False])
+@pytest.mark.parametrize("keep_activations", [True, False, None])
 def test_training_step_two_layers_matches_fp32_autograd_and_adam(keep_activations):
     """train.training_step over a 2-layer stack (checkpointed forward, backward through both layers with gradients on both
     halves of the layer-0 output and on the final state, flat per-layer buckets, Adam): input gradient and every parameter
