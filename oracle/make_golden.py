@@ -72,8 +72,55 @@ def run_case(name, case):
     print(name, {k: v.shape for k, v in arrays.items() if k != "meta"}, os.path.getsize(path), "bytes")
 
 
+def run_cache_case():
+    """tests/golden/tiny_cache.npz: the reference's CACHED path (aggregator.py:435-578 + attention.py:84-100) on the
+    tiny_conv model built with kv_cache=True: prime with the 2 anchors (SailRecon.tmp_forward, reloc_list = []), then
+    forward_with_cache on the 2 query frames and the camera head.  The reference parks the cache with .cpu() and fetches it
+    with .cuda(); this container has no GPU, so Tensor.cuda is patched to the identity FOR THE CALL (the reference source
+    is untouched and every arithmetic op is the reference's own, on CPU)."""
+    name, case = "tiny_cache", GOLDEN_CASES["tiny_conv"]
+    torch.manual_seed(0)
+    agg = Aggregator(**case["agg"], kv_cache=True).eval()
+    head = CameraHead(**case["head"]).eval()
+    sd = {"agg." + k: v for k, v in agg.state_dict().items()}
+    sd.update({"head." + k: v for k, v in head.state_dict().items()})
+    shapes = {k: list(v.shape) for k, v in sd.items()}
+    params = make_params(shapes, case["seed"])
+    agg.load_state_dict({k[4:]: v for k, v in params.items() if k.startswith("agg.")})
+    head.load_state_dict({k[5:]: v for k, v in params.items() if k.startswith("head.")})
+    S, Na = case["S"], case["Na"]
+    images = make_images(S, case["H"], case["W"], case["seed"] + 100)
+    orig_cuda = torch.Tensor.cuda
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    try:
+        with torch.no_grad():
+            agg.generator.manual_seed(1234)
+            out0, psi, cam = agg(images[:, :Na], list(range(Na)), [], fix_rank=case["fix_rank"])
+            assert len(out0) == 0 and agg.global_reloc_blocks[0].attn.k_cache is not None
+            out, psi = agg.forward_with_cache(images[:, Na:], fix_rank=case["fix_rank"])
+            poses = head(out, cam)
+            single, _ = agg.forward_with_cache(images[:, Na:Na + 1], fix_rank=case["fix_rank"])
+    finally:
+        torch.Tensor.cuda = orig_cuda
+    arrays = {f"out_{k}": v.numpy() for k, v in out.items()}
+    arrays["single_out_-1"] = single[-1].numpy()
+    arrays["cam_token_last_layer"] = cam.numpy()
+    arrays["k_cache_0"] = agg.global_reloc_blocks[0].attn.k_cache.numpy()
+    arrays["v_cache_0"] = agg.global_reloc_blocks[0].attn.v_cache.numpy()
+    for i, pz in enumerate(poses):
+        arrays[f"pose_{i}"] = pz.numpy()
+    arrays["meta"] = np.frombuffer(json.dumps(dict(shapes=shapes, no_reloc_list=list(range(Na)), reloc_list=[],
+                                                    rank=agg.rank, patch_start_idx=psi, num_recon=agg.num_recon)).encode(),
+                                   dtype=np.uint8)
+    path = os.path.join(os.path.dirname(HERE), "tests", "golden", name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(name, {k: v.shape for k, v in arrays.items() if k != "meta"}, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     for n, c in GOLDEN_CASES.items():
         if len(sys.argv) > 1 and n not in sys.argv[1:]:
             continue
         run_case(n, c)
+    if len(sys.argv) == 1 or "tiny_cache" in sys.argv[1:]:
+        run_cache_case()

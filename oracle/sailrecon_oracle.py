@@ -232,7 +232,8 @@ def special_tokens(p: Params, S: int, reloc_list: Sequence[int], pre: str = "") 
 def aggregator_blocks_forward(patch_tokens: Tensor, p: Params, no_reloc_list: Sequence[int], reloc_list: Sequence[int],
                               grid_hw: Tuple[int, int], rank: int, generator: torch.Generator, depth: int = 24,
                               num_heads: int = 16, intermediate_layer_idx=(4, 11, 17, 23), bf16: bool = False,
-                              dense_mask: bool = False, pre: str = "", collect: Optional[dict] = None):
+                              dense_mask: bool = False, pre: str = "", collect: Optional[dict] = None,
+                              scene_cache: Optional[list] = None):
     """Aggregator.forward after the patch embed (models/aggregator.py:276-433), batch 1.
 
     patch_tokens [S, h*w, C].  Returns (output_dict {layer: [1, Nq, P, 2C]}, patch_start_idx, cam_token_last_layer
@@ -240,6 +241,9 @@ def aggregator_blocks_forward(patch_tokens: Tensor, p: Params, no_reloc_list: Se
     [scene ; queries] under the dense boolean mask, aggregator.py:672-741); `dense_mask=False` is the mask-free
     restatement (scene rows are only K/V producers, each query frame attends to [scene ; itself]) that the CUDA path
     implements — tests prove the two equal.
+    `scene_cache`: a list that receives, per layer, the (k, v) [H, Na*P', d] the reloc block's Attention stores on its
+    first call with kv_cache=True (attention.py:94-97; post q/k-norm, post RoPE) — the SailRecon.tmp_forward priming pass
+    (sail_recon.py:176-199, reloc_list = []), whose reloc-block output is zeros + MLP and is discarded.
     """
     S, _, C = patch_tokens.shape
     Na, Nq = len(no_reloc_list), len(reloc_list)
@@ -267,6 +271,10 @@ def aggregator_blocks_forward(patch_tokens: Tensor, p: Params, no_reloc_list: Se
         if collect is not None:
             collect.setdefault("scene_sel", []).append(sel.clone())
         reloc_out = None
+        if scene_cache is not None:
+            sn = layer_norm(scene, p[rpre + "norm1.weight"], p[rpre + "norm1.bias"], 1e-5)
+            _, sk, sv = qkv_heads(sn, p, rpre + "attn.", num_heads, scene_pos, True, True, bf16)
+            scene_cache.append((sk, sv))
         if Nq > 0:
             queries = tokens[rl]                                                                 # [Nq, P, C]
             if dense_mask:
@@ -294,6 +302,55 @@ def aggregator_blocks_forward(patch_tokens: Tensor, p: Params, no_reloc_list: Se
     if Nq > 0:
         out[-1] = out[depth - 1]
     return out, psi, cam_last
+
+
+def cache_mask(num_recon: int, S: int, P: int, P_prime: int) -> Tensor:
+    """models/aggregator.py:496-508: allow block over [anchors ; S query frames] expanded to P tokens per frame, cropped
+    to rows = the S*P query tokens, cols = [num_recon * P' cached scene tokens ; S*P query tokens]."""
+    allow = build_allow_block(num_recon + S, list(range(num_recon)), list(range(num_recon, num_recon + S)))
+    m = allow.repeat_interleave(P, 0).repeat_interleave(P, 1)
+    return m[-S * P:, -(P_prime * num_recon + S * P):]
+
+
+def aggregator_blocks_forward_with_cache(patch_tokens: Tensor, p: Params, scene_cache: Sequence[Tuple[Tensor, Tensor]],
+                                         num_recon: int, grid_hw: Tuple[int, int], rank: int, depth: int = 24,
+                                         num_heads: int = 16, intermediate_layer_idx=(4, 11, 17, 23), bf16: bool = False,
+                                         dense_mask: bool = False, pre: str = ""):
+    """Aggregator.forward_with_cache after the patch embed (models/aggregator.py:469-578), batch 1: every frame is a
+    query carrying the *_reloc special tokens (:483-490); per layer a frame block on each frame, then the reloc block on
+    the S*P query tokens whose Attention prepends the cached scene K/V (attention.py:85-93).  `rank` is NOT clamped here
+    (:471-472): the mask columns assume rank + 5 cached tokens per anchor (:503-505).  `dense_mask=True` evaluates the
+    block exactly like the reference (one sequence under the cropped dense mask); False is the structured restatement
+    (each query frame attends to [cache ; itself]).  Returns (output_dict {layer: [1, S, P, 2C]}, patch_start_idx)."""
+    S, _, C = patch_tokens.shape
+    psi = 5
+    cam = p[pre + "camera_token_reloc"][0, 0]
+    reg = p[pre + "register_token_reloc"][0, 0]
+    special = torch.cat([cam, reg], dim=0)[None].expand(S, -1, -1)
+    tokens = torch.cat([special, patch_tokens], dim=1)                                         # [S, P, C]
+    P = tokens.shape[1]
+    P_prime = rank + psi
+    pos = aggregator_positions(*grid_hw, psi)
+    mask = cache_mask(num_recon, S, P, P_prime) if dense_mask else None
+    out: Dict[int, Tensor] = {}
+    for layer in range(depth):
+        fpre, rpre = (f"{pre}{n}.{layer}." for n in ("frame_blocks", "global_reloc_blocks"))
+        tokens = torch.stack([block_forward(tokens[s], p, fpre, num_heads, pos, None, True, True, bf16) for s in range(S)])
+        frame_out = tokens
+        ck, cv = scene_cache[layer]
+        if dense_mask:
+            assert ck.shape[1] == num_recon * P_prime, "cached scene length must match the mask crop (aggregator.py:503-505)"
+            y = block_forward(tokens.reshape(S * P, C), p, rpre, num_heads, pos.repeat(S, 1), mask, True, True, bf16,
+                              prefix_kv=(ck, cv))
+            tokens = y.reshape(S, P, C)
+        else:
+            tokens = torch.stack([block_forward(tokens[s], p, rpre, num_heads, pos, None, True, True, bf16,
+                                                prefix_kv=(ck, cv)) for s in range(S)])
+        if layer in intermediate_layer_idx:                                                     # :562-571
+            out[layer] = torch.cat([frame_out, tokens], dim=-1)[None]
+    assert depth - 1 in out
+    out[-1] = out[depth - 1]
+    return out, psi
 
 
 _RESNET_MEAN = (0.485, 0.456, 0.406)
@@ -353,6 +410,29 @@ def aggregator_forward(images: Tensor, p: Params, no_reloc_list, reloc_list, fix
         pt = dino_patch_embed(x, p, "patch_embed.", patch_size, num_heads, vit_depth, 4, bf16)
     return aggregator_blocks_forward(pt.float(), p, no_reloc_list, reloc_list, (H // patch_size, W // patch_size), fix_rank,
                                      generator, depth, num_heads, bf16=bf16, dense_mask=dense_mask, **kw)
+
+
+def _embed_images(images: Tensor, p: Params, patch_embed: str, patch_size: int, num_heads: int, vit_depth: int, bf16: bool) -> Tensor:
+    mean = torch.tensor(_RESNET_MEAN).view(1, 3, 1, 1)
+    std = torch.tensor(_RESNET_STD).view(1, 3, 1, 1)
+    x = (images[0] - mean) / std
+    if "conv" in patch_embed:
+        return conv_patch_embed(x, p, "patch_embed.", patch_size, bf16).float()
+    return dino_patch_embed(x, p, "patch_embed.", patch_size, num_heads, vit_depth, 4, bf16).float()
+
+
+def aggregator_forward_with_cache(images: Tensor, p: Params, scene_cache, num_recon: int, fix_rank: int,
+                                  patch_embed: str = "dinov2_vitl14_reg", depth: int = 24, num_heads: int = 16,
+                                  patch_size: int = 14, vit_depth: int = 24, bf16: bool = False, dense_mask: bool = False, **kw):
+    """Aggregator.forward_with_cache (models/aggregator.py:435-578) for images [1, S, 3, H, W] in [0, 1]; `scene_cache`
+    and `num_recon` are what the priming forward left behind (self.num_recon :262, the blocks' k_cache / v_cache)."""
+    B, S, Cin, H, W = images.shape
+    assert B == 1, "Batch size must be 1 for this model"                                       # :453
+    if Cin != 3:
+        raise ValueError(f"Expected 3 input channels, got {Cin}")
+    pt = _embed_images(images, p, patch_embed, patch_size, num_heads, vit_depth, bf16)
+    return aggregator_blocks_forward_with_cache(pt, p, scene_cache, num_recon, (H // patch_size, W // patch_size), fix_rank,
+                                                depth, num_heads, bf16=bf16, dense_mask=dense_mask, **kw)
 
 
 # --------------------------------------------------------------------------------------------------- camera head

@@ -113,14 +113,16 @@ def _cuda_step(q, kv, n_kv, out, carry: Optional[Carry], carry_in: bool, carry_o
 
 def ring_attention(q: torch.Tensor, kv_bufs: Sequence[torch.Tensor], out: torch.Tensor, plan: RingPlan, heads: int,
                    head_dim: int, scale: float, carry: Optional[Carry], group=None,
-                   step_fn: Callable = _cuda_step) -> torch.Tensor:
+                   step_fn: Callable = _cuda_step, wait_events: Optional[list] = None) -> torch.Tensor:
     """softmax(Q_r [K_0 .. K_{R-1}]^T) [V_0 .. V_{R-1}] for this rank's query rows.
 
     q [T_r, C]; kv_bufs = two [max_rows, 2C] buffers, kv_bufs[0][:T_r] holding this rank's own K|V block on entry (both
     are overwritten); out [T_r, C].  Per step: post (isend current block -> next rank, irecv next block <- previous
     rank), launch the attention step on the current block, then make the compute stream wait for the transfer.  The
     transfer is enqueued BEFORE the kernel, so it runs under it; the receive buffer was last read two steps ago.
-    `step_fn` is the attention step (the CUDA kernel; tests inject a reference to exercise the schedule on CPU)."""
+    `step_fn` is the attention step (the CUDA kernel; tests inject a reference to exercise the schedule on CPU).
+    `wait_events`: when a list, a CUDA event pair brackets every wait on the compute stream (recorded after the attention
+    kernel has been enqueued), so the time between them is the EXPOSED part of the exchange (bench.py `nccl_wait_ms`)."""
     R = plan.world
     if R == 1:
         step_fn(q, kv_bufs[0], plan.rows(), out, None, False, False, heads, head_dim, scale)
@@ -137,8 +139,15 @@ def ring_attention(q: torch.Tensor, kv_bufs: Sequence[torch.Tensor], out: torch.
                     dist.P2POp(dist.irecv, nxt[:n_nxt], _global_rank(group, plan.prev_rank), group)]
             reqs = dist.batch_isend_irecv(ops_)
         step_fn(q, cur, n_cur, out, carry, s > 0, s + 1 < R, heads, head_dim, scale)
+        if reqs and wait_events is not None:
+            e0 = torch.cuda.Event(enable_timing=True)
+            e0.record()
         for r in reqs:
             r.wait()
+        if reqs and wait_events is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            wait_events.append((e0, e1))
     return out
 
 
@@ -159,7 +168,7 @@ class RingWorkspace:
 
 
 def ring_global_block(blk, x: torch.Tensor, rows_pos: Optional[RowPositions], plan: RingPlan, ws: RingWorkspace,
-                      group=None, mode: str = "bf16") -> torch.Tensor:
+                      group=None, mode: str = "bf16", wait_events: Optional[list] = None) -> torch.Tensor:
     """One global Block (aggregator.py:743-769 -> block.py:86-112) on this rank's anchor rows x [T_r, C] (fp32, in place),
     attending to the anchor rows of every rank."""
     from . import ops
@@ -174,18 +183,19 @@ def ring_global_block(blk, x: torch.Tensor, rows_pos: Optional[RowPositions], pl
     ops.layernorm(x, w1, b1, eps1, ws.a)
     engine.qkv_rows(attn, ws.a, ws.q, mode, rows_pos, col_offset=0, n_cols=C)              # q columns
     engine.qkv_rows(attn, ws.a, ws.kv[0][:T], mode, rows_pos, col_offset=C, n_cols=2 * C)  # k | v, contiguous for the ring
-    ring_attention(ws.q, ws.kv, ws.a, plan, attn.num_heads, C // attn.num_heads, attn.scale, ws.carry, group)
+    ring_attention(ws.q, ws.kv, ws.a, plan, attn.num_heads, C // attn.num_heads, attn.scale, ws.carry, group,
+                   wait_events=wait_events)
     engine.block_tail(blk, x, ws.a, mode, tag="ring.")
     return x
 
 
 def run_global_stack(blocks, x: torch.Tensor, rows_pos: Optional[RowPositions], plan: RingPlan, group=None,
-                     ws: Optional[RingWorkspace] = None) -> torch.Tensor:
+                     ws: Optional[RingWorkspace] = None, wait_events: Optional[list] = None) -> torch.Tensor:
     """All global blocks over the sharded anchor tokens (the O(L^2) term of the aggregator, BASELINE.json configs[3])."""
     blk0 = blocks[0]
     ws = ws or RingWorkspace(plan, x.shape[1], blk0.attn.num_heads, x.device)
     for blk in blocks:
-        ring_global_block(blk, x, rows_pos, plan, ws, group)
+        ring_global_block(blk, x, rows_pos, plan, ws, group, wait_events=wait_events)
     return x
 
 
@@ -198,33 +208,53 @@ def _frame_tokens(frame: int, P: int, C: int, device) -> torch.Tensor:
     return torch.randn(P, C, generator=g, device=device, dtype=torch.float32)
 
 
-def bench_ring(args, rank: int, world: int, local: int) -> None:
-    """BASELINE.json configs[3]: the 24 global blocks over `--ring-frames` (512) anchor frames of 518x518 (1374 tokens
-    each), frames sharded over the ranks, ring K/V over NVLink.  Strong scaling: total work is fixed as N grows.
-    One step = one pass of the whole sharded stack; value = frames / s."""
+def _ring_problem(n_frames: int, depth: int, rank: int, world: int, dev, frames: Optional[Tuple[int, int]] = None):
+    """Blocks (identical on every rank: torch.manual_seed(0)), this rank's token rows and positions."""
     from .layers.block import Block
     from .layers.rope import PositionGetter, RotaryPositionEmbedding2D
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py --workload ring needs B200s: sailrecon_b200 has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    if world > 1 and not dist.is_initialized():
-        dist.init_process_group("nccl", device_id=dev)
     C, H, P, patch = 1024, 16, 1374, 14
-    n_frames, depth = args.ring_frames, args.ring_depth
     plan = RingPlan.make(n_frames, P, rank, world)
-    torch.manual_seed(0)                                   # identical weights on every rank
+    torch.manual_seed(0)
     rope = RotaryPositionEmbedding2D(frequency=100)
     with torch.device(dev):
         blocks = torch.nn.ModuleList([Block(dim=C, num_heads=H, mlp_ratio=4.0, init_values=0.01, qk_norm=True, rope=rope)
                                       for _ in range(depth)]).eval()
-    f0, fc = plan.frames[rank]
+    f0, fc = frames if frames is not None else plan.frames[rank]
     x0 = torch.cat([_frame_tokens(f, P, C, dev) for f in range(f0, f0 + fc)], dim=0)
     hw = 518 // patch
     grid = PositionGetter()(1, hw, hw, dev)[0] + 1
     frame_pos = torch.cat([torch.zeros(5, 2, dtype=grid.dtype, device=dev), grid], 0).to(torch.int32)
     rows_pos = RowPositions(frame_pos.repeat(fc, 1).contiguous(), hw + 1)
-    ws = RingWorkspace(plan, C, H, dev)
+    return plan, blocks, x0, rows_pos
+
+
+def ring_parity(rank: int, world: int, dev, depth: int = 2) -> Optional[float]:
+    """Parity ACROSS world sizes inside one launch (the 2-process pytest cases are skipped on 1-GPU boxes): 2*world + 1
+    anchor frames (uneven shards) through `depth` global blocks sharded over the ring, against the SAME stack run
+    un-sharded on rank 0's GPU; returns the rel-L2 of rank 0's rows (None on the other ranks)."""
+    n_frames = 2 * world + 1
+    plan, blocks, x0, rows_pos = _ring_problem(n_frames, depth, rank, world, dev)
+    x = x0.clone()
+    with torch.no_grad():
+        run_global_stack(blocks, x, rows_pos, plan, None, RingWorkspace(plan, 1024, 16, dev))
+    torch.cuda.synchronize()
+    if rank != 0:
+        return None
+    plan1, _, x_all, pos_all = _ring_problem(n_frames, depth, 0, 1, dev)
+    with torch.no_grad():
+        run_global_stack(blocks, x_all, pos_all, plan1, None, RingWorkspace(plan1, 1024, 16, dev))
+    ref = x_all[: x.shape[0]].double()
+    return float((x.double() - ref).norm() / ref.norm())
+
+
+def ring_measure(n_frames: int, depth: int, steps: int, warmup: int, rank: int, world: int, dev) -> dict:
+    """The sequence-sharded global stack (BASELINE.json configs[3]) timed on the device: barrier + synchronize on both
+    sides, CUDA events, max over ranks.  Also times the EXPOSED part of the K/V exchange (event pairs around the waits on
+    the compute stream).  Every rank returns the same dict (frame0_out_l2 is broadcast from rank 0)."""
+    from . import ops
+    C, P = 1024, 1374
+    plan, blocks, x0, rows_pos = _ring_problem(n_frames, depth, rank, world, dev)
+    ws = RingWorkspace(plan, C, 16, dev)
     x = torch.empty_like(x0)
 
     def barrier():
@@ -232,59 +262,78 @@ def bench_ring(args, rank: int, world: int, local: int) -> None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step():
+    waits: list = []
+
+    def step(ev=None):
         x.copy_(x0)
         with torch.no_grad():
-            run_global_stack(blocks, x, rows_pos, plan, None, ws)
+            run_global_stack(blocks, x, rows_pos, plan, None, ws, wait_events=ev)
 
-    from . import ops
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
     barrier()
-    import bench as _bench                                   # clock sampler + peaks live in bench.py
-    clocks = _bench.ClockSampler(local)
-    clocks.start()
     n0 = ops.num_kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
-    for _ in range(args.steps):
-        step()
+    for _ in range(steps):
+        step(waits)
     e1.record()
     barrier()
     launches = ops.num_kernel_launches() - n0
-    clk = clocks.stop()
-    ms = e0.elapsed_time(e1) / args.steps
+    ms = e0.elapsed_time(e1) / steps
+    wait_ms = sum(a.elapsed_time(b) for a, b in waits) / steps
     finite = bool(torch.isfinite(x).all())
     probe = float(x[:P].double().norm()) if rank == 0 else 0.0      # frame 0 lives on rank 0 for every world size
     if world > 1:
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t[0])
+        t = torch.tensor([ms, wait_ms, 1.0 if finite else 0.0, probe], device=dev, dtype=torch.float64)
+        mx = t.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        mn = t.clone()
+        dist.all_reduce(mn, op=dist.ReduceOp.MIN)
+        ms, wait_ms, finite, probe = float(mx[0]), float(mx[1]), bool(mn[2] > 0), float(mx[3])
+    L = n_frames * P
+    flops = depth * (4.0 * L * L * C + L * 24.0 * C * C)
+    return {"workload": f"ring: {depth} global blocks over {n_frames} anchor frames x {P} tokens (518 px), frames sharded over "
+                        f"{world} rank(s), K|V blocks passed round the ring by NCCL send/recv under the attention tiles",
+            "n_frames": n_frames, "depth": depth, "steps": steps, "warmup": warmup, "ms_per_step": ms,
+            "frames_per_s": n_frames / (ms * 1e-3), "kv_bytes_per_step": 2 * plan.max_rows * C * 2 * depth * (world - 1),
+            "nccl_wait_ms": wait_ms, "frame0_out_l2": probe, "outputs_finite": finite, "gpu_launches": launches,
+            "algorithmic_tflop_per_step": flops / 1e12, "tflops_per_gpu": flops / (ms * 1e-3) / 1e12 / world,
+            "scaling": "strong"}
+
+
+def bench_ring(args, rank: int, world: int, local: int) -> None:
+    """BASELINE.json configs[3]: the 24 global blocks over `--ring-frames` (512) anchor frames of 518x518 (1374 tokens
+    each), frames sharded over the ranks, ring K/V over NVLink.  Strong scaling: total work is fixed as N grows.
+    One step = one pass of the whole sharded stack; value = frames / s."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --workload ring needs B200s: sailrecon_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+    import bench as _bench                                   # clock sampler + peaks live in bench.py
+    clocks = _bench.ClockSampler(local)
+    clocks.start()
+    rec = ring_measure(args.ring_frames, args.ring_depth, args.steps, args.warmup, rank, world, dev)
+    clk = clocks.stop()
+    par = ring_parity(rank, world, dev) if world > 1 else None
     if rank == 0:
-        L = n_frames * P
-        flops_attn = depth * 4.0 * L * L * C
-        flops_lin = depth * L * 24.0 * C * C
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "MEASURED_PEAKS.json")))
-        except OSError:
-            pass
-        peak_tf = peaks.get("bf16_tflops_sustained", 1400.0)
-        achieved = (flops_attn + flops_lin) / (ms * 1e-3) / 1e12 / world
-        kv_bytes = 2 * plan.max_rows * C * 2
-        line = {"metric": "global-attention stack frames/s at N=%d (518px), sequence-sharded" % n_frames,
-                "value": n_frames / (ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+        peak_tf, peak_src = _bench.load_peak_tf()
+        line = {"metric": "global-attention stack frames/s at N=%d (518px), sequence-sharded" % args.ring_frames,
+                "value": rec["frames_per_s"], "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": rec["ms_per_step"], "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-                "config": {"workload": f"ring: {depth} global blocks over {n_frames} anchor frames x {P} tokens, frames sharded "
-                                       f"over {world} rank(s), ring K/V ({kv_bytes / 1e6:.0f} MB per step per rank) over NCCL send/recv",
+                "config": {"workload": rec["workload"],
                            "l2": "K/V block per head (>= 11 MB) x 16 heads and the fp32 carry exceed L2; no flush needed"},
-                "gpu_launches": launches, "clocks": clk,
-                "roofline": {"bound": "tensor", "kernel": "attn_tc + gemm_tc (whole stack)", "achieved": achieved, "peak": peak_tf,
-                             "unit": "TFLOP/s", "frac": achieved / peak_tf, "traffic": None,
-                             "peak_source": "measured (MEASURED_PEAKS.json bf16_tflops_sustained)" if peaks else "fallback"},
-                "algorithmic_tflop_per_step": (flops_attn + flops_lin) / 1e12, "frame0_out_l2": probe, "outputs_finite": finite}
+                "gpu_launches": rec["gpu_launches"], "clocks": clk,
+                "roofline": {"bound": "tensor", "kernel": "attn_tc + gemm_tc (whole stack)", "achieved": rec["tflops_per_gpu"],
+                             "peak": peak_tf, "unit": "TFLOP/s", "frac": rec["tflops_per_gpu"] / peak_tf, "traffic": None,
+                             "peak_source": peak_src},
+                "sharded": rec, "ring_parity_rel_l2": par,
+                "algorithmic_tflop_per_step": rec["algorithmic_tflop_per_step"], "frame0_out_l2": rec["frame0_out_l2"],
+                "outputs_finite": rec["outputs_finite"]}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -242,3 +242,39 @@ def test_imc_style_scene_more_queries_than_anchors():
         assert len(poses) == 4 and tuple(poses[-1].shape) == (1, Nq, 9)
         for a, b in zip(poses, ref_poses):
             assert rel_l2(a.cpu(), b) < 1e-2
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+def test_forward_with_cache_matches_reference_golden(bf16):
+    """A13 against a REFERENCE-derived expectation that travels: tests/golden/tiny_cache.npz is the unmodified reference's
+    kv-cache path (priming forward + forward_with_cache + camera head, oracle/make_golden.py run_cache_case)."""
+    from test_oracle_golden import load_golden_cache
+    from sailrecon_b200.heads import CameraHead
+    from sailrecon_b200.models import Aggregator
+    arrays, meta, params = load_golden_cache()
+    case = GOLDEN_CASES["tiny_conv"]
+    Na = case["Na"]
+    agg = Aggregator(**case["agg"], kv_cache=True).eval()
+    head = CameraHead(**case["head"]).eval()
+    agg.load_state_dict({k[4:]: v for k, v in params.items() if k.startswith("agg.")})
+    head.load_state_dict({k[5:]: v for k, v in params.items() if k.startswith("head.")})
+    agg, head = agg.to(DEV), head.to(DEV)
+    images = make_images(case["S"], case["H"], case["W"], case["seed"] + 100).to(DEV)
+    tol = 2e-2 if bf16 else 1e-4
+    agg.generator.manual_seed(1234)
+    with torch.no_grad():
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=bf16):
+            out0, psi, cam = agg(images[:, :Na], list(range(Na)), [], fix_rank=case["fix_rank"])
+            out, psi2 = agg.forward_with_cache(images[:, Na:], fix_rank=case["fix_rank"])
+            single, _ = agg.forward_with_cache(images[:, Na:Na + 1], fix_rank=case["fix_rank"])
+        poses = head(out, cam)
+    assert len(out0) == 0 and psi == psi2 == 5 and agg.num_recon == meta["num_recon"] and agg.rank == meta["rank"]
+    assert rel_l2(cam.cpu(), arrays["cam_token_last_layer"]) < tol
+    C = agg.camera_token.shape[-1]
+    k0 = agg.global_reloc_blocks[0].attn.k_cache.float().view(-1, 2, 64).transpose(0, 1).cpu()
+    assert rel_l2(k0, arrays["k_cache_0"][0]) < (1e-2 if bf16 else 1e-5)
+    for k, v in out.items():
+        assert rel_l2(v.cpu(), arrays[f"out_{k}"]) < tol, k
+    assert rel_l2(single[-1].cpu(), arrays["single_out_-1"]) < tol
+    for i, pz in enumerate(poses):
+        assert (pz.cpu() - arrays[f"pose_{i}"]).abs().max() < (5e-2 if bf16 else 1e-2)

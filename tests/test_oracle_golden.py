@@ -97,3 +97,63 @@ def test_oracle_layers_match_live_reference():
     got = O.block_forward(x[0], p, "", 2, pos[0], None, True, True, False)
     assert rel_l2(got, ref[0]) < 1e-6
     assert torch.allclose(O.rope_2d(x.view(12, 2, 64).transpose(0, 1), pos[0]), refq[0], atol=1e-6)
+
+
+def _cache_oracle(dense_mask, bf16=False):
+    """Priming forward (kv_cache=True, reloc_list = []) + forward_with_cache, oracle restatement."""
+    arrays, meta, params = load_golden_cache()
+    case = GOLDEN_CASES["tiny_conv"]
+    Na = case["Na"]
+    images = make_images(case["S"], case["H"], case["W"], case["seed"] + 100)
+    agg_p = {k[4:]: v for k, v in params.items() if k.startswith("agg.")}
+    head_p = {k[5:]: v for k, v in params.items() if k.startswith("head.")}
+    a = case["agg"]
+    cache = []
+    out0, _, cam = O.aggregator_forward(images[:, :Na], agg_p, list(range(Na)), [], case["fix_rank"],
+                                        torch.Generator().manual_seed(1234), patch_embed="conv", depth=a["depth"],
+                                        num_heads=a["num_heads"], intermediate_layer_idx=(0, 1), bf16=bf16, scene_cache=cache)
+    assert len(out0) == 0 and len(cache) == a["depth"]
+    kw = dict(patch_embed="conv", depth=a["depth"], num_heads=a["num_heads"], intermediate_layer_idx=(0, 1), bf16=bf16,
+              dense_mask=dense_mask)
+    out, psi = O.aggregator_forward_with_cache(images[:, Na:], agg_p, cache, Na, case["fix_rank"], **kw)
+    single, _ = O.aggregator_forward_with_cache(images[:, Na:Na + 1], agg_p, cache, Na, case["fix_rank"], **kw)
+    h = case["head"]
+    poses = O.camera_head_forward(out[-1][:, :, 0], cam, head_p, 4, h["num_heads"], h["trunk_depth"])
+    return arrays, out, single, cam, cache, poses
+
+
+def load_golden_cache():
+    import json
+    import numpy as np
+    from golden_common import make_params
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tiny_cache.npz"))
+    meta = json.loads(bytes(z["meta"]).decode())
+    arrays = {k: torch.from_numpy(z[k]) for k in z.files if k != "meta"}
+    return arrays, meta, make_params(meta["shapes"], GOLDEN_CASES["tiny_conv"]["seed"])
+
+
+@pytest.mark.parametrize("dense_mask", [True, False])
+def test_oracle_cached_path_matches_reference_golden(dense_mask):
+    """aggregator.py:435-578 + attention.py:84-100 restated (oracle.aggregator_forward_with_cache, scene_cache hook) against
+    tests/golden/tiny_cache.npz, which oracle/make_golden.py produced by running the UNMODIFIED reference's kv-cache path
+    (priming forward, forward_with_cache on 2 frames and on 1 frame, camera head)."""
+    arrays, out, single, cam, cache, poses = _cache_oracle(dense_mask)
+    assert rel_l2(cache[0][0], arrays["k_cache_0"][0]) < TOL and rel_l2(cache[0][1], arrays["v_cache_0"][0]) < TOL
+    assert rel_l2(cam, arrays["cam_token_last_layer"]) < TOL
+    for k, v in out.items():
+        assert rel_l2(v, arrays[f"out_{k}"]) < TOL, k
+    assert rel_l2(single[-1], arrays["single_out_-1"]) < TOL
+    for i, pz in enumerate(poses):
+        assert rel_l2(pz, arrays[f"pose_{i}"]) < 1e-4, i
+
+
+def test_cache_mask_structure():
+    """aggregator.py:496-508 crop == [every cached scene token | block diagonal over the query frames]."""
+    Na, S, P, Pp = 3, 2, 7, 4
+    m = O.cache_mask(Na, S, P, Pp)
+    assert m.shape == (S * P, Na * Pp + S * P)
+    exp = torch.zeros_like(m)
+    exp[:, : Na * Pp] = True
+    for i in range(S):
+        exp[i * P:(i + 1) * P, Na * Pp + i * P: Na * Pp + (i + 1) * P] = True
+    assert torch.equal(m, exp)
