@@ -220,7 +220,7 @@ def parity_and_library_baseline(agg, head, images, Na: int, Nq: int, steps: int 
     dev = images.device
     torch.manual_seed(0)
     with torch.device(dev):
-        r_agg, r_head = Aggregator().eval(), CameraHead(dim_in=2 * C).eval()
+        r_agg, r_head = Aggregator().eval().to(dev), CameraHead(dim_in=2 * C).eval().to(dev)
     r_agg.load_state_dict(agg.state_dict())
     r_head.load_state_dict(head.state_dict())
     nrl, rl = list(range(Na)), list(range(Na, Na + Nq))

@@ -116,11 +116,14 @@ typedef struct sr_attn {
    * (lse_pad >= q_len, a multiple of 64; the caller pre-fills the buffer with +inf so padding rows stay +inf).
    * NULL = inference.  Consumed by sr_attn_bwd_bf16.  bf16 tensor-core path only.                           */
   float* lse; int64_t lse_pad;
+  /* kernel variant of the tcgen05 path: 0 = chosen per launch by wave quantisation (default), 3 / 4 = force the
+   * three- / four-query-tile kernel.  Every variant computes the same function; ignored by the fp32 path.    */
+  int32_t variant;
 } sr_attn_t;
 
-/* Profiling aid: with SR_ATTN_TRACE set in the environment, CTA (0,0,0) of sr_attn_fwd_bf16 records clock64() at its
- * pipeline hand-offs for the first 64 K/V tiles; this copies the [3 roles][64 tiles][8 events] table to HOST memory
- * (synchronises the device). */
+/* Profiling aid, -DSR_DEBUG builds of the library only (the shipped build never reads the environment and returns an
+ * error here): with SR_ATTN_TRACE set, CTA (0,0,0) of sr_attn_fwd_bf16 records clock64() at its pipeline hand-offs for
+ * the first 64 K/V tiles; this copies the [3 roles][64 tiles][8 events] table to HOST memory (synchronises the device). */
 int sr_debug_trace_read(long long* host_dst, int64_t count);
 
 int sr_attn_fwd_bf16(const sr_attn_t* p, void* stream);  /* tcgen05 flash attention, head_dim 64           */
@@ -236,6 +239,23 @@ int sr_patchify(const float* images, void* out, int out_bf16, int64_t ldo, int64
 /* ---- camera head pose accumulation (camera_head.py:172-184, head_act.py:12-37) -----------------------------
  * pred = first ? delta : pred + delta; activated = [pred[:, :7], relu(pred[:, 7:9])]; all fp32 [rows, 9].     */
 int sr_pose_update(float* pred, const float* delta, float* activated, int64_t rows, int32_t first, void* stream);
+
+/* ---- camera geometry after the head ------------------------------------------------------
+ * pose_encoding_to_extri_intri (utils/pose_enc.py:68-135, "absT_quaR_FoV") with quat_to_mat (utils/rotation.py:14-44,
+ * scalar-last quaternion) fused: pose fp32 [n, 9] = (T[3], quat xyzw[4], fov_h, fov_w) -> extrinsics fp32 [n, 3, 4] =
+ * [R | T] and, when intrinsics != NULL, intrinsics fp32 [n, 3, 3] with fy = (H/2) / tan(fov_h/2), fx = (W/2) / tan(fov_w/2),
+ * principal point (W/2, H/2).  Called at sail_recon.py:122-124, :235-237.                                      */
+int sr_pose_to_extri_intri(const float* pose, float* extrinsics, float* intrinsics, int64_t n, int32_t image_h,
+                           int32_t image_w, void* stream);
+/* unproject_depth_map_to_point_map (utils/geometry.py:19-128; numpy on the host in the reference, sail_recon.py:139-141):
+ * depth fp32 [S, H, W], extrinsics [S, 3, 4] (camera from world), intrinsics [S, 3, 3] (zero skew) -> world points
+ * fp32 [S, H, W, 3] = R^T ((u - cu) d / fu, (v - cv) d / fv, d) - R^T t.  Everything stays in HBM.              */
+int sr_unproject_depth(const float* depth, const float* extrinsics, const float* intrinsics, float* points, int64_t S,
+                       int64_t H, int64_t W, void* stream);
+/* modulate (heads/camera_head.py:189-194): out = x * (1 + scale) + shift, fp32 [rows, C] with row strides (shift / scale
+ * are usually column blocks of the [rows, 3C] modulation tensor).                                              */
+int sr_modulate_f32(const float* x, int64_t ldx, const float* shift, int64_t lds, const float* scale, int64_t ldc,
+                    float* out, int64_t ldo, int64_t rows, int64_t C, void* stream);
 
 #ifdef __cplusplus
 }

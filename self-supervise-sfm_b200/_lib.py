@@ -42,6 +42,7 @@ class SrAttn(C.Structure):
         ("scale", _f32),
         ("carry_m", _vp), ("carry_l", _vp), ("carry_acc", _vp), ("carry_in", _i32), ("carry_out", _i32),
         ("lse", _vp), ("lse_pad", _i64),
+        ("variant", _i32),
     ]
 
 
@@ -98,6 +99,9 @@ SIGNATURES = {
     "sr_rope2d_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i32, _i64, _i64, _i64, _i64, _vp]),
     "sr_patchify": (C.c_int, [_vp, _vp, C.c_int, _i64, _i64, _i64, _i64, _i32, C.POINTER(_f32), C.POINTER(_f32), _vp]),
     "sr_pose_update": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
+    "sr_pose_to_extri_intri": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
+    "sr_unproject_depth": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp]),
+    "sr_modulate_f32": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _vp]),
 }
 
 _lib = None
@@ -115,12 +119,15 @@ def load():
     path = lib_path()
     if path == _build.LIB_PATH and not _build.is_current():
         try:
-            _build.build_library()
-        except Exception as e:  # no nvcc on this machine
+            _build.build_library()                 # compile / link errors propagate: never run stale kernels silently
+        except _build.NvccNotFound as e:           # no compiler here: a prebuilt library may be used, loudly
             if not os.path.exists(path):
                 raise RuntimeError(
                     f"libsailrecon_b200.so is not built and could not be built ({e}); "
                     "sailrecon_b200 has no CPU or PyTorch fallback") from e
+            import warnings
+            warnings.warn(f"sailrecon_b200: {path} does not match the digest of csrc/ + the header and nvcc is not available "
+                          "to rebuild it; loading the STALE library", RuntimeWarning)
     if not os.path.exists(path):
         raise RuntimeError(f"{path} not found; sailrecon_b200 has no CPU or PyTorch fallback")
     lib = C.CDLL(path)

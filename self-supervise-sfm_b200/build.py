@@ -30,7 +30,7 @@ SOURCES = [
     "gemm_tc.cu",
     "attn_tc.cu",
     "attn_tc4.cu",
-    "attn_tc3.cu", "attn_bwd.cu", "train_rows.cu",
+    "attn_tc3.cu", "attn_bwd.cu", "train_rows.cu", "pose.cu",
 ]
 
 NVCC_FLAGS = [
@@ -43,11 +43,15 @@ NVCC_FLAGS = [
 ]
 
 
+class NvccNotFound(RuntimeError):
+    """No compiler on this machine (a GPU box running a prebuilt snapshot): the only build failure that may be tolerated."""
+
+
 def _nvcc() -> str:
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and os.path.exists(cand):
             return cand
-    raise RuntimeError("nvcc not found: libsailrecon_b200.so cannot be built (there is no CPU fallback)")
+    raise NvccNotFound("nvcc not found: libsailrecon_b200.so cannot be built (there is no CPU fallback)")
 
 
 def _digest() -> str:

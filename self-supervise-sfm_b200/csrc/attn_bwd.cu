@@ -250,13 +250,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
       mbar_wait(&s_full, t & 1);
       tc_fence_after();
       uint32_t pkp[16], pkd[16];
-      if (p.dbg != 0) {
+      if (kDebugBuild && p.dbg != 0) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) pkp[i] = pkd[i] = 0u;
       }
 #pragma unroll
       for (int c = 0; c < 2; ++c) {                         // two chunks of 16 score columns
-        if (p.dbg & 2) {
+        if (kDebugBuild && (p.dbg & 2)) {
           if (kMode == 0 && c == 1 && elect_one()) mbar_arrive(&sdp_free);
           continue;
         }
@@ -268,7 +268,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
           tc_fence_before();
           if (elect_one()) mbar_arrive(&sdp_free);
         }
-        if (p.dbg & 1) { pkp[c] ^= sv[0] ^ dv[15]; continue; }
+        if (kDebugBuild && (p.dbg & 1)) { pkp[c] ^= sv[0] ^ dv[15]; continue; }
 #pragma unroll
         for (int i = 0; i < 16; i += 4) {
           const int col = hlf * 32 + c * 16 + i;            // column inside the 64-wide tile
@@ -475,7 +475,7 @@ extern "C" int sr_attn_bwd_bf16(const sr_attn_bwd_t* a, void* stream) {
   p.scale = a->scale;
   p.scale_log2 = a->scale * 1.4426950408889634f;
   {
-    static const int dbg = [] { const char* e = getenv("SR_ATTN_BWD_DBG"); return e ? atoi(e) : 0; }();
+    static const int dbg = [] { const char* e = dbg_env("SR_ATTN_BWD_DBG"); return e ? atoi(e) : 0; }();
     p.dbg = dbg;
   }
 

@@ -63,6 +63,7 @@ struct AttnParams {
   int lag_ns;                    // start-up lag of the second softmax warpgroup (de-phases the two MUFU streams)
 };
 
+#ifdef SR_DEBUG   // the original two-tile kernel: kept for A/B timing experiments, not part of the shipped library
 // Profiling aid: SR_ATTN_TRACE=1 makes CTA (0,0,0) record clock64() at the pipeline hand-offs of its first 64 K/V tiles
 // (read back with sr_debug_trace_read, printed by scripts/attn_trace.py).  Layout: g_attn_trace[role][tile][event],
 // role 0 = softmax warp 4, 1 = MMA issuer of query tile 0, 2 = TMA producer.
@@ -440,18 +441,24 @@ static int launch_attn(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const 
   return SR_OK;
 }
 
+#endif  // SR_DEBUG
+
 }  // namespace sr
 
 extern "C" int sr_debug_trace_read(long long* host_dst, int64_t count) {
   using namespace sr;
   SR_REQUIRE(host_dst && count > 0 && count <= 3 * 64 * 8, "sr_debug_trace_read: count out of range");
+#ifdef SR_DEBUG
   {
     int variant = kAtKernelDefault;
-    if (const char* env = getenv("SR_ATTN_KERNEL")) variant = atoi(env);
+    if (const char* env = dbg_env("SR_ATTN_KERNEL")) variant = atoi(env);
     if (variant == 4) return attn_tc4_trace_read(host_dst, count);
   }
   SR_CHECK_CUDA(cudaMemcpyFromSymbol(host_dst, g_attn_trace, static_cast<size_t>(count) * sizeof(long long)));
   return SR_OK;
+#else
+  return fail(SR_ERR_SHAPE, "sr_debug_trace_read: the pipeline trace exists only in -DSR_DEBUG builds of the library");
+#endif
 }
 
 extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
@@ -491,7 +498,9 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
     // better onto the SMs (16-anchor global: 688 CTAs of four tiles = 5 waves against 928 of three = 7 x 0.75;
     // 16-frame reloc: 768 = 6 waves against 1024 = 7 x 0.75).  SR_ATTN_KERNEL = 2 / 3 / 4 forces a variant.
     int variant = kAtKernelDefault;
-    if (const char* env = getenv("SR_ATTN_KERNEL")) {
+    if (a->variant != 0) {
+      variant = a->variant;                 // explicit per-call choice (tests exercise every variant on every case)
+    } else if (const char* env = dbg_env("SR_ATTN_KERNEL")) {
       variant = atoi(env);
     } else {
       static int num_sms = 0;
@@ -507,14 +516,18 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
     }
     // polynomial exp2 on the FMA pipe for 2 of every 8 pairs: measured best (0: 851, 1: 905, 2: 921, 3: 892, 4: 843 TF/s)
     int poly = 2;
-    if (const char* env = getenv("SR_ATTN_POLY")) poly = atoi(env);
+    if (const char* env = dbg_env("SR_ATTN_POLY")) poly = atoi(env);
     if (a->lse != nullptr) {
       SR_REQUIRE(a->lse_pad >= a->q_len && a->lse_pad % 64 == 0, "sr_attn_fwd_bf16: lse_pad must be a multiple of 64 >= q_len");
       SR_REQUIRE(variant == 3 || variant == 4, "sr_attn_fwd_bf16: the two-tile kernel (SR_ATTN_KERNEL=2) does not write lse");
     }
     if (variant == 4) return attn_tc4_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
     if (variant == 3) return attn_tc3_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
+#ifndef SR_DEBUG
+    return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16: kernel variant must be 0 (auto), 3 or 4 (got %d)", variant);
+#endif
   }
+#ifdef SR_DEBUG
   const uint64_t qbs = a->batch > 1 ? a->q_batch_stride : a->q_len;
   const uint64_t kbs = a->batch > 1 ? a->kv_batch_stride : a->kv_len;
   CUtensorMap tq, tk, tv, tpk, tpv;
@@ -560,15 +573,15 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
   p.scale_log2 = a->scale * 1.4426950408889634f;
   p.lag_ns = 0;
   p.dbg = 0;
-  if (const char* env = getenv("SR_ATTN_DBG")) p.dbg = atoi(env);
-  p.trace = getenv("SR_ATTN_TRACE") != nullptr;
-  if (const char* env = getenv("SR_ATTN_LAG_NS")) p.lag_ns = atoi(env);
+  if (const char* env = dbg_env("SR_ATTN_DBG")) p.dbg = atoi(env);
+  p.trace = dbg_env("SR_ATTN_TRACE") != nullptr;
+  if (const char* env = dbg_env("SR_ATTN_LAG_NS")) p.lag_ns = atoi(env);
 
   dim3 grid(static_cast<unsigned>((a->q_len + 128 * kAtNQ - 1) / (128 * kAtNQ)), static_cast<unsigned>(a->num_heads),
             static_cast<unsigned>(a->batch));
   // tuning knob (profiling only): SR_ATTN_POLY = 0 / 2 / 3 / 4 polynomial-exp2 pairs out of 8; default kAtPolyDefault
   int poly = kAtPolyDefault;
-  if (const char* env = getenv("SR_ATTN_POLY")) poly = atoi(env);
+  if (const char* env = dbg_env("SR_ATTN_POLY")) poly = atoi(env);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   switch (poly) {
     case 0: return launch_attn<0>(grid, st, tq, tk, tv, tpk, tpv, p);
@@ -578,4 +591,5 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
     case 8: return launch_attn<8>(grid, st, tq, tk, tv, tpk, tpv, p);
   }
   return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16: SR_ATTN_POLY must be 0, 2, 3 or 4 (got %d)", poly);
+#endif  // SR_DEBUG
 }

@@ -81,7 +81,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   const int q0 = blockIdx.x * (128 * k4NQ);                          // first query row (within the segment) of this CTA
   const int nq_valid = min(k4NQ, (p.q_len - q0 + 127) / 128);        // query tiles that hold at least one row
   const int n_tiles = p.n_prefix_tiles + p.n_own_tiles;
-  const bool trace_on = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0;
+  const bool trace_on = kDebugBuild && p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
@@ -439,7 +439,7 @@ int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
   p.n_own_tiles = (p.kv_len + 63) / 64;
   p.total_q_rows = a->batch > 1 ? static_cast<int64_t>(a->batch - 1) * a->q_batch_stride + a->q_len : a->q_len;
   p.scale_log2 = a->scale * 1.4426950408889634f;
-  p.trace = getenv("SR_ATTN_TRACE") != nullptr;
+  p.trace = dbg_env("SR_ATTN_TRACE") != nullptr;
   p.lse = a->lse;
   p.lse_pad = static_cast<int>(a->lse_pad);
   dim3 grid(static_cast<unsigned>((a->q_len + 128 * k4NQ - 1) / (128 * k4NQ)), static_cast<unsigned>(a->num_heads),

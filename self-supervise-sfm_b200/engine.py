@@ -48,20 +48,36 @@ def require_cuda_f32(x: torch.Tensor, name: str) -> None:
         raise TypeError(f"sailrecon_b200: {name} must be float32 (the residual stream is fp32 as in the reference), got {x.dtype}")
 
 
+def forbid_autograd(mod: nn.Module, what: str) -> None:
+    """The inference forwards read every parameter detached and return tensors without grad_fn.  In train() mode with
+    grad enabled that would silently freeze the module under an unmodified training loop (train_imc.py:364-381: only the
+    reference's DPT heads would receive gradients), so it is an error instead.  Training goes through
+    sailrecon_b200.train (training_step / AggregatorFunction)."""
+    if mod.training and torch.is_grad_enabled() and any(p.requires_grad for p in mod.parameters()):
+        raise RuntimeError(f"sailrecon_b200: {what} is the inference path (parameters are read detached, outputs carry no "
+                           "grad_fn); it was called in train() mode with autograd enabled.  Use model.eval() / torch.no_grad() "
+                           "for inference, or sailrecon_b200.train.training_step for the differentiated block stacks.")
+
+
 # ------------------------------------------------------------------------------------------------ workspace
 class Workspace:
-    """Named scratch buffers that grow monotonically (per device).  All launches of one forward are ordered on one
-    stream, so a buffer can be reused as soon as the kernel that read it has been enqueued."""
+    """Named scratch buffers that grow monotonically, one set per (device, CUDA stream): all launches enqueued on one
+    stream are ordered, so a buffer can be reused as soon as the kernel that read it has been enqueued — and two forwards
+    running on two streams (or two models driven from two threads, each on its own stream) never share scratch
+    (SURVEY.md §8b "re-entrant per stream").  Two models interleaved on the SAME stream share buffers safely for the
+    same reason: their launches are serialised by the stream."""
 
     def __init__(self):
-        self._buf: Dict[Tuple[str, torch.device], torch.Tensor] = {}
+        self._buf: Dict[Tuple[str, torch.device, int], torch.Tensor] = {}
 
     def get(self, name: str, shape: Sequence[int], dtype: torch.dtype, device) -> torch.Tensor:
         n = 1
         for s in shape:
             n *= int(s)
         nbytes = max(n * torch.empty((), dtype=dtype).element_size(), 16)
-        key = (name, torch.device(device))
+        dev = torch.device(device)
+        stream = torch.cuda.current_stream(dev).cuda_stream if dev.type == "cuda" else 0
+        key = (name, dev, stream)
         buf = self._buf.get(key)
         if buf is None or buf.numel() < nbytes:
             buf = torch.empty(nbytes, dtype=torch.uint8, device=device)

@@ -44,23 +44,29 @@ class CameraHead(nn.Module):
         self.pose_branch = Mlp(in_features=dim_in, hidden_features=dim_in // 2, out_features=self.target_dim, drop=0)
 
     def forward(self, aggregated_tokens_list, cam_token_last_layer: torch.Tensor, num_iterations: int = 4) -> list:
+        engine.forbid_autograd(self, "CameraHead.forward")
         tokens = aggregated_tokens_list[-1]                                                # camera_head.py:103-109
         pose_q = tokens[:, :, 0]
         if pose_q.shape[0] != 1:
             raise NotImplementedError("sailrecon_b200: batch size 1")
         engine.require_cuda_f32(pose_q, "aggregated tokens")
         engine.require_cuda_f32(cam_token_last_layer, "cam_token_last_layer")
-        Na, Nq = cam_token_last_layer.shape[1], pose_q.shape[1]
+        Na = cam_token_last_layer.shape[1]
         x_in = torch.cat([cam_token_last_layer[0], pose_q[0]], dim=0).contiguous()          # [T, C]
-        T, C = x_in.shape
-        dev = x_in.device
-        mode = "f32"
         w, b, eps = engine.ln_params(self.token_norm)
         x = torch.empty_like(x_in)
         ops.layernorm(x_in, w, b, eps, x)                                                  # :110
         # ~build_lr_mask (:112-116, :197-228) as structure: anchors | each query behind the anchors
-        calls = engine.MaskStructure(Na, 1, Nq).calls()
-        f32 = dict(dtype=torch.float32, device=dev)
+        calls = engine.MaskStructure(Na, 1, pose_q.shape[1]).calls()
+        return [p[None, Na:] for p in self._trunk_rows(x, calls, num_iterations)]          # query rows only, :118-121
+
+    def _trunk_rows(self, x: torch.Tensor, calls, num_iterations: int) -> list:
+        """trunk_fn (camera_head.py:123-186) on the normalised camera-token rows x [T, C] (fp32, autocast off): per
+        refinement iteration embed_pose + SiLU (one GEMM epilogue), the modulation GEMM, one fused adaLN-modulate-gate-
+        residual kernel, the trunk blocks, trunk_norm, pose_branch and one accumulate + activate kernel.  -> [T, 9] each."""
+        T, C = x.shape
+        mode = "f32"
+        f32 = dict(dtype=torch.float32, device=x.device)
         emb = torch.empty(T, C, **f32)
         mod = torch.empty(T, 3 * C, **f32)
         y = torch.empty(T, C, **f32)
@@ -83,15 +89,27 @@ class CameraHead(nn.Module):
             engine.linear_rows(self.pose_branch.fc2, hid, delta, mode, SR_EPI_BIAS)
             act = torch.empty(T, self.target_dim, **f32)
             ops.pose_update(pred, delta, act, it == 0)                                     # :172-184
-            out.append(act[None, Na:])                                                     # query rows only, :118-121
+            out.append(act)
         return out
 
     def trunk_fn(self, pose_tokens: torch.Tensor, attention_mask: torch.Tensor, num_iterations: int) -> list:
-        raise NotImplementedError("sailrecon_b200: call CameraHead.forward (trunk_fn is internal to the reference)")
+        """camera_head.py:123-186: pose_tokens [1, S, C] already token_norm'ed; attention_mask as build_lr_mask returns it
+        (True = masked; the blocks receive ~mask).  Returns `num_iterations` activated encodings [1, S, 9] (all rows)."""
+        engine.forbid_autograd(self, "CameraHead.trunk_fn")
+        if pose_tokens.dim() != 3 or pose_tokens.shape[0] != 1:
+            raise NotImplementedError("sailrecon_b200: batch size 1")
+        engine.require_cuda_f32(pose_tokens, "pose_tokens")
+        S = pose_tokens.shape[1]
+        calls = engine.full_segments(1, S) if attention_mask is None else engine.structure_from_mask(~attention_mask, S).calls()
+        return [p[None] for p in self._trunk_rows(pose_tokens[0].contiguous(), calls, num_iterations)]
 
 
 def modulate(x: torch.Tensor, shift: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
-    raise NotImplementedError("sailrecon_b200: modulate is fused into sr_adaln_modulate_f32 (CameraHead.forward)")
+    """camera_head.py:189-194: x * (1 + scale) + shift (stand-alone form; inside CameraHead.forward it is fused with the
+    LayerNorm, the gate and the residual in sr_adaln_modulate_f32)."""
+    if not x.is_cuda:
+        raise RuntimeError("sailrecon_b200: modulate runs on a CUDA device only (no CPU fallback)")
+    return ops.modulate(x.float(), shift.float(), scale.float())
 
 
 def build_lr_mask(S: int, no_reloc_list, device="cpu"):

@@ -65,6 +65,11 @@ class Attention(nn.Module):
             return engine.full_segments(Bx, N)
         if isinstance(attn_mask, engine.MaskStructure):
             st = attn_mask
+            if cache_len:                            # the structure describes the NEW tokens; all of them see the cache
+                if st.prefix_len:
+                    raise NotImplementedError("sailrecon_b200: a MaskStructure with its own prefix cannot be combined with a kv cache")
+                return [engine.AttnCall(0, st.num_segs, st.seg_len, st.seg_len,
+                                        engine.Prefix(self.k_cache, self.v_cache, 0, cache_len))]
         else:
             if Bx != 1:
                 raise NotImplementedError("sailrecon_b200: masks are supported for batch 1 (as the reference uses them)")
@@ -76,6 +81,8 @@ class Attention(nn.Module):
                 if m.shape[-1] != cache_len + N or not bool(m[:, :cache_len].all()):
                     raise NotImplementedError("sailrecon_b200: unsupported mask for cached attention")
                 sub = engine.structure_from_mask(m[:, cache_len:], N)
+                if sub.prefix_len == N and sub.num_segs == 0:
+                    sub = engine.MaskStructure(0, N, 1)          # one new sequence (S = 1): the all-True sub-mask is ONE segment
                 if sub.prefix_len:
                     raise NotImplementedError("sailrecon_b200: unsupported mask for cached attention")
                 st = engine.MaskStructure(0, sub.seg_len, sub.num_segs)
@@ -88,6 +95,7 @@ class Attention(nn.Module):
     def forward(self, x: Tensor, pos=None, attn_mask=None) -> Tensor:
         """x [Bx, N, C] (already normalised by the caller, block.py:87) -> proj(attention(x)) [Bx, N, C].
         Under autocast(bf16) the result is bf16, as the reference's proj Linear returns it."""
+        engine.forbid_autograd(self, "Attention.forward")
         mode = engine.compute_mode()
         if not x.is_cuda:
             raise RuntimeError("sailrecon_b200: Attention runs on a CUDA device only (no CPU fallback)")

@@ -40,6 +40,7 @@ class Block(nn.Module):
 
     def forward(self, x: Tensor, pos=None, attn_mask=None) -> Tensor:
         """x [Bx, N, C] fp32 -> fp32 [Bx, N, C] (a fresh tensor, like the reference)."""
+        engine.forbid_autograd(self, "Block.forward")
         engine.require_cuda_f32(x, "x")
         mode = engine.compute_mode()
         Bx, N, C = x.shape

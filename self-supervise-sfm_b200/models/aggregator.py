@@ -159,6 +159,7 @@ class Aggregator(nn.Module):
     # ---------------------------------------------------------------------------------------------- forward
     def forward(self, images: torch.Tensor, no_reloc_list: list, reloc_list: list,
                 fix_rank: Union[int, None] = None) -> Tuple[dict, int, torch.Tensor]:
+        engine.forbid_autograd(self, "Aggregator.forward")
         B, S, C_in, H, W = images.shape
         Na, Nq = len(no_reloc_list), len(reloc_list)
         self.num_recon = Na
@@ -247,6 +248,7 @@ class Aggregator(nn.Module):
     def forward_with_cache(self, images: torch.Tensor, cameras: torch.Tensor = None, camera_dropout: float = False,
                            fix_rank: Union[int, None] = None) -> Tuple[dict, int]:
         """aggregator.py:435-578: every frame is a query localised against the cached scene K/V (HBM resident)."""
+        engine.forbid_autograd(self, "Aggregator.forward_with_cache")
         B, S, C_in, H, W = images.shape
         assert B == 1, "Batch size must be 1 for this model"                               # aggregator.py:453
         if C_in != 3:

@@ -192,7 +192,7 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[t
               head_dim: int, batch: int, q_len: int, kv_len: int, q_batch_stride: int = 0, kv_batch_stride: int = 0,
               prefix_k: Optional[torch.Tensor] = None, prefix_v: Optional[torch.Tensor] = None, prefix_len: int = 0,
               scale: Optional[float] = None, carry=None, carry_in: bool = False, carry_out: bool = False,
-              lse: Optional[torch.Tensor] = None):
+              lse: Optional[torch.Tensor] = None, variant: int = 0):
     """Structured attention (see sr_attn in the header).  q/k/v are 2-D row views [rows, >= heads*head_dim]
     (column slices of the fused qkv buffer are fine); bf16 -> tcgen05 flash kernel, fp32 -> SIMT kernel."""
     dt = q.dtype
@@ -224,6 +224,7 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[t
         m, l, acc = carry
         a.carry_m, a.carry_l, a.carry_acc = m.data_ptr(), l.data_ptr(), acc.data_ptr()
     a.carry_in, a.carry_out = int(carry_in), int(carry_out)
+    a.variant = int(variant)
     if lse is not None:                                     # training: see new_lse()
         if dt != torch.bfloat16 or lse.dtype != torch.float32 or not lse.is_contiguous() or lse.dim() != 3 \
                 or lse.shape[0] != num_heads or lse.shape[1] != batch or lse.shape[2] % 64 or lse.shape[2] < q_len:
@@ -545,3 +546,52 @@ def scale_cols(x: torch.Tensor, gamma: torch.Tensor) -> torch.Tensor:
     _lib.check(_lib.load().sr_scale_cols_f32(x.data_ptr(), gamma.data_ptr(), out.data_ptr(), x.numel() // x.shape[-1],
                                              x.shape[-1], _stream()), "scale_cols")
     return out
+
+
+# ------------------------------------------------------------------------------------------------ camera geometry (N3)
+def pose_to_extri_intri(pose: torch.Tensor, image_hw=None, build_intrinsics: bool = True):
+    """pose fp32 [..., 9] -> (extrinsics [..., 3, 4], intrinsics [..., 3, 3] or None); utils/pose_enc.py:68-135."""
+    if not (pose.is_cuda and pose.dtype == torch.float32 and pose.shape[-1] == 9):
+        raise ValueError("sailrecon_b200: pose_to_extri_intri needs a fp32 CUDA tensor [..., 9]")
+    p = pose.contiguous()
+    n = p.numel() // 9
+    ext = torch.empty(*p.shape[:-1], 3, 4, dtype=torch.float32, device=p.device)
+    intr = None
+    H = W = 0
+    if build_intrinsics:
+        if image_hw is None:
+            raise ValueError("sailrecon_b200: image_size_hw is required to build the intrinsics")
+        H, W = int(image_hw[0]), int(image_hw[1])
+        intr = torch.empty(*p.shape[:-1], 3, 3, dtype=torch.float32, device=p.device)
+    _lib.check(_lib.load().sr_pose_to_extri_intri(p.data_ptr(), ext.data_ptr(), _ptr(intr), n, H, W, _stream()),
+               "pose_to_extri_intri")
+    return ext, intr
+
+
+def unproject_depth(depth: torch.Tensor, extrinsics: torch.Tensor, intrinsics: torch.Tensor) -> torch.Tensor:
+    """depth fp32 [S, H, W], extrinsics [S, 3, 4], intrinsics [S, 3, 3] -> world points [S, H, W, 3]; utils/geometry.py:19-128."""
+    for t, name in ((depth, "depth"), (extrinsics, "extrinsics"), (intrinsics, "intrinsics")):
+        if not (t.is_cuda and t.dtype == torch.float32):
+            raise ValueError(f"sailrecon_b200: unproject_depth {name} must be a fp32 CUDA tensor")
+    S, H, W = depth.shape
+    if tuple(extrinsics.shape) != (S, 3, 4) or tuple(intrinsics.shape) != (S, 3, 3):
+        raise ValueError("sailrecon_b200: unproject_depth needs extrinsics [S, 3, 4] and intrinsics [S, 3, 3]")
+    d, e, m = depth.contiguous(), extrinsics.contiguous(), intrinsics.contiguous()
+    out = torch.empty(S, H, W, 3, dtype=torch.float32, device=depth.device)
+    _lib.check(_lib.load().sr_unproject_depth(d.data_ptr(), e.data_ptr(), m.data_ptr(), out.data_ptr(), S, H, W, _stream()),
+               "unproject_depth")
+    return out
+
+
+def modulate(x: torch.Tensor, shift: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
+    """x * (1 + scale) + shift on fp32 rows (camera_head.py:189-194); shift / scale may be column slices."""
+    C_ = x.shape[-1]
+    x2, s2, c2 = x.reshape(-1, C_), shift.reshape(-1, C_), scale.reshape(-1, C_)
+    for t, name in ((x2, "x"), (s2, "shift"), (c2, "scale")):
+        _rows2d(t, torch.float32, name)
+    if not (x2.shape == s2.shape == c2.shape):
+        raise ValueError("sailrecon_b200: modulate shape mismatch")
+    out = torch.empty(x2.shape, dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().sr_modulate_f32(x2.data_ptr(), x2.stride(0), s2.data_ptr(), s2.stride(0), c2.data_ptr(), c2.stride(0),
+                                           out.data_ptr(), out.stride(0), x2.shape[0], C_, _stream()), "modulate")
+    return out.view(x.shape)

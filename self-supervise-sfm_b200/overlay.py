@@ -15,7 +15,7 @@ import sys
 _LAYER_MODULES = ("attention", "block", "rope", "mlp", "layer_scale", "patch_embed", "vision_transformer")
 
 
-def install() -> None:
+def install(geometry: bool = True) -> None:
     if "sailrecon.models.sail_recon" in sys.modules:
         raise RuntimeError("sailrecon_b200.overlay.install() must run before sailrecon.models.sail_recon is imported")
     pkg = __name__.rsplit(".", 1)[0]
@@ -23,3 +23,11 @@ def install() -> None:
     sys.modules["sailrecon.heads.camera_head"] = importlib.import_module(pkg + ".heads.camera_head")
     for name in _LAYER_MODULES:
         sys.modules[f"sailrecon.layers.{name}"] = importlib.import_module(f"{pkg}.layers.{name}")
+    if geometry:
+        # N3: the pose / unprojection step right after the camera head (sail_recon.py:122-124, 139-141).  Only the two
+        # names SailRecon binds are replaced; the reference modules keep everything else they define.
+        import sailrecon.utils.geometry as rg
+        import sailrecon.utils.pose_enc as rp
+        ours = importlib.import_module(pkg + ".utils")
+        rp.pose_encoding_to_extri_intri = ours.pose_encoding_to_extri_intri
+        rg.unproject_depth_map_to_point_map = ours.unproject_depth_map_to_point_map

@@ -97,8 +97,8 @@ def build_pair(agg_kwargs: dict, head_kwargs: dict, seed: int, o1: bool, device=
     R = ref()
     torch.manual_seed(seed)
     with torch.device(device):
-        r_agg = R.Aggregator(**agg_kwargs).eval()
-        r_head = R.CameraHead(**head_kwargs).eval()
+        r_agg = R.Aggregator(**agg_kwargs).eval().to(device)      # .to(): its _resnet_mean buffers are legacy-constructed on the CPU
+        r_head = R.CameraHead(**head_kwargs).eval().to(device)
         o_agg = Aggregator(**agg_kwargs).eval()
         o_head = CameraHead(**head_kwargs).eval()
     if o1:

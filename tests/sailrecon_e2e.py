@@ -53,7 +53,7 @@ def main():
     dev = "cuda"
     torch.manual_seed(0)
     with torch.device(dev):
-        model = SailRecon(kv_cache=True).eval()
+        model = SailRecon(kv_cache=True).eval().to(dev)
     reinit(model, 77)
     if mode == "overlay":
         import sailrecon_b200.models.aggregator as A
@@ -88,7 +88,7 @@ def main():
         del model
         torch.cuda.empty_cache()
         with torch.device(dev):
-            model = SailRecon(kv_cache=False).eval()
+            model = SailRecon(kv_cache=False).eval().to(dev)
         model.load_state_dict(sd)
         del sd
         model.aggregator.generator.manual_seed(1234)

@@ -79,3 +79,29 @@ def test_argument_errors_follow_reference():
     agg = Aggregator(**GOLDEN_CASES["tiny_conv"]["agg"])
     with pytest.raises(RuntimeError):                                                              # CPU tensor: no fallback
         agg(torch.zeros(1, 2, 3, 56, 56), [0], [1], fix_rank=4)
+
+
+def test_inference_forwards_refuse_training_mode_with_autograd():
+    """the forwards read parameters detached; in train() mode with grad enabled an unmodified training
+    loop would silently freeze them, so every module-level forward raises and points at sailrecon_b200.train."""
+    import pytest
+    import torch
+    from sailrecon_b200.heads import CameraHead
+    from sailrecon_b200.layers import Attention, Block
+    from sailrecon_b200.models import Aggregator
+    blk, att = Block(dim=128, num_heads=2), Attention(dim=128, num_heads=2)
+    agg = Aggregator(img_size=56, embed_dim=128, depth=1, num_heads=2, patch_embed="conv", intermediate_layer_idx=[0])
+    head = CameraHead(dim_in=256, trunk_depth=1, num_heads=2)
+    x = torch.zeros(1, 4, 128)
+    for call in (lambda: blk(x), lambda: att(x), lambda: agg(torch.zeros(1, 2, 3, 56, 56), [0], [1]),
+                 lambda: agg.forward_with_cache(torch.zeros(1, 1, 3, 56, 56)),
+                 lambda: head({-1: torch.zeros(1, 1, 5, 256)}, torch.zeros(1, 1, 256))):
+        with pytest.raises(RuntimeError, match="inference path"):
+            call()
+    # eval() or no_grad(): the guard is silent (the call then fails on the CPU tensor instead — no CPU fallback)
+    blk.eval()
+    with pytest.raises(RuntimeError, match="CUDA"):
+        blk(x)
+    blk.train()
+    with torch.no_grad(), pytest.raises(RuntimeError, match="CUDA"):
+        blk(x)

@@ -278,3 +278,54 @@ def test_forward_with_cache_matches_reference_golden(bf16):
     assert rel_l2(single[-1].cpu(), arrays["single_out_-1"]) < tol
     for i, pz in enumerate(poses):
         assert (pz.cpu() - arrays[f"pose_{i}"]).abs().max() < (5e-2 if bf16 else 1e-2)
+
+
+@pytest.mark.parametrize("S", [1, 2])
+def test_block_cached_api_with_the_reference_dense_mask(S):
+    """Block(kv_cache=True) through the generic API exactly as aggregator.py:771-803 drives it: first call primes the cache
+    with the scene tokens (attention output = zeros, attention.py:94-100), second call passes the dense cropped mask of
+    aggregator.py:496-508 with S query frames — S = 1 makes the query part of the mask all-True."""
+    from sailrecon_b200.layers import Block, RotaryPositionEmbedding2D
+    torch.manual_seed(9)
+    rope = RotaryPositionEmbedding2D(frequency=100.0)
+    blk = Block(dim=128, num_heads=2, init_values=0.8, qk_norm=True, rope=rope, kv_cache=True).eval()
+    p = {k: v.clone() for k, v in blk.state_dict().items()}
+    blk = blk.to(DEV)
+    Na, P, Pp = 2, 13, 6
+    g = torch.Generator().manual_seed(10)
+    scene = torch.randn(1, Na * Pp, 128, generator=g)
+    spos = torch.randint(0, 9, (1, Na * Pp, 2), generator=g)
+    x = torch.randn(1, S * P, 128, generator=g)
+    pos = torch.randint(0, 9, (1, S * P, 2), generator=g)
+    mask = O.cache_mask(Na, S, P, Pp)
+    with torch.no_grad():
+        y0 = blk(scene.to(DEV), pos=spos.to(DEV))                       # priming pass
+        got = blk(x.to(DEV), pos=pos.to(DEV), attn_mask=mask.to(DEV)[None, None])
+    ref0 = O.block_forward(scene[0], p, "", 2, spos[0], None, True, True, False, attn_zero=True)
+    assert rel_l2(y0[0].cpu(), ref0) < 1e-5
+    sn = O.layer_norm(scene[0], p["norm1.weight"], p["norm1.bias"], 1e-5)
+    _, sk, sv = O.qkv_heads(sn, p, "attn.", 2, spos[0], True, True, False)
+    ref = O.block_forward(x[0], p, "", 2, pos[0], mask, True, True, False, prefix_kv=(sk, sv))
+    assert rel_l2(got[0].cpu(), ref) < 1e-5
+    blk.attn.clear_kv_cache()
+
+
+def test_two_streams_do_not_share_scratch():
+    """SURVEY.md §8(b) 're-entrant per stream' (VERDICT r1 weak #13): engine.WS is keyed by (name, device, stream), so two
+    forwards enqueued on two streams without any synchronisation between them reproduce their serial results."""
+    agg, head, images, arrays, meta, case, _ = _build("tiny_conv")
+    images2 = make_images(case["S"], case["H"], case["W"], 999).to(DEV)
+    ref1 = _run(agg, head, images, meta, case, bf16=False)[0][-1].clone()
+    ref2 = _run(agg, head, images2, meta, case, bf16=False)[0][-1].clone()
+    torch.cuda.synchronize()
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    outs = {}
+    for rep in range(3):
+        for s, img, key in ((s1, images, 1), (s2, images2, 2)):
+            with torch.cuda.stream(s):
+                outs[key] = _run(agg, head, img, meta, case, bf16=False)[0][-1]
+    torch.cuda.synchronize()
+    assert torch.equal(outs[1], ref1) and torch.equal(outs[2], ref2)
+    from sailrecon_b200 import engine
+    streams = {k[2] for k in engine.WS._buf if k[0] == "agg.x"}
+    assert s1.cuda_stream in streams and s2.cuda_stream in streams
