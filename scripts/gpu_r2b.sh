@@ -1,5 +1,7 @@
 #!/bin/bash
 cd "${GRAFT_REPO_ROOT:-.}"
 mkdir -p gpurun_out
-timeout 1700 python -m pytest tests/test_reference_gpu.py tests/test_overlay_gpu.py "tests/test_modules_gpu.py::test_forward_with_cache_matches_reference_golden" "tests/test_kernels_gpu.py" -m gpu -q -s --timeout 1400 > gpurun_out/pytest_ref.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_ref.log
-grep -E "parity|passed|failed|Error|exit|assert" gpurun_out/pytest_ref.log | tail -40
+timeout 2400 python -m pytest tests -m gpu -q -s --timeout 1400 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
+grep -E "parity|passed|failed|Error|exit|assert|FAILED" gpurun_out/pytest_gpu.log | tail -60
+timeout 600 python bench.py --workload reloc --anchors 100 --queries 20 --steps 2 --warmup 3 > gpurun_out/bench_reloc.log 2> gpurun_out/bench_reloc.err; echo "reloc exit $?"
+tail -3 gpurun_out/bench_reloc.err; cat gpurun_out/bench_reloc.log

@@ -334,6 +334,43 @@ def block_tail(blk: nn.Module, x: torch.Tensor, a: torch.Tensor, mode: str, tag:
     return x
 
 
+def run_block_camera_rows(blk: nn.Module, X: torch.Tensor, S: int, P: int, prefix: Prefix,
+                          rows_pos: Optional[RowPositions], mode: str, tag: str = "") -> torch.Tensor:
+    """The LAST reloc block of a camera-only localisation (SailRecon.reloc(fast_reloc=True), sail_recon.py:240-244): the
+    caller only reads token 0 of every frame (`rgb_feats[-1][:, :, 0]`), so the block's query side, output projection and
+    MLP run on those S rows alone; K / V are still produced for all S*P rows (the camera token attends to its whole frame
+    behind the cached scene prefix).  X [S*P, C] fp32 is NOT modified; returns the S updated camera rows [S, C] fp32."""
+    T, C = X.shape
+    dev = X.device
+    act = torch.bfloat16 if mode == "bf16" else torch.float32
+    attn = blk.attn
+    a = WS.get(tag + "a", (T, C), act, dev)
+    w1, b1, eps1 = ln_params(blk.norm1)
+    ops.layernorm(X, w1, b1, eps1, a)
+    cam_pos = None
+    if rows_pos is not None:
+        cam_pos = RowPositions(rows_pos.pos32.view(S, P, 2)[:, 0].contiguous(), rows_pos.max_pos)
+    if mode == "bf16":
+        kv = WS.get(tag + "kv", (T, 2 * C), act, dev)
+        qkv_rows(attn, a, kv, mode, rows_pos, col_offset=C)                           # k | v for every row
+        k, v = kv[:, :C], kv[:, C:]
+        a_cam = a.view(S, P, C)[:, 0].contiguous()
+        q = WS.get(tag + "q_cam", (S, C), act, dev)
+        qkv_rows(attn, a_cam, q, mode, cam_pos, col_offset=0, n_cols=C)               # q for the camera rows only
+    else:
+        qkv = WS.get(tag + "qkv", (T, 3 * C), act, dev)
+        qkv_rows(attn, a, qkv, mode, rows_pos)
+        k, v = qkv[:, C:2 * C], qkv[:, 2 * C:]
+        q = qkv.view(S, P, 3 * C)[:, 0, :C].contiguous()
+    o = WS.get(tag + "o_cam", (S, C), act, dev)
+    H = attn.num_heads
+    ops.attention(q, k, v, o, H, C // H, S, 1, P, 1, P, prefix_k=prefix.k[prefix.row0:prefix.row0 + prefix.length],
+                  prefix_v=prefix.v[prefix.row0:prefix.row0 + prefix.length], prefix_len=prefix.length, scale=attn.scale)
+    x_cam = X.view(S, P, C)[:, 0].clone()
+    block_tail(blk, x_cam, o, mode, tag + "cam.")
+    return x_cam
+
+
 def linear_rows(lin: nn.Module, a_in: torch.Tensor, out: torch.Tensor, mode: str, kind: int = SR_EPI_BIAS) -> torch.Tensor:
     """A plain nn.Linear on rows through the GEMM kernels (bf16 tensor-core path needs K % 64 == 0, N % 128 == 0)."""
     w = weight_bf16(lin) if mode == "bf16" else weight_f32(lin)

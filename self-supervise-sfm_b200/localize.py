@@ -1,0 +1,233 @@
+"""Two-phase localisation — the train/demo_imc.py workload as a B200-first fast path.
+
+Reference flow (sail_recon.py:176-286, demo_imc.py:91-106): `tmp_forward(anchor images)` primes the scene K/V cache of the
+24 reloc blocks (parked on the CPU, ~4.5 GB moved back over PCIe on EVERY `reloc` call at 100 anchors), then one `reloc`
+call per query image builds a ((Na + 1) * P)^2 boolean mask on the host (19 GB at 100 anchors) and runs ~700 small library
+kernels.  Here:
+
+  * the scene K/V cache never leaves HBM (layers/attention.py, models/aggregator.py);
+  * `Localizer.localize` runs the camera-only path (`Aggregator.forward_with_cache(camera_only=True)` -> `CameraHead` ->
+    `pose_encoding_to_extri_intri`): what `reloc(fast_reloc=True)` returns, without producing the patch-token outputs
+    nobody reads;
+  * one query image is ~650 launches of 5-50 us each, i.e. launch-latency bound from Python: the whole per-image pipeline
+    is captured ONCE into a CUDA graph (static input / output buffers) and replayed per image.
+
+Host code is Python / PyTorch plumbing; every kernel is the C-ABI library's.  No CPU fallback.
+"""
+from __future__ import annotations
+
+import json
+import os
+from typing import Optional, Tuple
+
+import torch
+
+from . import engine, ops
+from .utils import pose_encoding_to_extri_intri
+
+
+class Localizer:
+    """scene = Localizer(aggregator, camera_head); scene.build(anchor_images); pose, ext, intr = scene.localize(image)."""
+
+    def __init__(self, aggregator, camera_head, fix_rank: Optional[int] = 300, use_cuda_graph: bool = True,
+                 autocast_bf16: bool = True):
+        if not aggregator.kv_cache:
+            raise ValueError("sailrecon_b200: Localizer needs Aggregator(kv_cache=True) (SailRecon(kv_cache=True), demo_imc.py)")
+        self.agg, self.head = aggregator, camera_head
+        self.fix_rank, self.use_graph, self.bf16 = fix_rank, use_cuda_graph, autocast_bf16
+        self.cam_token_last_layer: Optional[torch.Tensor] = None
+        self._graph = None
+        self._key = None
+        self._stream: Optional[torch.cuda.Stream] = None
+
+    # ---------------------------------------------------------------------------------------------- phase 1
+    def clear(self) -> None:
+        """SailRecon.clear_cache (sail_recon.py:161-174)."""
+        for blk in self.agg.global_reloc_blocks:
+            blk.attn.clear_kv_cache()
+        self.cam_token_last_layer = None
+        self._graph = None
+        self._key = None
+
+    def build(self, anchor_images: torch.Tensor) -> torch.Tensor:
+        """SailRecon.tmp_forward (sail_recon.py:176-199): anchor_images [Na, 3, H, W] (or [1, Na, 3, H, W]) in [0, 1]."""
+        self.clear()
+        imgs = anchor_images if anchor_images.dim() == 5 else anchor_images[None]
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
+            _, _, cam = self.agg(imgs, list(range(imgs.shape[1])), [], fix_rank=self.fix_rank)
+        self.cam_token_last_layer = cam.clone()
+        return self.cam_token_last_layer
+
+    # ---------------------------------------------------------------------------------------------- phase 2
+    def _pipeline(self, images: torch.Tensor):
+        """What SailRecon.reloc(fast_reloc=True) computes (sail_recon.py:218-244), camera rows only."""
+        with torch.no_grad():
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
+                feats, _ = self.agg.forward_with_cache(images, fix_rank=self.fix_rank, camera_only=True)
+            with torch.autocast("cuda", enabled=False):
+                poses = self.head(feats, self.cam_token_last_layer)
+                ext, intr = pose_encoding_to_extri_intri(poses[-1], (images.shape[-2], images.shape[-1]))
+        return poses[-1], ext, intr
+
+    def localize(self, images: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+        """images [S, 3, H, W] (or [1, S, 3, H, W]), S query frames localised independently against the scene.
+        Returns (pose encodings [1, S, 9], extrinsics [1, S, 3, 4], intrinsics [1, S, 3, 3]).  With the CUDA graph the
+        returned tensors are the graph's static outputs: they are overwritten by the next call (clone to keep them)."""
+        if self.cam_token_last_layer is None:
+            raise RuntimeError("sailrecon_b200: Localizer.localize needs a scene (call build(anchor_images) first)")
+        imgs = images if images.dim() == 5 else images[None]
+        engine.require_cuda_f32(imgs, "images")
+        if not self.use_graph:
+            return self._pipeline(imgs)
+        key = (tuple(imgs.shape), imgs.device)
+        if self._graph is None or self._key != key:
+            self._capture(imgs, key)
+        self._static_in.copy_(imgs, non_blocking=True)
+        self._graph.replay()
+        return self._static_out
+
+    def _capture(self, imgs: torch.Tensor, key) -> None:
+        """Warm up on a side stream (lazy per-kernel attributes, bf16 weight copies, position / RoPE tables), then record
+        the per-image pipeline once.  Scratch buffers (engine.WS is keyed per stream) and outputs live in the graph's pool."""
+        dev = imgs.device
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(device=dev)
+        self._static_in = imgs.clone()
+        self._stream.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(self._stream):
+            for _ in range(2):
+                self._pipeline(self._static_in)
+        torch.cuda.current_stream(dev).wait_stream(self._stream)
+        torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=self._stream):
+            self._static_out = self._pipeline(self._static_in)
+        self._graph, self._key = g, key
+        # the graph holds raw addresses of the per-stream scratch buffers: keep them alive even if engine.WS is cleared
+        sid = self._stream.cuda_stream
+        self._keep = [buf for k, buf in engine.WS._buf.items() if k[2] == sid]
+
+
+# ------------------------------------------------------------------------------------------------ bench.py --workload reloc
+def bench_reloc(args, rank: int, world: int, local: int) -> None:
+    """BASELINE.json configs[2] as demo_imc.py runs it: `--anchors` frames build the scene (tmp_forward), then `--queries`
+    images are localised ONE PER CALL against the HBM-resident scene K/V (camera-only, fast_reloc).  Each rank holds its
+    own scene (no data-path collective: replicas).  value = localised images / s on the device-resident images;
+    e2e = each image copied from pinned host memory and its extrinsics read back inside the timed region."""
+    import bench as _bench
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --workload reloc needs a B200: sailrecon_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from .heads import CameraHead
+    from .models import Aggregator
+    Na, Nq, size = args.anchors, args.queries, args.size
+    torch.manual_seed(0)
+    with torch.device(dev):
+        agg = Aggregator(kv_cache=True).eval()
+        head = CameraHead(dim_in=2048).eval()
+    g = torch.Generator().manual_seed(1 + rank)
+    host_anchors = torch.rand(Na, 3, size, size, generator=g).pin_memory()
+    host_queries = torch.rand(Nq, 3, size, size, generator=g).pin_memory()
+    queries = host_queries.to(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    res = {}
+    for graph in (False, True):
+        loc = Localizer(agg, head, use_cuda_graph=graph)
+        agg.generator.manual_seed(1234)
+        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+        barrier()
+        t0.record()
+        loc.build(host_anchors.to(dev, non_blocking=True))
+        t1.record()
+        barrier()
+        build_ms = t0.elapsed_time(t1)
+        for i in range(max(args.warmup, 3)):
+            loc.localize(queries[i % Nq:i % Nq + 1])
+        barrier()
+        clocks = _bench.ClockSampler(local)
+        clocks.start()
+        n0 = ops.num_kernel_launches()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            for i in range(Nq):
+                pose, ext, intr = loc.localize(queries[i:i + 1])
+        e1.record()
+        barrier()
+        launches = ops.num_kernel_launches() - n0
+        clk = clocks.stop()
+        ms = e0.elapsed_time(e1) / (args.steps * Nq)
+        ref_ext = ext.clone()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            for i in range(Nq):
+                pose, ext, intr = loc.localize(host_queries[i:i + 1].to(dev, non_blocking=True))
+                host_ext = ext.cpu()
+        e1.record()
+        barrier()
+        ms_e2e = e0.elapsed_time(e1) / (args.steps * Nq)
+        res[graph] = dict(ms=ms, ms_e2e=ms_e2e, build_ms=build_ms, launches=launches, clk=clk,
+                          finite=bool(torch.isfinite(host_ext).all()), ext=ref_ext)
+        loc.clear()
+    same = float((res[True]["ext"] - res[False]["ext"]).abs().max())
+    # where the per-image time goes (eager path, events around every launch)
+    loc = Localizer(agg, head, use_cuda_graph=False)
+    agg.generator.manual_seed(1234)
+    loc.build(host_anchors.to(dev))
+    ops.PROFILE = []
+    for i in range(min(Nq, 8)):
+        loc.localize(queries[i:i + 1])
+    barrier()
+    records, ops.PROFILE = ops.PROFILE, None
+    prof = _bench.summarize_profile(records)
+    n_prof = min(Nq, 8)
+    if world > 1:
+        t = torch.tensor([res[True]["ms"], res[True]["ms_e2e"], res[False]["ms"]], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res[True]["ms"], res[True]["ms_e2e"], res[False]["ms"] = (float(x) for x in t)
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(_bench.ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        hbm = peaks.get("hbm_gbs", 6500.0)
+        kern = {k: {"launches_per_image": v["launches"] // n_prof, "ms_per_image": v["ms"] / n_prof,
+                    "tflops": (v["flops"] / (v["ms"] * 1e-3) / 1e12) if v["flops"] else None,
+                    "gbs": v["bytes"] / (v["ms"] * 1e-3) / 1e9} for k, v in prof.items()}
+        gf = kern.get("gemm_f32", {})
+        r = res[True]
+        line = {"metric": f"localised images/s against a cached scene of {Na} anchors ({size}px, camera-only reloc)",
+                "value": world * 1e3 / r["ms"], "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+                "ms_per_step": r["ms"] * Nq, "ms_per_image": r["ms"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": f"reloc: tmp_forward over {Na} anchor frames once ({r['build_ms']:.0f} ms), then {Nq} query images "
+                                       f"localised one per call (demo_imc.py:91-106, fast_reloc): DINOv2 ViT-L + 24 x (frame, reloc) "
+                                       "blocks against the HBM-resident scene K/V + fp32 camera head + pose -> extrinsics / "
+                                       "intrinsics; the per-image pipeline is one CUDA-graph replay; one scene per GPU (replicas)",
+                           "l2": "per image the camera head streams 4 x 865 MB of fp32 weights and the scene K/V is 24 x "
+                                 f"{Na * 305 * 2048 * 2 / 1e6:.0f} MB: far beyond the 126 MB L2; no flush needed"},
+                "e2e": {"value": world * 1e3 / r["ms_e2e"], "unit": "images/s", "h2d_bytes_per_step": 3 * size * size * 4 * Nq,
+                        "d2h_bytes_per_step": 48 * Nq},
+                "gpu_launches": res[False]["launches"], "gpu_launches_note": "kernel launches of the eager path; the graph "
+                "replays the same kernels with one cudaGraphLaunch per image", "clocks": r["clk"],
+                "roofline": {"bound": "hbm", "kernel": "gemm_f32 (camera head, fp32 weights read once per launch)",
+                             "achieved": gf.get("gbs"), "peak": hbm, "unit": "GB/s",
+                             "frac": (gf.get("gbs") or 0.0) / hbm, "traffic": None,
+                             "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+                "eager_ms_per_image": res[False]["ms"], "graph_ms_per_image": r["ms"], "scene_build_ms": r["build_ms"],
+                "graph_vs_eager_max_abs_extrinsics": same, "kernels": kern, "outputs_finite": r["finite"]}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()

@@ -76,6 +76,7 @@ class Aggregator(nn.Module):
         self.num_recon = 0
         self.rank = 0
         self._pos_cache = {}
+        self._sel_cache = {}
 
     def __build_patch_embed__(self, patch_embed, img_size, patch_size, num_register_tokens, interpolate_antialias=True,
                               interpolate_offset=0.0, block_chunks=0, init_values=1.0, embed_dim=1024):
@@ -134,8 +135,13 @@ class Aggregator(nn.Module):
         cam, reg = self.camera_token.detach()[0], self.register_token.detach()[0]          # [2,1,C], [2,R,C]
         slots = torch.cat([torch.cat([cam[0], reg[0]], 0)[None], torch.cat([cam[1], reg[1]], 0)[None],
                            torch.cat([self.camera_token_reloc.detach()[0, 0], self.register_token_reloc.detach()[0, 0]], 0)[None]])
-        sel = [2 if (all_reloc or f in reloc) else (0 if f == 0 else 1) for f in order]
-        return slots[torch.tensor(sel, device=slots.device)]
+        sel = tuple(2 if (all_reloc or f in reloc) else (0 if f == 0 else 1) for f in order)
+        key = (sel, slots.device)
+        idx = self._sel_cache.get(key)               # cached: no H2D copy per call (and none under CUDA-graph capture)
+        if idx is None:
+            idx = torch.tensor(sel, device=slots.device)
+            self._sel_cache = {key: idx}
+        return slots[idx]
 
     def _draw_scene(self, Na: int, P: int, hw: int, l_prime: int, frame_pos_cpu: torch.Tensor):
         """aggregator.py:580-626 for one layer, host side: per anchor (batch-major, anchor order of no_reloc_list) ONE
@@ -246,8 +252,11 @@ class Aggregator(nn.Module):
         return output_dict, self.patch_start_idx, cam_token_last_layer
 
     def forward_with_cache(self, images: torch.Tensor, cameras: torch.Tensor = None, camera_dropout: float = False,
-                           fix_rank: Union[int, None] = None) -> Tuple[dict, int]:
-        """aggregator.py:435-578: every frame is a query localised against the cached scene K/V (HBM resident)."""
+                           fix_rank: Union[int, None] = None, camera_only: bool = False) -> Tuple[dict, int]:
+        """aggregator.py:435-578: every frame is a query localised against the cached scene K/V (HBM resident).
+        `camera_only=True` (not in the reference; used by localize.Localizer for SailRecon.reloc(fast_reloc=True),
+        sail_recon.py:240-244, where only `rgb_feats[-1][:, :, 0]` is read): no intermediate outputs are written and the last
+        reloc block computes its query side / projection / MLP for the camera rows only; returns {-1: [1, S, 1, 2C]}."""
         engine.forbid_autograd(self, "Aggregator.forward_with_cache")
         B, S, C_in, H, W = images.shape
         assert B == 1, "Batch size must be 1 for this model"                               # aggregator.py:453
@@ -271,7 +280,7 @@ class Aggregator(nn.Module):
         for i in range(self.depth):
             engine.run_block(self.frame_blocks[i], X, frame_calls, rows_pos, mode, tag="agg.")
             out_i = None
-            if i in self.intermediate_layer_idx:
+            if i in self.intermediate_layer_idx and not camera_only:
                 out_i = torch.empty(1, S, P, 2 * C, dtype=torch.float32, device=dev)
                 ops.copy_cols(X, out_i.view(S * P, 2 * C), 0)
             attn = self.global_reloc_blocks[i].attn
@@ -279,6 +288,10 @@ class Aggregator(nn.Module):
                 raise RuntimeError("sailrecon_b200: forward_with_cache needs a primed scene kv cache (run forward() with "
                                    "kv_cache=True first, SailRecon.tmp_forward)")
             pre = Prefix(attn.k_cache, attn.v_cache, 0, attn.k_cache.shape[0])
+            if camera_only and i == self.depth - 1:
+                cam_frame = X.view(S, P, C)[:, 0]
+                cam_reloc = engine.run_block_camera_rows(self.global_reloc_blocks[i], X, S, P, pre, rows_pos, mode, tag="agg.")
+                return {-1: torch.cat([cam_frame, cam_reloc], dim=-1).view(1, S, 1, 2 * C)}, self.patch_start_idx
             engine.run_block(self.global_reloc_blocks[i], X, [AttnCall(0, S, P, P, pre)], rows_pos, mode, tag="agg.")
             if out_i is not None:
                 ops.copy_cols(X, out_i.view(S * P, 2 * C), C)

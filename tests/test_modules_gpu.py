@@ -329,3 +329,49 @@ def test_two_streams_do_not_share_scratch():
     from sailrecon_b200 import engine
     streams = {k[2] for k in engine.WS._buf if k[0] == "agg.x"}
     assert s1.cuda_stream in streams and s2.cuda_stream in streams
+
+
+@pytest.mark.parametrize("bf16", [False, True])
+def test_localizer_camera_only_matches_full_reloc_path(bf16):
+    """N2: localize.Localizer (camera-only forward_with_cache + camera head + pose -> extrinsics, eager and as a CUDA-graph
+    replay) returns what the full cached path returns for the camera: SailRecon.reloc(fast_reloc=True) semantics
+    (sail_recon.py:218-244).  Full width (C = 1024, 16 heads, bf16 tensor-core kernels at M = 1 rows) at 224 px."""
+    from sailrecon_b200.heads import CameraHead
+    from sailrecon_b200.localize import Localizer
+    from sailrecon_b200.models import Aggregator
+    from sailrecon_b200.utils import pose_encoding_to_extri_intri
+    torch.manual_seed(0)
+    agg = Aggregator(img_size=224, depth=2, intermediate_layer_idx=[0, 1], kv_cache=True).eval()
+    agg.patch_embed.blocks = agg.patch_embed.blocks[:2]
+    head = CameraHead(dim_in=2048, trunk_depth=1).eval()
+    shapes = {"agg." + k: list(v.shape) for k, v in agg.state_dict().items()}
+    shapes.update({"head." + k: list(v.shape) for k, v in head.state_dict().items()})
+    params = make_params(shapes, 44)
+    agg.load_state_dict({k[4:]: v for k, v in params.items() if k.startswith("agg.")})
+    head.load_state_dict({k[5:]: v for k, v in params.items() if k.startswith("head.")})
+    agg, head = agg.to(DEV), head.to(DEV)
+    anchors = make_images(3, 224, 224, 144)[0].to(DEV)
+    queries = make_images(3, 224, 224, 145)[0].to(DEV)
+    eager = Localizer(agg, head, fix_rank=100, use_cuda_graph=False, autocast_bf16=bf16)
+    agg.generator.manual_seed(1234)
+    cam = eager.build(anchors)
+    # reference semantics: the FULL cached path, then the camera head on its last-layer tokens
+    with torch.no_grad():
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=bf16):
+            full, _ = agg.forward_with_cache(queries[None, :1], fix_rank=100)
+        poses = head(full, cam)
+        ext_ref, intr_ref = pose_encoding_to_extri_intri(poses[-1], (224, 224))
+    pose, ext, intr = eager.localize(queries[:1])
+    tol = 5e-3 if bf16 else 1e-4
+    assert rel_l2(pose, poses[-1]) < tol and rel_l2(ext, ext_ref) < tol and rel_l2(intr, intr_ref) < tol
+    graph = Localizer(agg, head, fix_rank=100, use_cuda_graph=True, autocast_bf16=bf16)
+    graph.cam_token_last_layer = cam                         # same primed scene
+    for i in range(3):
+        pe, ee, ie = eager.localize(queries[i:i + 1])
+        pe, ee = pe.clone(), ee.clone()
+        pg, eg, ig = graph.localize(queries[i:i + 1])
+        torch.cuda.synchronize()
+        assert torch.equal(pg, pe) and torch.equal(eg, ee), i            # same kernels, same inputs: bit-identical
+    eager.clear()
+    with pytest.raises(RuntimeError):
+        eager.localize(queries[:1])
