@@ -127,6 +127,10 @@ typedef struct sr_attn {
 int sr_debug_trace_read(long long* host_dst, int64_t count);
 
 int sr_attn_fwd_bf16(const sr_attn_t* p, void* stream);  /* tcgen05 flash attention, head_dim 64           */
+/* Host-only query (no GPU needed): the work decomposition sr_attn_fwd_bf16 uses for a launch of num_heads x batch
+ * (head, segment) rows of q_len query rows on num_sms SMs — n4 CTAs of four 128-row query tiles and n3 CTAs of three per
+ * row; all four-tile CTAs are dispatched first, so the lighter ones fill the tail wave.                           */
+int sr_attn_plan(int64_t q_len, int32_t num_heads, int32_t batch, int32_t num_sms, int32_t* n4, int32_t* n3);
 int sr_attn_fwd_f32(const sr_attn_t* p, void* stream);   /* fp32 SIMT, head_dim <= 128 (check mode, camera) */
 
 /* ---- Attention backward (training step, train_imc.py:358-380: autograd through attention.py:103-109) -----

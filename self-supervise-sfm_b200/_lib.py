@@ -78,6 +78,7 @@ SIGNATURES = {
     "sr_debug_trace_read": (C.c_int, [C.POINTER(C.c_longlong), _i64]),
     "sr_attn_fwd_bf16": (C.c_int, [C.POINTER(SrAttn), _vp]),
     "sr_attn_fwd_f32": (C.c_int, [C.POINTER(SrAttn), _vp]),
+    "sr_attn_plan": (C.c_int, [_i64, _i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)]),
     "sr_attn_bwd_bf16": (C.c_int, [C.POINTER(SrAttnBwd), _vp]),
     "sr_transpose_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _vp]),
     "sr_colsum": (C.c_int, [_vp, C.c_int, _i64, _vp, _i64, _vp, _i64, _i64, C.c_int, _vp]),

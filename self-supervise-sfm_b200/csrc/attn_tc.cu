@@ -494,26 +494,12 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
 
   {
     // Kernel choice.  The three- and four-tile kernels run the same ~590 clk per (128-row query tile x 64-row K/V tile)
-    // and one CTA per SM, so the launch time is  waves x tiles-per-CTA: pick the variant whose CTA count quantises
-    // better onto the SMs (16-anchor global: 688 CTAs of four tiles = 5 waves against 928 of three = 7 x 0.75;
-    // 16-frame reloc: 768 = 6 waves against 1024 = 7 x 0.75).  SR_ATTN_KERNEL = 2 / 3 / 4 forces a variant.
-    int variant = kAtKernelDefault;
-    if (a->variant != 0) {
-      variant = a->variant;                 // explicit per-call choice (tests exercise every variant on every case)
-    } else if (const char* env = dbg_env("SR_ATTN_KERNEL")) {
-      variant = atoi(env);
-    } else {
-      static int num_sms = 0;
-      if (num_sms == 0) {
-        int dev = 0;
-        SR_CHECK_CUDA(cudaGetDevice(&dev));
-        SR_CHECK_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-      }
-      const int64_t hb = static_cast<int64_t>(a->num_heads) * a->batch;
-      const int64_t waves3 = (((a->q_len + 383) / 384) * hb + num_sms - 1) / num_sms;
-      const int64_t waves4 = (((a->q_len + 511) / 512) * hb + num_sms - 1) / num_sms;
-      variant = (3 * waves3 < 4 * waves4) ? 3 : 4;
-    }
+    // and one CTA per SM, so a launch's time is the makespan of its CTAs weighted by their active query tiles.
+    // variant 0 (default): the four-tile kernel with its mixed four- / three-tile work decomposition (attn_tc4.cu,
+    // choose_mix); 4: the same kernel with uniform four-tile CTAs; 3: the three-tile kernel (P outside S, one issuer per tile).
+    int variant = a->variant != 0 ? a->variant : kAtKernelDefault;
+    if (a->variant == 0)
+      if (const char* env = dbg_env("SR_ATTN_KERNEL")) variant = atoi(env);
     // polynomial exp2 on the FMA pipe for 2 of every 8 pairs: measured best (0: 851, 1: 905, 2: 921, 3: 892, 4: 843 TF/s)
     int poly = 2;
     if (const char* env = dbg_env("SR_ATTN_POLY")) poly = atoi(env);

@@ -17,6 +17,11 @@
 //   warps 4-19          softmax: warp 4 + 4q + r owns rows [32r, 32r + 32) of query tile q, one thread per row
 // 640 threads; registers re-distributed with setmaxnreg (control 56, softmax 104).
 #include <cstdlib>
+#include <algorithm>
+#include <functional>
+#include <mutex>
+#include <queue>
+#include <vector>
 
 #include "attn_math.cuh"
 #include "common.cuh"
@@ -55,6 +60,12 @@ struct Attn4Params {
   int trace;
   float* lse;                        // training: [num_heads, batch, lse_pad] log2-domain log-sum-exp (nullptr = off)
   int lse_pad;
+  // Work decomposition (1-D grid).  A "row" is one (head, segment) pair; its query tiles are covered by n4 CTAs of four
+  // tiles followed by n3 CTAs of three tiles.  ALL four-tile CTAs of the launch come first in the grid, the three-tile
+  // CTAs last: the hardware dispatches CTAs in linear order onto SMs as they drain, so the lighter CTAs fill the tail wave
+  // (16-anchor global shape: 172 tiles per head = 37 x 4 + 8 x 3 -> 592 heavy CTAs = exactly 4 waves of 148 SMs + 128 light
+  // ones = 19 tile-steps of makespan instead of the 20 of 688 uniform four-tile CTAs; chosen per shape by choose_mix()).
+  int n_rows, n4, n3, batch;
 };
 
 template <int kPoly>
@@ -76,12 +87,25 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   uint8_t* sV = sK + k4Stages * k4KvTile;
   uint8_t* sK0 = sV + k4Stages * k4KvTile;                           // K(0)
 
-  const int head = blockIdx.y;
-  const int b = blockIdx.z;
-  const int q0 = blockIdx.x * (128 * k4NQ);                          // first query row (within the segment) of this CTA
-  const int nq_valid = min(k4NQ, (p.q_len - q0 + 127) / 128);        // query tiles that hold at least one row
+  int row, q0, nq_cap;                                               // see Attn4Params: heavy CTAs first, light CTAs last
+  {
+    const int lin = blockIdx.x, heavy = p.n_rows * p.n4;
+    if (lin < heavy) {
+      row = lin / p.n4;
+      q0 = (lin - row * p.n4) * 512;
+      nq_cap = 4;
+    } else {
+      const int r = lin - heavy;
+      row = r / p.n3;
+      q0 = p.n4 * 512 + (r - row * p.n3) * 384;
+      nq_cap = 3;
+    }
+  }
+  const int b = row / p.num_heads;
+  const int head = row - b * p.num_heads;
+  const int nq_valid = min(nq_cap, (p.q_len - q0 + 127) / 128);      // query tiles that hold at least one row
   const int n_tiles = p.n_prefix_tiles + p.n_own_tiles;
-  const bool trace_on = kDebugBuild && p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0;
+  const bool trace_on = kDebugBuild && p.trace && blockIdx.x == 0 && lane == 0;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_q);
@@ -356,7 +380,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         }
       }
       if (row_ok && p.lse != nullptr)
-        p.lse[(static_cast<int64_t>(head) * gridDim.z + b) * p.lse_pad + q_row] = m + log2f(l);
+        p.lse[(static_cast<int64_t>(head) * p.batch + b) * p.lse_pad + q_row] = m + log2f(l);
       if (row_ok && p.carry_out) {
         p.carry_m[static_cast<int64_t>(head) * p.total_q_rows + g_row] = m;
         p.carry_l[static_cast<int64_t>(head) * p.total_q_rows + g_row] = l;
@@ -390,6 +414,51 @@ static int launch4(dim3 grid, cudaStream_t st, const CUtensorMap& tq, const CUte
 int attn_tc4_trace_read(long long* host_dst, int64_t count) {
   SR_CHECK_CUDA(cudaMemcpyFromSymbol(host_dst, g_attn_trace, static_cast<size_t>(count) * sizeof(long long)));
   return SR_OK;
+}
+
+// Picks (n4, n3) for a launch of `rows` (head, segment) pairs with `t` query tiles each on `sms` SMs: simulates the in-order
+// dispatch of [all four-tile CTAs, then all three-tile CTAs] onto the earliest-free SM with CTA time ~ its active query
+// tiles (the kernel is bound by the per-tile softmax work, 1 CTA/SM) and keeps the smallest makespan.  Cached per shape.
+static void choose_mix(int t, int rows, int sms, int force_uniform, int* n4_out, int* n3_out) {
+  struct Key { int t, rows, sms, n4, n3; };
+  static std::mutex mu;
+  static std::vector<Key> cache;
+  const int a_max = (t + 3) / 4;
+  if (force_uniform) { *n4_out = a_max; *n3_out = 0; return; }
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    for (const Key& k : cache)
+      if (k.t == t && k.rows == rows && k.sms == sms) { *n4_out = k.n4; *n3_out = k.n3; return; }
+  }
+  long best = -1;
+  int best_a = a_max, best_b = 0;
+  std::vector<long> load(sms);
+  for (int a = a_max; a >= 0 && a >= a_max - 24; --a) {
+    const int rem = t - 4 * a;
+    const int b = rem > 0 ? (rem + 2) / 3 : 0;
+    if (a == 0 && b == 0) continue;
+    if (static_cast<long>(rows) * b > 16384) break;
+    // heavy phase in closed form, light phase with a min-heap
+    const long n_heavy = static_cast<long>(rows) * a;
+    const int last_heavy = (a == a_max && rem < 0) ? 4 + rem : 4;          // tiles of a row's last heavy CTA when b == 0
+    for (int i = 0; i < sms; ++i) load[i] = 4 * (n_heavy / sms + (i < n_heavy % sms ? 1 : 0));
+    (void)last_heavy;
+    std::priority_queue<long, std::vector<long>, std::greater<long>> heap(load.begin(), load.end());
+    for (int r = 0; r < rows; ++r)
+      for (int x = 0; x < b; ++x) {
+        const int cost = (x == b - 1) ? rem - 3 * (b - 1) : 3;
+        const long l = heap.top();
+        heap.pop();
+        heap.push(l + cost);
+      }
+    long mk = 0;
+    while (!heap.empty()) { mk = std::max(mk, heap.top()); heap.pop(); }
+    if (best < 0 || mk < best) { best = mk; best_a = a; best_b = b; }
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  cache.push_back({t, rows, sms, best_a, best_b});
+  *n4_out = best_a;
+  *n3_out = best_b;
 }
 
 // Called by sr_attn_fwd_bf16 (attn_tc.cu) after argument validation.
@@ -442,17 +511,40 @@ int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
   p.trace = dbg_env("SR_ATTN_TRACE") != nullptr;
   p.lse = a->lse;
   p.lse_pad = static_cast<int>(a->lse_pad);
-  dim3 grid(static_cast<unsigned>((a->q_len + 128 * k4NQ - 1) / (128 * k4NQ)), static_cast<unsigned>(a->num_heads),
-            static_cast<unsigned>(a->batch));
+  static int num_sms = 0;
+  if (num_sms == 0) {
+    int dev = 0;
+    SR_CHECK_CUDA(cudaGetDevice(&dev));
+    SR_CHECK_CUDA(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  p.batch = a->batch;
+  p.n_rows = a->num_heads * a->batch;
+  const int t_tiles = static_cast<int>((a->q_len + 127) / 128);
+  choose_mix(t_tiles, p.n_rows, num_sms, a->variant == 4, &p.n4, &p.n3);
+  const int64_t n_ctas = static_cast<int64_t>(p.n_rows) * (p.n4 + p.n3);
+  SR_REQUIRE(n_ctas < (1ll << 31), "sr_attn_fwd_bf16: too many CTAs");
+  dim3 grid(static_cast<unsigned>(n_ctas), 1, 1);
   switch (poly) {
+    case 2: return launch4<2>(grid, st, tq, tk, tv, tpk, tpv, p);
+#ifdef SR_DEBUG
     case 0: return launch4<0>(grid, st, tq, tk, tv, tpk, tpv, p);
     case 1: return launch4<1>(grid, st, tq, tk, tv, tpk, tpv, p);
-    case 2: return launch4<2>(grid, st, tq, tk, tv, tpk, tpv, p);
     case 3: return launch4<3>(grid, st, tq, tk, tv, tpk, tpv, p);
     case 4: return launch4<4>(grid, st, tq, tk, tv, tpk, tpv, p);
     case 8: return launch4<8>(grid, st, tq, tk, tv, tpk, tpv, p);
+#endif
   }
   return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16 (4-tile kernel): SR_ATTN_POLY must be 0..4 or 8 (got %d)", poly);
 }
 
 }  // namespace sr
+
+extern "C" int sr_attn_plan(int64_t q_len, int32_t num_heads, int32_t batch, int32_t num_sms, int32_t* n4, int32_t* n3) {
+  using namespace sr;
+  SR_REQUIRE(q_len > 0 && num_heads > 0 && batch > 0 && num_sms > 0 && n4 && n3, "sr_attn_plan: bad argument");
+  int a = 0, b = 0;
+  choose_mix(static_cast<int>((q_len + 127) / 128), num_heads * batch, num_sms, 0, &a, &b);
+  *n4 = a;
+  *n3 = b;
+  return SR_OK;
+}

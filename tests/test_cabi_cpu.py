@@ -56,3 +56,23 @@ def test_no_cpu_fallback():
     assert b"no CPU fallback" in lib.sr_last_error()
     with pytest.raises(RuntimeError):
         ops.layernorm(torch.zeros(4, 64), None, None, 1e-5, torch.zeros(4, 64))
+
+
+def test_attention_work_decomposition_plan():
+    """sr_attn_plan (host only): four-tile CTAs first, three-tile CTAs in the tail wave.  16-anchor global shape on 148 SMs:
+    172 query tiles per head = 37 x 4 + 8 x 3 (592 heavy CTAs = exactly 4 waves) — and every plan covers all the tiles."""
+    import ctypes as C
+    from sailrecon_b200 import _lib
+    lib = _lib.load()
+
+    def plan(q_len, heads, batch, sms=148):
+        n4, n3 = C.c_int32(), C.c_int32()
+        assert lib.sr_attn_plan(q_len, heads, batch, sms, C.byref(n4), C.byref(n3)) == 0
+        return n4.value, n3.value
+
+    assert plan(16 * 1374, 16, 1) == (37, 8)
+    for q_len, heads, batch in ((1374, 16, 32), (1374, 16, 16), (1, 16, 1), (128, 2, 3), (512 * 1374, 16, 1), (70, 16, 3), (600, 16, 1)):
+        n4, n3 = plan(q_len, heads, batch)
+        t = (q_len + 127) // 128
+        assert n4 >= 0 and n3 >= 0 and n4 + n3 >= 1
+        assert 4 * n4 + 3 * n3 >= t and (4 * n4 + 3 * (n3 - 1) < t if n3 else 4 * (n4 - 1) < t), (q_len, n4, n3)
