@@ -165,7 +165,13 @@ class Aggregator(nn.Module):
     # ---------------------------------------------------------------------------------------------- forward
     def forward(self, images: torch.Tensor, no_reloc_list: list, reloc_list: list,
                 fix_rank: Union[int, None] = None) -> Tuple[dict, int, torch.Tensor]:
-        engine.forbid_autograd(self, "Aggregator.forward")
+        if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            # training (train_imc.py:361-381): one autograd node over the block stacks — forward keeps what the backward
+            # kernels read, loss.backward() reaches them (sailrecon_b200.train.AggregatorFunction)
+            from .. import train
+            if self.kv_cache:
+                raise NotImplementedError("sailrecon_b200: the differentiated forward is the kv_cache=False path (sail_recon.py:70-78)")
+            return train.aggregator_forward_autograd(self, images, no_reloc_list, reloc_list, fix_rank)
         B, S, C_in, H, W = images.shape
         Na, Nq = len(no_reloc_list), len(reloc_list)
         self.num_recon = Na

@@ -435,12 +435,14 @@ def layer_backward_saved(fblk: nn.Module, gblk: nn.Module, rblk: nn.Module, save
     return block_backward(fblk, sf, d_all, grads)
 
 
-def stack_forward(agg: nn.Module, X: torch.Tensor, ctx: LayerCtx, draw_scene, keep_activations: bool = False) -> list:
+def stack_forward(agg: nn.Module, X: torch.Tensor, ctx: LayerCtx, draw_scene, keep_activations: bool = False,
+                  on_layer=None) -> list:
     """The 24 aggregator layers (aggregator.py:339-423) on X.  draw_scene() -> (idx int32 [Na P'], RowPositions) is called
     once per layer, in order (the per-layer scene-token draw, :351-360).
     keep_activations False: the reference's schedule — inference kernels in place on X, per layer only what
     torch.utils.checkpoint keeps (the block inputs: layer input and the state after the frame block, :654-657,726-729,
-    758-761); the backward re-runs each block.  True: every block runs its saving forward once and nothing is re-run."""
+    758-761); the backward re-runs each block.  True: every block runs its saving forward once and nothing is re-run.
+    on_layer(i, X_mid, X_out) sees the two states the reference collects per layer (read them before the next layer runs)."""
     ck = []
     for i in range(agg.depth):
         idx, spos = draw_scene()
@@ -448,10 +450,13 @@ def stack_forward(agg: nn.Module, X: torch.Tensor, ctx: LayerCtx, draw_scene, ke
         if keep_activations:
             X, saved = layer_forward_saving(*blocks, X, ctx, idx, spos)
             ck.append((saved,))
+            X_mid = saved[4]
         else:
             X_in = X.clone()
             X_mid = layer_forward(*blocks, X, ctx, idx, spos)
             ck.append((X_in, X_mid, idx, spos))
+        if on_layer is not None:
+            on_layer(i, X_mid, X)            # state after the frame block / after the whole layer (aggregator.py:403-423)
     return ck
 
 
@@ -532,3 +537,143 @@ def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: Laye
         w.wait()
     (optimizer_step or state.adam_step)(grad_scale=1.0 / world)
     return dX0
+
+
+# ------------------------------------------------------------------------------------------------ autograd bridge
+class AggregatorFunction(torch.autograd.Function):
+    """Aggregator.forward as ONE autograd node, so the reference's training loop runs unchanged through the overlay
+    (train_imc.py:361-381: `predictions = model(...)` under autocast(bf16), `scaler.scale(loss).backward()`, DDP hooks,
+    `scaler.step(optimizer)`): forward = patch embed + stack_forward on the C-ABI kernels, backward = stack_backward.
+    Differentiated: the 3 x depth aggregator blocks and the four special-token parameters (the gradient of the token rows
+    the stack starts from).  NOT differentiated here: the patch embed (DINOv2 / conv) — its parameters receive no gradient
+     — and the images.  Inputs after the six non-tensor arguments are exactly the tensors that receive
+    gradients, in `AggregatorFunction.parameters_of(agg)` order."""
+
+    @staticmethod
+    def parameters_of(agg: nn.Module) -> List[nn.Parameter]:
+        ps = [agg.camera_token, agg.register_token, agg.camera_token_reloc, agg.register_token_reloc]
+        for i in range(agg.depth):
+            for blk in (agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i]):
+                ps.extend(blk.parameters())
+        return ps
+
+    @staticmethod
+    def forward(ctx, agg, images, no_reloc_list, reloc_list, fix_rank, keep_activations, *params):
+        B, S, C_in, H, W = images.shape
+        Na, Nq = len(no_reloc_list), len(reloc_list)
+        if C_in != 3:
+            raise ValueError(f"Expected 3 input channels, got {C_in}")
+        if B != 1 or Na == 0 or sorted(list(no_reloc_list) + list(reloc_list)) != list(range(S)):
+            raise NotImplementedError("sailrecon_b200: training forward needs B = 1, at least one anchor and disjoint lists "
+                                      "covering range(S)")
+        if engine.compute_mode() != "bf16":
+            raise NotImplementedError("sailrecon_b200: the differentiated path runs under torch.autocast(bfloat16), as "
+                                      "train/train_imc.py:363 does")
+        engine.require_cuda_f32(images, "images")
+        dev = images.device
+        C = agg.camera_token.shape[-1]
+        psi = agg.patch_start_idx
+        h, w = H // agg.patch_size, W // agg.patch_size
+        hw, P = h * w, psi + h * w
+        agg.num_recon = Na
+        agg.rank = agg._draw_rank(fix_rank, hw, clamp=True)
+        l_prime = min(agg.rank, hw)
+        order = list(no_reloc_list) + list(reloc_list)
+        imgs = images[0] if order == list(range(S)) else images[0][torch.tensor(order, device=dev)]
+        T = S * P
+        X0 = torch.empty(T, C, dtype=torch.float32, device=dev)
+        agg._embed(imgs.contiguous(), "bf16", X0, S, P, C)
+        X0.view(S, P, C)[:, :psi] = agg._special_rows(order, set(reloc_list), False)
+        rows_pos, frame_pos_cpu = agg._positions(S, h, w, dev)
+        lctx = LayerCtx(Na, Nq, P, rows_pos)
+
+        def draw_scene():
+            idx, spos, drawn = agg._scene_rows(Na, P, hw, l_prime, frame_pos_cpu, dev)
+            agg.last_scene_indices.append(drawn)
+            return idx, engine.RowPositions(spos, rows_pos.max_pos)
+
+        if keep_activations is None:
+            free, _ = torch.cuda.mem_get_info(dev)
+            free += torch.cuda.memory_reserved(dev) - torch.cuda.memory_allocated(dev)
+            keep_activations = choose_keep_activations(lctx, agg.depth, C, Na * (psi + l_prime) if Nq else 0, free)
+        outs, cams = {}, {}
+
+        def on_layer(i, X_mid, X_out):
+            if i in agg.intermediate_layer_idx and Nq > 0:                               # aggregator.py:403-413
+                o = torch.empty(1, Nq, P, 2 * C, dtype=torch.float32, device=dev)
+                ops.copy_cols(X_mid[Na * P:], o.view(Nq * P, 2 * C), 0)
+                ops.copy_cols(X_out[Na * P:], o.view(Nq * P, 2 * C), C)
+                outs[i] = o
+            if i == agg.depth - 1:                                                       # :414-423
+                cams[0] = torch.cat([X_mid.view(S, P, C)[:Na, 0], X_out.view(S, P, C)[:Na, 0]], dim=-1)[None].clone()
+
+        agg.last_scene_indices = []
+        ck = stack_forward(agg, X0 if keep_activations else X0.clone(), lctx, draw_scene, keep_activations, on_layer)
+        ctx.agg, ctx.ck, ctx.lctx, ctx.order = agg, ck, lctx, order
+        ctx.geom = (S, P, C, Na, Nq, psi)
+        ctx.layers = sorted(outs)
+        ctx.params = params
+        ctx.reloc = set(reloc_list)
+        return tuple(outs[i] for i in ctx.layers) + (cams[0],)
+
+    @staticmethod
+    def backward(ctx, *gouts):
+        agg, lctx = ctx.agg, ctx.lctx
+        S, P, C, Na, Nq, psi = ctx.geom
+        T = S * P
+        dev = ctx.params[0].device
+        d_out = {}
+        for i, g in zip(ctx.layers, gouts[:-1]):
+            if g is None:
+                continue
+            g2 = g.reshape(Nq * P, 2 * C).float()
+            d_mid = torch.zeros(T, C, dtype=torch.float32, device=dev)
+            d_post = torch.zeros(T, C, dtype=torch.float32, device=dev)
+            d_mid[Na * P:] = g2[:, :C]
+            d_post[Na * P:] = g2[:, C:]
+            d_out[i] = (d_mid, d_post)
+        g_cam = gouts[-1]
+        if g_cam is not None:
+            last = agg.depth - 1
+            if last not in d_out:
+                d_out[last] = (torch.zeros(T, C, dtype=torch.float32, device=dev), torch.zeros(T, C, dtype=torch.float32, device=dev))
+            d_out[last][0].view(S, P, C)[:Na, 0] += g_cam[0, :, :C].float()
+            d_out[last][1].view(S, P, C)[:Na, 0] += g_cam[0, :, C:].float()
+        grads: Dict[nn.Parameter, torch.Tensor] = {}
+        dX0 = stack_backward(agg, ctx.ck, d_out, lctx, grads)
+        ctx.ck = None
+        # gradient of the special-token rows (aggregator.py:287-299): frame 0 -> slot 0, other anchors -> slot 1, queries -> *_reloc
+        d_sp = dX0.view(S, P, C)[:, :psi]
+        g_cam_tok = torch.zeros_like(agg.camera_token)
+        g_reg_tok = torch.zeros_like(agg.register_token)
+        g_cam_rel = torch.zeros_like(agg.camera_token_reloc)
+        g_reg_rel = torch.zeros_like(agg.register_token_reloc)
+        for pos_in_order, f in enumerate(ctx.order):
+            row = d_sp[pos_in_order]
+            if f in ctx.reloc:
+                g_cam_rel[0, 0] += row[:1]
+                g_reg_rel[0, 0] += row[1:]
+            else:
+                slot = 0 if f == 0 else 1
+                g_cam_tok[0, slot] += row[:1]
+                g_reg_tok[0, slot] += row[1:]
+        grads[agg.camera_token], grads[agg.register_token] = g_cam_tok, g_reg_tok
+        grads[agg.camera_token_reloc], grads[agg.register_token_reloc] = g_cam_rel, g_reg_rel
+        by_id = {id(p): g for p, g in grads.items()}
+        plist = AggregatorFunction.parameters_of(agg)
+        return (None,) * 6 + tuple(by_id.get(id(p)) for p in plist)
+
+
+def aggregator_forward_autograd(agg: nn.Module, images: torch.Tensor, no_reloc_list, reloc_list, fix_rank=None,
+                                keep_activations: Optional[bool] = None):
+    """Aggregator.forward (aggregator.py:242-433) with a grad_fn: what Aggregator.forward dispatches to in train() mode
+    with autograd enabled.  Returns (output_dict, patch_start_idx, cam_token_last_layer) like the inference forward."""
+    params = AggregatorFunction.parameters_of(agg)
+    res = AggregatorFunction.apply(agg, images, list(no_reloc_list), list(reloc_list), fix_rank, keep_activations, *params)
+    layers = sorted(i for i in agg.intermediate_layer_idx) if len(reloc_list) else []
+    output_dict = dict(zip(layers, res[:-1]))
+    assert (agg.depth - 1 in output_dict) or len(reloc_list) == 0, \
+        f"Please make sure the last layer ({agg.depth - 1}) is in the output_dict: {output_dict.keys()}"
+    if len(reloc_list):
+        output_dict[-1] = output_dict[agg.depth - 1]
+    return output_dict, agg.patch_start_idx, res[-1]

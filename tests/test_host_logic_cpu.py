@@ -93,7 +93,11 @@ def test_inference_forwards_refuse_training_mode_with_autograd():
     agg = Aggregator(img_size=56, embed_dim=128, depth=1, num_heads=2, patch_embed="conv", intermediate_layer_idx=[0])
     head = CameraHead(dim_in=256, trunk_depth=1, num_heads=2)
     x = torch.zeros(1, 4, 128)
-    for call in (lambda: blk(x), lambda: att(x), lambda: agg(torch.zeros(1, 2, 3, 56, 56), [0], [1]),
+    # Aggregator.forward itself dispatches to the autograd bridge in train() mode (train.AggregatorFunction); without
+    # autocast(bfloat16) that path refuses loudly as well
+    with pytest.raises(NotImplementedError, match="autocast"):
+        agg(torch.zeros(1, 2, 3, 56, 56), [0], [1])
+    for call in (lambda: blk(x), lambda: att(x),
                  lambda: agg.forward_with_cache(torch.zeros(1, 1, 3, 56, 56)),
                  lambda: head({-1: torch.zeros(1, 1, 5, 256)}, torch.zeros(1, 1, 256))):
         with pytest.raises(RuntimeError, match="inference path"):

@@ -143,3 +143,51 @@ def test_stack_backward_matches_reference_autograd(keep):
     for n, e in errs.items():
         assert e < (4e-2 if ("q_norm" in n or "k_norm" in n) else 3e-2), (n, e)
     assert e_in32 < 3e-2 and max(errs32.values()) < 6e-2
+
+
+def test_autograd_bridge_runs_the_reference_training_calls():
+    """train_imc.py:361-381 through the module API: model.train(); under autocast(bf16) `out = aggregator(images, ...)` carries a
+    grad_fn (train.AggregatorFunction), `loss.backward()` fills .grad of every block parameter and of the special tokens —
+    compared with the reference's own .grad after the same calls — and torch.optim.Adam steps on them.  GradScaler-style
+    loss scaling (x 1024) must scale the gradients linearly."""
+    r_agg, o_agg = _pair()
+    images = torch.rand(1, NA + NQ, 3, SIZE, SIZE, generator=torch.Generator().manual_seed(8)).to(DEV)
+    P = (SIZE // 14) ** 2 + 5
+    gg = torch.Generator(device=DEV).manual_seed(9)
+    G = {i: torch.randn(1, NQ, P, 2 * C, device=DEV, generator=gg) for i in range(DEPTH)}
+    Gc = torch.randn(1, NA, 2 * C, device=DEV, generator=gg)
+    _, _, r_out, r_cam, r_grads = _reference_grads(r_agg, images, G, Gc, bf16=True)
+    o_agg.train()
+    o_agg.generator.manual_seed(1234)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out, psi, cam = o_agg(images, list(range(NA)), list(range(NA, NA + NQ)), fix_rank=300)
+    assert psi == 5 and set(out) == {0, 1, -1} and out[-1] is out[DEPTH - 1]
+    assert out[0].requires_grad and cam.requires_grad and out[0].grad_fn is not None
+    for i in range(DEPTH):
+        assert rel_l2(out[i].detach(), r_out[i].float()) < 2e-2
+    assert rel_l2(cam.detach(), r_cam.float()) < 2e-2
+    loss = (cam * Gc).sum()
+    for i in range(DEPTH):
+        loss = loss + (out[i] * G[i]).sum()
+    (1024.0 * loss).backward()
+    named = dict(o_agg.named_parameters())
+    checked = 0
+    for n, p in named.items():
+        top = n.split(".")[0]
+        if top == "patch_embed":
+            assert p.grad is None                      # not differentiated by the bridge (DESIGN.md §8)
+            continue
+        assert p.grad is not None, n
+        e = rel_l2(p.grad / 1024.0, r_grads[n])
+        assert e < (4e-2 if ("q_norm" in n or "k_norm" in n) else 3e-2), (n, e)
+        checked += 1
+    assert checked == 4 + 3 * DEPTH * 18
+    before = named["frame_blocks.0.attn.qkv.weight"].detach().clone()
+    torch.optim.Adam([p for p in o_agg.parameters() if p.grad is not None], lr=1e-4).step()
+    assert not torch.equal(named["frame_blocks.0.attn.qkv.weight"].detach(), before)
+    # the cached bf16 weight copies follow the update (engine._cached is keyed on the parameter version)
+    o_agg.eval()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        o_agg.generator.manual_seed(1234)
+        out2, _, _ = o_agg(images, list(range(NA)), list(range(NA, NA + NQ)), fix_rank=300)
+    assert rel_l2(out2[-1], out[-1].detach()) > 1e-6
