@@ -75,6 +75,9 @@ typedef struct sr_epilogue {
   const float* rope_sin;
   int32_t rope_max_pos;
   const int32_t* pos;    /* int32 [M, 2] (y, x) positions (rope.py:25-66 + aggregator.py:319-328)           */
+  /* LS_RESIDUAL only: 1 = out = resid + gamma * (acc + bias) WITHOUT the bf16 rounding of the Linear output that
+   * autocast performs (0, default) — the fp32 accumulate of the split-precision convolution passes (dpt.cu).   */
+  int32_t exact_residual;
 } sr_epilogue_t;
 
 /* bf16 tensor-core path (tcgen05.mma, TMA-fed): A bf16 [M,K] row stride lda, W bf16 [N,K] row stride ldw.
@@ -260,6 +263,28 @@ int sr_unproject_depth(const float* depth, const float* extrinsics, const float*
  * are usually column blocks of the [rows, 3C] modulation tensor).                                              */
 int sr_modulate_f32(const float* x, int64_t ldx, const float* shift, int64_t lds, const float* scale, int64_t ldc,
                     float* out, int64_t ldo, int64_t rows, int64_t C, void* stream);
+
+/* ---- DPT dense heads (heads/dpt_head.py:22-344), channels-last fp32 row matrices -------------
+ * Convolutions run on sr_gemm_bf16 with split-precision operands (see csrc/dpt.cu): this writes, for x fp32 [N, H, W, C]
+ * (pixel stride ldx), the im2col rows out bf16 [N*Ho*Wo, 2*k*k*C] = [hi | lo], hi = bf16(x), lo = bf16(x - hi), column
+ * (ky*k + kx)*C + c; k = 1 (stride 1, pad 0: a plain split) or 3; relu = 1 applies max(x, 0) first.                */
+int sr_im2col_split_bf16(const float* x, int64_t ldx, void* out, int64_t N, int64_t H, int64_t W, int64_t C, int32_t k,
+                         int32_t stride, int32_t pad, int32_t relu, void* stream);
+/* F.interpolate(mode="bilinear", align_corners=True) (custom_interpolate, dpt_head.py:565-594), x [N,Hi,Wi,C] -> [N,Ho,Wo,C] */
+int sr_bilinear_nhwc_f32(const float* x, float* out, int64_t N, int64_t Hi, int64_t Wi, int64_t Ho, int64_t Wo, int64_t C,
+                         void* stream);
+/* ConvTranspose2d(kernel = stride = k) epilogue (dpt_head.py:85-102): g [N*H*W, k*k*C] (GEMM output, columns (ky, kx, c))
+ * -> out [N, H*k, W*k, C] + bias[c] (NULL = none)                                                                  */
+int sr_pixel_shuffle_f32(const float* g, const float* bias, float* out, int64_t N, int64_t H, int64_t W, int64_t C, int32_t k,
+                         void* stream);
+/* out[i] = a[i] + alpha * b[i mod period]: skip additions (period = n) and the broadcast positional embedding       */
+int sr_add_bcast_f32(const float* a, const float* b, float* out, int64_t n, int64_t period, float alpha, void* stream);
+/* create_uv_grid + position_grid_to_embed (heads/utils.py:11-123) evaluated in double: out fp32 [H, W, C]            */
+int sr_uv_posembed_table(float* out, int64_t H, int64_t W, int64_t C, double aspect_ratio, double omega0, void* stream);
+/* ReLU -> 1x1 conv (hid -> out_dim) -> activate_head (dpt_head.py:150-160, head_act.py:63-114): h [px, ldh] -> pred
+ * [px, out_dim - 1], conf [px].  act: 0 inv_log, 1 exp, 2 linear, 3 relu, 4 sigmoid; conf_act: 0 expp1, 1 expp0, 2 sigmoid */
+int sr_dpt_out_head_f32(const float* h, int64_t ldh, const float* w, const float* bias, float* pred, float* conf, int64_t px,
+                        int32_t hid, int32_t out_dim, int32_t act, int32_t conf_act, void* stream);
 
 #ifdef __cplusplus
 }

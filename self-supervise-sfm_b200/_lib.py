@@ -26,6 +26,7 @@ class SrEpilogue(C.Structure):
         ("qkv_dim", _i64), ("col_offset", _i64), ("head_dim", _i32), ("qk_norm", _i32),
         ("qn_w", _vp), ("qn_b", _vp), ("kn_w", _vp), ("kn_b", _vp), ("qk_eps", _f32),
         ("rope", _i32), ("rope_cos", _vp), ("rope_sin", _vp), ("rope_max_pos", _i32), ("pos", _vp),
+        ("exact_residual", _i32),
     ]
 
 
@@ -102,6 +103,12 @@ SIGNATURES = {
     "sr_pose_update": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
     "sr_pose_to_extri_intri": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
     "sr_unproject_depth": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp]),
+    "sr_im2col_split_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "sr_bilinear_nhwc_f32": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _vp]),
+    "sr_pixel_shuffle_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp]),
+    "sr_add_bcast_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _f32, _vp]),
+    "sr_uv_posembed_table": (C.c_int, [_vp, _i64, _i64, _i64, C.c_double, C.c_double, _vp]),
+    "sr_dpt_out_head_f32": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
     "sr_modulate_f32": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _vp]),
 }
 

@@ -88,10 +88,11 @@ __device__ __forceinline__ void epi_store32(const GemmParams& p, int row, int co
       const float4 rr = resid_regs[i >> 2];                  // loaded before the accumulator was ready (see kernel)
       float4 g = e.gamma ? __ldg(reinterpret_cast<const float4*>(e.gamma + col + i)) : make_float4(1.f, 1.f, 1.f, 1.f);
       float4 y;
-      y.x = rr.x + g.x * bf16_round(x[i + 0]);
-      y.y = rr.y + g.y * bf16_round(x[i + 1]);
-      y.z = rr.z + g.z * bf16_round(x[i + 2]);
-      y.w = rr.w + g.w * bf16_round(x[i + 3]);
+      const bool ex = e.exact_residual != 0;               // fp32 accumulate across split-precision passes (dpt.cu)
+      y.x = rr.x + g.x * (ex ? x[i + 0] : bf16_round(x[i + 0]));
+      y.y = rr.y + g.y * (ex ? x[i + 1] : bf16_round(x[i + 1]));
+      y.z = rr.z + g.z * (ex ? x[i + 2] : bf16_round(x[i + 2]));
+      y.w = rr.w + g.w * (ex ? x[i + 3] : bf16_round(x[i + 3]));
       *reinterpret_cast<float4*>(o + i) = y;
     }
     return;
@@ -411,10 +412,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
               if (r < p.M) {
                 const float4 rr = resid_regs[c * 8 + i];
                 float4 y;
-                y.x = rr.x + g4.x * bf16_round(a.x + b4.x);
-                y.y = rr.y + g4.y * bf16_round(a.y + b4.y);
-                y.z = rr.z + g4.z * bf16_round(a.z + b4.z);
-                y.w = rr.w + g4.w * bf16_round(a.w + b4.w);
+                const bool ex = e.exact_residual != 0;     // fp32 accumulate across split-precision passes (dpt.cu)
+                y.x = rr.x + g4.x * (ex ? a.x + b4.x : bf16_round(a.x + b4.x));
+                y.y = rr.y + g4.y * (ex ? a.y + b4.y : bf16_round(a.y + b4.y));
+                y.z = rr.z + g4.z * (ex ? a.z + b4.z : bf16_round(a.z + b4.z));
+                y.w = rr.w + g4.w * (ex ? a.w + b4.w : bf16_round(a.w + b4.w));
                 *reinterpret_cast<float4*>(reinterpret_cast<float*>(e.out) + static_cast<int64_t>(r) * e.ldo + col) = y;
               }
             }

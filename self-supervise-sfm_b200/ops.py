@@ -563,6 +563,8 @@ def pose_to_extri_intri(pose: torch.Tensor, image_hw=None, build_intrinsics: boo
             raise ValueError("sailrecon_b200: image_size_hw is required to build the intrinsics")
         H, W = int(image_hw[0]), int(image_hw[1])
         intr = torch.empty(*p.shape[:-1], 3, 3, dtype=torch.float32, device=p.device)
+    if n == 0:
+        return ext, intr
     _lib.check(_lib.load().sr_pose_to_extri_intri(p.data_ptr(), ext.data_ptr(), _ptr(intr), n, H, W, _stream()),
                "pose_to_extri_intri")
     return ext, intr

@@ -39,6 +39,13 @@ def test_reference_sailrecon_two_phase_and_one_pass_through_overlay(tmp_path):
     ref = _run("ref", str(tmp_path / "ref.npz"), 3, 2, 518)
     ours = _run("overlay", str(tmp_path / "ours.npz"), 3, 2, 518)
     assert set(ref) == set(ours)
+    # FoV = relu(.) is exactly 0 for some frames at random init: the focal length is then +inf in BOTH arms (pose_enc.py:123-124)
+    for k in ref:
+        if k.endswith("intrinsic"):
+            bad = ~np.isfinite(ref[k])
+            assert np.array_equal(bad, ~np.isfinite(ours[k])), k
+            ref[k] = np.where(bad, 0.0, ref[k])
+            ours[k] = np.where(bad, 0.0, ours[k])
     errs = {k: _rel(ours[k], ref[k]) for k in ref}
     print("overlay parity", {k: f"{v:.2e}" for k, v in sorted(errs.items())})
     for k, e in errs.items():
