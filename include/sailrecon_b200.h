@@ -277,8 +277,10 @@ int sr_bilinear_nhwc_f32(const float* x, float* out, int64_t N, int64_t Hi, int6
  * -> out [N, H*k, W*k, C] + bias[c] (NULL = none)                                                                  */
 int sr_pixel_shuffle_f32(const float* g, const float* bias, float* out, int64_t N, int64_t H, int64_t W, int64_t C, int32_t k,
                          void* stream);
-/* out[i] = a[i] + alpha * b[i mod period]: skip additions (period = n) and the broadcast positional embedding       */
-int sr_add_bcast_f32(const float* a, const float* b, float* out, int64_t n, int64_t period, float alpha, void* stream);
+/* out[i] = act(a[i] + alpha * b[i mod period]): skip additions (period = n) and the broadcast positional embedding;
+ * b may be NULL; relu_out = 1: act = ReLU (the in-place activation of the ResidualConvUnit, dpt_head.py:357,461)     */
+int sr_add_bcast_f32(const float* a, const float* b, float* out, int64_t n, int64_t period, float alpha, int32_t relu_out,
+                     void* stream);
 /* create_uv_grid + position_grid_to_embed (heads/utils.py:11-123) evaluated in double: out fp32 [H, W, C]            */
 int sr_uv_posembed_table(float* out, int64_t H, int64_t W, int64_t C, double aspect_ratio, double omega0, void* stream);
 /* ReLU -> 1x1 conv (hid -> out_dim) -> activate_head (dpt_head.py:150-160, head_act.py:63-114): h [px, ldh] -> pred

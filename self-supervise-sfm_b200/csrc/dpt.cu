@@ -128,15 +128,20 @@ pixel_shuffle_kernel(const float* __restrict__ g, const float* __restrict__ bias
   *reinterpret_cast<float4*>(out + o) = v;
 }
 
-// out = a + alpha * b[i mod period]  (period = n: plain add; period = H*W*C: the broadcast positional embedding)
+// out = act(a + alpha * b[i mod period])  (period = n: plain add; period = H*W*C: the broadcast positional embedding; b may be
+// NULL; act = ReLU when relu_out: the ResidualConvUnit's in-place nn.ReLU(inplace=True), dpt_head.py:357,461)
 __global__ void __launch_bounds__(256)
 add_bcast_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, int64_t n4, int64_t period4,
-                 float alpha) {
+                 float alpha, int relu_out) {
   const int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
   if (idx >= n4) return;
-  const float4 x = __ldg(reinterpret_cast<const float4*>(a) + idx);
-  const float4 y = __ldg(reinterpret_cast<const float4*>(b) + (idx % period4));
-  reinterpret_cast<float4*>(out)[idx] = make_float4(x.x + alpha * y.x, x.y + alpha * y.y, x.z + alpha * y.z, x.w + alpha * y.w);
+  float4 x = __ldg(reinterpret_cast<const float4*>(a) + idx);
+  if (b != nullptr) {
+    const float4 y = __ldg(reinterpret_cast<const float4*>(b) + (idx % period4));
+    x = make_float4(x.x + alpha * y.x, x.y + alpha * y.y, x.z + alpha * y.z, x.w + alpha * y.w);
+  }
+  if (relu_out) x = make_float4(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f), fmaxf(x.z, 0.f), fmaxf(x.w, 0.f));
+  reinterpret_cast<float4*>(out)[idx] = x;
 }
 
 // create_uv_grid + position_grid_to_embed (heads/utils.py:11-123): table [H, W, C] fp32, evaluated in double like the
@@ -262,15 +267,16 @@ extern "C" int sr_pixel_shuffle_f32(const float* g, const float* bias, float* ou
   return SR_OK;
 }
 
-extern "C" int sr_add_bcast_f32(const float* a, const float* b, float* out, int64_t n, int64_t period, float alpha, void* stream) {
+extern "C" int sr_add_bcast_f32(const float* a, const float* b, float* out, int64_t n, int64_t period, float alpha, int32_t relu_out,
+                                void* stream) {
   using namespace sr;
   if (int rc = require_sm100()) return rc;
-  SR_REQUIRE(a && b && out && n >= 0 && period > 0 && n % 4 == 0 && period % 4 == 0, "sr_add_bcast_f32: n and period must be multiples of 4");
+  SR_REQUIRE(a && out && n >= 0 && period > 0 && n % 4 == 0 && period % 4 == 0, "sr_add_bcast_f32: n and period must be multiples of 4");
   SR_REQUIRE(((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
              "sr_add_bcast_f32: 16-byte alignment");
   if (n == 0) return SR_OK;
   SR_REQUIRE((n / 4 + 255) / 256 < (1ll << 31), "sr_add_bcast_f32: too many elements");
-  add_bcast_kernel<<<blocks_for(n / 4), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, b, out, n / 4, period / 4, alpha);
+  add_bcast_kernel<<<blocks_for(n / 4), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a, b, out, n / 4, period / 4, alpha, relu_out);
   ++g_launch_count;
   SR_CHECK_CUDA(cudaGetLastError());
   return SR_OK;

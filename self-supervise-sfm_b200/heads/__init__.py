@@ -1,3 +1,4 @@
 from .camera_head import CameraHead
+from .dpt_head import DPTHead
 
-__all__ = ["CameraHead"]
+__all__ = ["CameraHead", "DPTHead"]

@@ -149,7 +149,7 @@ def _fill_qkv(e: SrEpilogue, qkv: "QkvEpilogue", M: int) -> list:
 
 def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor, kind: int = SR_EPI_BIAS,
          gamma: Optional[torch.Tensor] = None, resid: Optional[torch.Tensor] = None,
-         qkv: Optional[QkvEpilogue] = None) -> torch.Tensor:
+         qkv: Optional[QkvEpilogue] = None, exact: bool = False) -> torch.Tensor:
     """out = epilogue(a @ w.T + bias).  a/w both bf16 -> tcgen05 path; both fp32 -> SIMT fp32 path."""
     if a.dtype != w.dtype or a.dtype not in (torch.bfloat16, torch.float32):
         raise TypeError(f"sailrecon_b200: gemm operands must both be bf16 or both fp32, got {a.dtype} / {w.dtype}")
@@ -173,6 +173,7 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: to
         if resid.shape != (M, N):
             raise ValueError("sailrecon_b200: residual shape mismatch")
         e.resid, e.ldr = resid.data_ptr(), resid.stride(0)
+        e.exact_residual = int(exact)
     keep = []
     if kind == SR_EPI_QKV:
         if qkv is None:
@@ -597,3 +598,105 @@ def modulate(x: torch.Tensor, shift: torch.Tensor, scale: torch.Tensor) -> torch
     _lib.check(_lib.load().sr_modulate_f32(x2.data_ptr(), x2.stride(0), s2.data_ptr(), s2.stride(0), c2.data_ptr(), c2.stride(0),
                                            out.data_ptr(), out.stride(0), x2.shape[0], C_, _stream()), "modulate")
     return out.view(x.shape)
+
+
+# ------------------------------------------------------------------------------------------------ DPT dense heads (N1)
+def im2col_split(x: torch.Tensor, k: int, stride: int = 1, pad: int = 0, relu: bool = False,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x fp32 channels-last [N, H, W, C] -> bf16 rows [N*Ho*Wo, 2*k*k*C] = [hi | lo] (csrc/dpt.cu)."""
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.stride(3) == 1 and x.stride(2) >= x.shape[3]
+            and x.stride(1) == x.shape[2] * x.stride(2) and x.stride(0) == x.shape[1] * x.stride(1)):
+        raise ValueError("sailrecon_b200: im2col_split needs a dense channels-last fp32 CUDA tensor [N, H, W, C]")
+    N, H, W, Cc = x.shape
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    rows, cols = N * Ho * Wo, 2 * k * k * Cc
+    if out is None:
+        out = torch.empty(rows, cols, dtype=torch.bfloat16, device=x.device)
+    elif out.shape != (rows, cols) or out.dtype != torch.bfloat16 or not out.is_contiguous():
+        raise ValueError("sailrecon_b200: im2col_split out must be contiguous bf16 [N*Ho*Wo, 2*k*k*C]")
+    t = _Timed("im2col", 0.0, rows * cols * 2 + x.numel() * 4)
+    _lib.check(_lib.load().sr_im2col_split_bf16(x.data_ptr(), x.stride(2), out.data_ptr(), N, H, W, Cc, k, stride, pad, int(relu),
+                                                _stream()), "im2col_split")
+    t.done()
+    return out
+
+
+def gemm_split(a2: torch.Tensor, w_hh: torch.Tensor, w_lo: torch.Tensor, bias: Optional[torch.Tensor], out: torch.Tensor,
+               resid: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32-accurate out = A W^T (+ bias) (+ resid) on the bf16 tensor-core GEMM: a2 = [A_hi | A_lo] (im2col_split),
+    w_hh = [W_hi | W_hi], w_lo = W_lo (engine.weight_split).  Two launches: K' = 2K, then the exact accumulate of A_hi W_lo^T."""
+    K = w_lo.shape[1]
+    if resid is None:
+        gemm(a2, w_hh, bias, out, kind=SR_EPI_BIAS)
+    else:
+        gemm(a2, w_hh, bias, out, kind=SR_EPI_LS_RESIDUAL, resid=resid, exact=True)
+    gemm(a2[:, :K], w_lo, None, out, kind=SR_EPI_LS_RESIDUAL, resid=out, exact=True)
+    return out
+
+
+def bilinear_nhwc(x: torch.Tensor, Ho: int, Wo: int) -> torch.Tensor:
+    """F.interpolate(bilinear, align_corners=True) on channels-last fp32 [N, Hi, Wi, C]."""
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.is_contiguous()):
+        raise ValueError("sailrecon_b200: bilinear_nhwc needs a contiguous fp32 CUDA tensor [N, H, W, C]")
+    N, Hi, Wi, Cc = x.shape
+    out = torch.empty(N, Ho, Wo, Cc, dtype=torch.float32, device=x.device)
+    t = _Timed("bilinear", 0.0, (x.numel() + out.numel()) * 4)
+    _lib.check(_lib.load().sr_bilinear_nhwc_f32(x.data_ptr(), out.data_ptr(), N, Hi, Wi, Ho, Wo, Cc, _stream()), "bilinear_nhwc")
+    t.done()
+    return out
+
+
+def pixel_shuffle(g: torch.Tensor, bias: Optional[torch.Tensor], N: int, H: int, W: int, Cc: int, k: int) -> torch.Tensor:
+    """ConvTranspose2d(kernel = stride = k) epilogue: g fp32 [N*H*W, k*k*C] -> [N, H*k, W*k, C] + bias."""
+    _rows2d(g, torch.float32, "g")
+    if not g.is_contiguous() or g.shape != (N * H * W, k * k * Cc):
+        raise ValueError("sailrecon_b200: pixel_shuffle shape mismatch")
+    _vec(bias, Cc, "bias")
+    out = torch.empty(N, H * k, W * k, Cc, dtype=torch.float32, device=g.device)
+    _lib.check(_lib.load().sr_pixel_shuffle_f32(g.data_ptr(), _ptr(bias), out.data_ptr(), N, H, W, Cc, k, _stream()), "pixel_shuffle")
+    return out
+
+
+def add_bcast(a: torch.Tensor, b: Optional[torch.Tensor], alpha: float = 1.0, out: Optional[torch.Tensor] = None,
+              relu: bool = False) -> torch.Tensor:
+    """out = act(a + alpha * b), b broadcast over the leading elements of a (b.numel() divides a.numel()) or None;
+    act = ReLU when relu; fp32 contiguous."""
+    for t_, n_ in ((a, "a"), (b, "b")):
+        if t_ is not None and not (t_.is_cuda and t_.dtype == torch.float32 and t_.is_contiguous()):
+            raise ValueError(f"sailrecon_b200: add_bcast {n_} must be a contiguous fp32 CUDA tensor")
+    period = a.numel() if b is None else b.numel()
+    if period == 0 or a.numel() % period:
+        raise ValueError("sailrecon_b200: add_bcast period must divide the tensor")
+    if out is None:
+        out = torch.empty_like(a)
+    _lib.check(_lib.load().sr_add_bcast_f32(a.data_ptr(), _ptr(b), out.data_ptr(), a.numel(), period, float(alpha), int(relu),
+                                            _stream()), "add_bcast")
+    return out
+
+
+def uv_posembed_table(H: int, W: int, Cc: int, aspect_ratio: float, device, omega0: float = 100.0) -> torch.Tensor:
+    """create_uv_grid + position_grid_to_embed (heads/utils.py) -> fp32 [H, W, C]."""
+    out = torch.empty(H, W, Cc, dtype=torch.float32, device=device)
+    _lib.check(_lib.load().sr_uv_posembed_table(out.data_ptr(), H, W, Cc, float(aspect_ratio), float(omega0), _stream()),
+               "uv_posembed_table")
+    return out
+
+
+_DPT_ACT = {"inv_log": 0, "exp": 1, "linear": 2, "relu": 3, "sigmoid": 4}
+_DPT_CONF = {"expp1": 0, "expp0": 1, "sigmoid": 2}
+
+
+def dpt_out_head(h: torch.Tensor, hid: int, w: torch.Tensor, bias: torch.Tensor, activation: str, conf_activation: str):
+    """ReLU -> 1x1 conv -> activate_head: h fp32 [px, >= hid] -> (pred [px, out_dim - 1], conf [px])."""
+    _rows2d(h, torch.float32, "h")
+    if activation not in _DPT_ACT or conf_activation not in _DPT_CONF:
+        raise ValueError(f"Unknown activation: {activation} / {conf_activation}")
+    w2 = w.reshape(w.shape[0], -1).contiguous()
+    out_dim = w2.shape[0]
+    px = h.shape[0]
+    pred = torch.empty(px, out_dim - 1, dtype=torch.float32, device=h.device)
+    conf = torch.empty(px, dtype=torch.float32, device=h.device)
+    _lib.check(_lib.load().sr_dpt_out_head_f32(h.data_ptr(), h.stride(0), w2.data_ptr(), bias.data_ptr(), pred.data_ptr(),
+                                               conf.data_ptr(), px, hid, out_dim, _DPT_ACT[activation], _DPT_CONF[conf_activation],
+                                               _stream()), "dpt_out_head")
+    return pred, conf

@@ -5,6 +5,10 @@ train/demo_imc_forward.py, train/demo_imc.py) build its aggregator and camera he
     overlay.install()                      # before `import sailrecon.models.sail_recon`
     from sailrecon.models.sail_recon import SailRecon
 
+Replaced: sailrecon.models.aggregator, sailrecon.layers.{attention, block, rope, mlp, layer_scale, patch_embed,
+vision_transformer}, sailrecon.heads.camera_head, sailrecon.heads.dpt_head (dpt=True) and the two functions SailRecon binds
+from sailrecon.utils (pose_encoding_to_extri_intri, unproject_depth_map_to_point_map; geometry=True).  SailRecon itself —
+forward / tmp_forward / reloc / clear_cache — stays the reference's code.
 Only `sys.modules` aliases are installed; the reference tree is not modified.
 """
 from __future__ import annotations
@@ -15,12 +19,14 @@ import sys
 _LAYER_MODULES = ("attention", "block", "rope", "mlp", "layer_scale", "patch_embed", "vision_transformer")
 
 
-def install(geometry: bool = True) -> None:
+def install(geometry: bool = True, dpt: bool = True) -> None:
     if "sailrecon.models.sail_recon" in sys.modules:
         raise RuntimeError("sailrecon_b200.overlay.install() must run before sailrecon.models.sail_recon is imported")
     pkg = __name__.rsplit(".", 1)[0]
     sys.modules["sailrecon.models.aggregator"] = importlib.import_module(pkg + ".models.aggregator")
     sys.modules["sailrecon.heads.camera_head"] = importlib.import_module(pkg + ".heads.camera_head")
+    if dpt:                                          # N1: the two dense heads (sail_recon.py:46-66,129-136,246-252)
+        sys.modules["sailrecon.heads.dpt_head"] = importlib.import_module(pkg + ".heads.dpt_head")
     for name in _LAYER_MODULES:
         sys.modules[f"sailrecon.layers.{name}"] = importlib.import_module(f"{pkg}.layers.{name}")
     if geometry:
