@@ -226,6 +226,81 @@ static int launch_skinny(const GemmF32Params& p, cudaStream_t st) {
   return SR_OK;
 }
 
+// ---------------------------------------------------------------------------------------------- tiny-M path (M <= 8)
+// One to eight rows against the same big weights: the per-query-image camera head of the localisation workload
+// (localize.Localizer: the anchors' rows are cached, only the query rows run — M = 1 per image) and any M <= 8 call.
+// Pure weight streaming: a warp owns kTyCols rows of W, lanes split K in float4s (512 contiguous bytes per row and step,
+// kTyUnroll steps in flight), the M rows of A come through L1 (they are re-read by every warp and total <= 256 KB), partial
+// sums are reduced with shuffles.  Grid = N / (kTyCols * kTyWarps) CTAs = 256 ... 1024 for the camera-head shapes.
+constexpr int kTyCols = 2, kTyWarps = 4, kTyUnroll = 4;
+
+template <int EPI, int MR>
+__global__ void __launch_bounds__(kTyWarps * 32)
+gemm_f32_tiny_kernel(const GemmF32Params p) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n_base = (blockIdx.x * kTyWarps + warp) * kTyCols;
+  if (n_base >= p.N) return;
+  const float* wrow[kTyCols];
+#pragma unroll
+  for (int j = 0; j < kTyCols; ++j) wrow[j] = p.W + static_cast<int64_t>(min(n_base + j, p.N - 1)) * p.ldw;
+  float acc[kTyCols][MR];
+#pragma unroll
+  for (int j = 0; j < kTyCols; ++j)
+#pragma unroll
+    for (int m = 0; m < MR; ++m) acc[j][m] = 0.f;
+  const int k4 = p.K >> 2;                                   // float4 columns (K % 4 == 0 checked by the caller)
+  for (int c0 = lane; c0 < k4; c0 += 32 * kTyUnroll) {
+    float4 w[kTyUnroll][kTyCols];
+#pragma unroll
+    for (int u = 0; u < kTyUnroll; ++u) {
+      const int c = c0 + u * 32;
+#pragma unroll
+      for (int j = 0; j < kTyCols; ++j)
+        w[u][j] = c < k4 ? __ldcs(reinterpret_cast<const float4*>(wrow[j]) + c) : make_float4(0.f, 0.f, 0.f, 0.f);   // streamed once
+    }
+#pragma unroll
+    for (int u = 0; u < kTyUnroll; ++u) {
+      const int c = c0 + u * 32;
+      if (c >= k4) break;
+#pragma unroll
+      for (int m = 0; m < MR; ++m) {
+        const float4 a = m < p.M ? __ldg(reinterpret_cast<const float4*>(p.A + static_cast<int64_t>(m) * p.lda) + c)
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int j = 0; j < kTyCols; ++j)
+          acc[j][m] = fmaf(a.w, w[u][j].w, fmaf(a.z, w[u][j].z, fmaf(a.y, w[u][j].y, fmaf(a.x, w[u][j].x, acc[j][m]))));
+      }
+    }
+  }
+  const sr_epilogue_t& e = p.e;
+#pragma unroll
+  for (int j = 0; j < kTyCols; ++j)
+#pragma unroll
+    for (int m = 0; m < MR; ++m) {
+      const float s = warp_sum(acc[j][m]);
+      const int gn = n_base + j;
+      if (lane != 0 || gn >= p.N || m >= p.M) continue;
+      float y = s + (e.bias ? __ldg(e.bias + gn) : 0.f);
+      if (EPI == SR_EPI_BIAS_GELU) y = gelu_erf(y);
+      if (EPI == SR_EPI_BIAS_SILU) y = y / (1.f + expf(-y));
+      if (EPI == SR_EPI_LS_RESIDUAL) {
+        const float g = e.gamma ? __ldg(e.gamma + gn) : 1.f;
+        y = e.resid[static_cast<int64_t>(m) * e.ldr + gn] + g * y;
+      }
+      reinterpret_cast<float*>(e.out)[static_cast<int64_t>(m) * e.ldo + gn] = y;
+    }
+}
+
+template <int EPI>
+static int launch_tiny(const GemmF32Params& p, cudaStream_t st) {
+  const unsigned grid = static_cast<unsigned>((p.N + kTyCols * kTyWarps - 1) / (kTyCols * kTyWarps));
+  if (p.M == 1) gemm_f32_tiny_kernel<EPI, 1><<<grid, kTyWarps * 32, 0, st>>>(p);
+  else if (p.M == 2) gemm_f32_tiny_kernel<EPI, 2><<<grid, kTyWarps * 32, 0, st>>>(p);
+  else if (p.M <= 4) gemm_f32_tiny_kernel<EPI, 4><<<grid, kTyWarps * 32, 0, st>>>(p);
+  else gemm_f32_tiny_kernel<EPI, 8><<<grid, kTyWarps * 32, 0, st>>>(p);
+  return SR_OK;
+}
+
 // In-place q/k LayerNorm(d) + 2D RoPE on an fp32 [M, 3C] qkv buffer (check mode; attention.py:78-82).
 // One warp per (token, head, q|k); head_dim 64: lane holds features lane and lane+32.
 __global__ void __launch_bounds__(256)
@@ -285,7 +360,16 @@ extern "C" int sr_gemm_f32(const float* A, int64_t lda, const float* W, int64_t 
   // few rows against a big weight matrix (camera head): stream W once, warp-per-output-column
   const bool skinny = M <= 128 && K >= 256 && K % 4 == 0 && lda % 4 == 0 && ldw % 4 == 0 &&
                       ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(W)) & 15) == 0;
-  if (skinny) {
+  const bool tiny = skinny && M <= 8;
+  if (tiny) {
+    switch (kind) {
+      case SR_EPI_BIAS: launch_tiny<SR_EPI_BIAS>(p, st); break;
+      case SR_EPI_BIAS_GELU: launch_tiny<SR_EPI_BIAS_GELU>(p, st); break;
+      case SR_EPI_LS_RESIDUAL: launch_tiny<SR_EPI_LS_RESIDUAL>(p, st); break;
+      case SR_EPI_BIAS_SILU: launch_tiny<SR_EPI_BIAS_SILU>(p, st); break;
+      default: return fail(SR_ERR_SHAPE, "sr_gemm_f32: unknown epilogue kind %d", epi->kind);
+    }
+  } else if (skinny) {
     int rc = SR_OK;
     switch (kind) {
       case SR_EPI_BIAS: rc = launch_skinny<SR_EPI_BIAS>(p, st); break;

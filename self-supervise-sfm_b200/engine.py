@@ -293,9 +293,10 @@ def attention_rows(attn: nn.Module, qkv: torch.Tensor, o: torch.Tensor, calls: S
 
 
 def run_block(blk: nn.Module, x: torch.Tensor, calls: Sequence[AttnCall], rows_pos: Optional[RowPositions], mode: str,
-              tag: str = "", attn_zero: bool = False) -> torch.Tensor:
+              tag: str = "", attn_zero: bool = False, capture_kv: Optional[list] = None) -> torch.Tensor:
     """Block.forward (block.py:86-112) in place on the fp32 residual rows x [T, C].  `attn_zero` reproduces the
-    kv-cache priming pass where Attention returns zeros (attention.py:94-100)."""
+    kv-cache priming pass where Attention returns zeros (attention.py:94-100).  `capture_kv`: a list that receives a copy
+    of this call's (K, V) rows [T, C] (the anchors' keys / values the camera head caches for later query-only calls)."""
     T, C = x.shape
     dev = x.device
     act = torch.bfloat16 if mode == "bf16" else torch.float32
@@ -306,6 +307,8 @@ def run_block(blk: nn.Module, x: torch.Tensor, calls: Sequence[AttnCall], rows_p
         ops.layernorm(x, w1, b1, eps1, a)
         qkv = WS.get(tag + "qkv", (T, 3 * C), act, dev)
         qkv_rows(attn, a, qkv, mode, rows_pos)
+        if capture_kv is not None:
+            capture_kv.append((qkv[:, C:2 * C].clone(), qkv[:, 2 * C:].clone()))
         attention_rows(attn, qkv, a, calls)              # `a` is free again: reuse it for the attention output
     block_tail(blk, x, a, mode, tag, attn_zero)
     return x

@@ -60,7 +60,48 @@ class CameraHead(nn.Module):
         calls = engine.MaskStructure(Na, 1, pose_q.shape[1]).calls()
         return [p[None, Na:] for p in self._trunk_rows(x, calls, num_iterations)]          # query rows only, :118-121
 
-    def _trunk_rows(self, x: torch.Tensor, calls, num_iterations: int) -> list:
+    # ---------------------------------------------------------------------------------------------- cached anchors
+    def prime_anchors(self, cam_token_last_layer: torch.Tensor, num_iterations: int = 4) -> None:
+        """Localisation fast path (localize.Localizer).  build_lr_mask (camera_head.py:197-228) lets anchor tokens attend to
+        anchors only, so the anchors' rows of the trunk do not depend on the query frames: they are run ONCE here and the
+        keys / values they present to the queries are kept per (iteration, trunk block).  `forward_queries` then runs the
+        query rows alone (M = Nq rows instead of Na + Nq: at one query image per call the head becomes a stream of GEMVs
+        over its fp32 weights) and returns what `forward` returns."""
+        engine.forbid_autograd(self, "CameraHead.prime_anchors")
+        engine.require_cuda_f32(cam_token_last_layer, "cam_token_last_layer")
+        x_in = cam_token_last_layer[0].contiguous()
+        w, b, eps = engine.ln_params(self.token_norm)
+        x = torch.empty_like(x_in)
+        ops.layernorm(x_in, w, b, eps, x)
+        kv: list = []
+        self._trunk_rows(x, engine.full_segments(1, x.shape[0]), num_iterations, capture_kv=kv)
+        n = len(self.trunk)
+        self._anchor_kv = [kv[i * n:(i + 1) * n] for i in range(num_iterations)]
+        self._anchor_rows = x.shape[0]
+
+    def forward_queries(self, aggregated_tokens_list, num_iterations: int = 4) -> list:
+        """== forward(aggregated_tokens_list, cam_token_last_layer) for the anchors given to prime_anchors."""
+        engine.forbid_autograd(self, "CameraHead.forward_queries")
+        kv = getattr(self, "_anchor_kv", None)
+        if kv is None or len(kv) != num_iterations:
+            raise RuntimeError("sailrecon_b200: CameraHead.forward_queries needs prime_anchors(cam_token_last_layer, num_iterations) first")
+        pose_q = aggregated_tokens_list[-1][:, :, 0]
+        if pose_q.shape[0] != 1:
+            raise NotImplementedError("sailrecon_b200: batch size 1")
+        engine.require_cuda_f32(pose_q, "aggregated tokens")
+        x_in = pose_q[0].contiguous()
+        Nq, Na = x_in.shape[0], self._anchor_rows
+        w, b, eps = engine.ln_params(self.token_norm)
+        x = torch.empty_like(x_in)
+        ops.layernorm(x_in, w, b, eps, x)
+
+        def calls_for(it, bi):
+            k, v = kv[it][bi]
+            return [engine.AttnCall(0, Nq, 1, 1, engine.Prefix(k, v, 0, Na))]
+
+        return [p[None] for p in self._trunk_rows(x, calls_for, num_iterations)]
+
+    def _trunk_rows(self, x: torch.Tensor, calls, num_iterations: int, capture_kv=None) -> list:
         """trunk_fn (camera_head.py:123-186) on the normalised camera-token rows x [T, C] (fp32, autocast off): per
         refinement iteration embed_pose + SiLU (one GEMM epilogue), the modulation GEMM, one fused adaLN-modulate-gate-
         residual kernel, the trunk blocks, trunk_norm, pose_branch and one accumulate + activate kernel.  -> [T, 9] each."""
@@ -82,8 +123,9 @@ class CameraHead(nn.Module):
             engine.linear_rows(self.embed_pose, inp, emb, mode, SR_EPI_BIAS_SILU)          # embed_pose + the SiLU of :72-74
             engine.linear_rows(self.poseLN_modulation[1], emb, mod, mode, SR_EPI_BIAS)     # shift | scale | gate
             ops.adaln_modulate(x, mod, float(self.adaln_norm.eps), y)                      # :157-161
-            for blk in self.trunk:
-                engine.run_block(blk, y, calls, None, mode, tag="cam.")                   # :163-166
+            for bi, blk in enumerate(self.trunk):
+                engine.run_block(blk, y, calls(it, bi) if callable(calls) else calls, None, mode, tag="cam.",
+                                 capture_kv=capture_kv)                                    # :163-166
             ops.layernorm(y, tw, tb, teps, yn)
             engine.linear_rows(self.pose_branch.fc1, yn, hid, mode, SR_EPI_BIAS_GELU)      # :168-170
             engine.linear_rows(self.pose_branch.fc2, hid, delta, mode, SR_EPI_BIAS)

@@ -46,6 +46,7 @@ class Localizer:
         for blk in self.agg.global_reloc_blocks:
             blk.attn.clear_kv_cache()
         self.cam_token_last_layer = None
+        self.head._anchor_kv = None
         self._graph = None
         self._key = None
 
@@ -56,6 +57,8 @@ class Localizer:
         with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
             _, _, cam = self.agg(imgs, list(range(imgs.shape[1])), [], fix_rank=self.fix_rank)
         self.cam_token_last_layer = cam.clone()
+        with torch.no_grad(), torch.autocast("cuda", enabled=False):
+            self.head.prime_anchors(self.cam_token_last_layer)      # anchors' trunk rows once per scene, not once per query
         return self.cam_token_last_layer
 
     # ---------------------------------------------------------------------------------------------- phase 2
@@ -65,7 +68,7 @@ class Localizer:
             with torch.autocast("cuda", dtype=torch.bfloat16, enabled=self.bf16):
                 feats, _ = self.agg.forward_with_cache(images, fix_rank=self.fix_rank, camera_only=True)
             with torch.autocast("cuda", enabled=False):
-                poses = self.head(feats, self.cam_token_last_layer)
+                poses = self.head.forward_queries(feats)
                 ext, intr = pose_encoding_to_extri_intri(poses[-1], (images.shape[-2], images.shape[-1]))
         return poses[-1], ext, intr
 

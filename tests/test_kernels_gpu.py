@@ -161,7 +161,10 @@ def test_gemm_qkv_epilogue(M, col_offset):
 def test_gemm_f32_all_epilogues():
     ops = _ops()
     from sailrecon_b200._lib import SR_EPI_BIAS_GELU, SR_EPI_LS_RESIDUAL
-    for (M, N, K) in [(37, 9, 1024), (37, 2048, 9), (100, 300, 130)]:
+    # (37, 9, 1024) / (100, ...): skinny and tiled paths; M <= 8 with K >= 256: the tiny-M weight-streaming kernel (M = 1 is the
+    # per-image camera head of the localisation workload), incl. N not a multiple of the warp's columns and K % (4*32*4) != 0
+    for (M, N, K) in [(37, 9, 1024), (37, 2048, 9), (100, 300, 130), (1, 2048, 2048), (1, 9, 1024), (2, 6144, 2048), (3, 2049, 260),
+                      (5, 1024, 8192), (8, 131, 1028)]:
         a, w, b = _gemm_inputs(M, N, K, 10)
         out = torch.empty(M, N, device=DEV)
         ops.gemm(a.to(DEV), w.to(DEV), b.to(DEV), out)

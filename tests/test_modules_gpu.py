@@ -366,6 +366,11 @@ def test_localizer_camera_only_matches_full_reloc_path(bf16):
     fin = torch.isfinite(intr_ref)                          # FoV = relu(.) can be exactly 0 at random init -> infinite focal length
     assert torch.equal(torch.isfinite(intr), fin)
     assert rel_l2(pose, poses[-1]) < tol and rel_l2(ext, ext_ref) < tol and rel_l2(intr[fin], intr_ref[fin]) < tol
+    # the query-only camera head (anchors' keys / values cached by prime_anchors) == the full head on [anchors ; query]
+    with torch.no_grad():
+        q_only = head.forward_queries(full)
+    for a, b in zip(q_only, poses):
+        assert rel_l2(a, b) < 1e-5
     graph = Localizer(agg, head, fix_rank=100, use_cuda_graph=True, autocast_bf16=bf16)
     graph.cam_token_last_layer = cam                         # same primed scene
     for i in range(3):
