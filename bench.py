@@ -529,6 +529,7 @@ def main():
                     help="workload train: the reference's torch.utils.checkpoint schedule (re-run every block inside the backward) "
                          "instead of keeping the activations in HBM")
     ap.add_argument("--only-timed", action="store_true", help="workload train: skip the per-kernel profile and e2e passes (ncu runs)")
+    ap.add_argument("--reloc-batch", type=int, default=8, help="workload reloc: query images per call of the batched record")
     ap.add_argument("--ring-frames", type=int, default=512)
     ap.add_argument("--ring-depth", type=int, default=None, help="global blocks of the ring workload (24) / the sharded record (4)")
     args = ap.parse_args()

@@ -539,19 +539,155 @@ def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: Laye
     return dX0
 
 
+# ------------------------------------------------------------------------------------------------ patch embed (DINOv2 ViT / conv)
+@dataclass
+class EmbedSaved:
+    a: torch.Tensor                    # normalised im2col rows of the images, bf16 [S*hw, Kp] (operand of the projection's wgrad)
+    blocks: list                       # BlockSaved per ViT block ([] for the "conv" patch embed)
+    x_final: Optional[torch.Tensor]    # ViT residual rows before the final LayerNorm, fp32 [S*Pd, D]
+    S: int
+    Pd: int
+    hw: int
+    HW: tuple
+
+
+def embed_forward_saving(agg: nn.Module, imgs: torch.Tensor, X0: torch.Tensor, S: int, P: int, C: int):
+    """aggregator.py:267-274 + vision_transformer.py:242-307 in the bf16 autocast arithmetic, keeping what the backward reads.
+    Writes the patch-token rows of X0 [S*P, C] (rows psi.. of every frame) and returns EmbedSaved.  Same arithmetic as
+    Aggregator._embed (inference kernels); the ViT blocks run block_forward_saving instead of engine.run_block."""
+    from .layers.patch_embed import PatchEmbed
+    from .models.aggregator import _RESNET_MEAN, _RESNET_STD
+    pe_mod = agg.patch_embed
+    dev = imgs.device
+    _, _, H, W = imgs.shape
+    psi = agg.patch_start_idx
+    if isinstance(pe_mod, PatchEmbed):                                   # patch_embed="conv": tokens = proj(patches)
+        ph = pe_mod.patch_size[0]
+        hw = (H // ph) * (W // ph)
+        K = 3 * ph * ph
+        Kp = (K + 63) // 64 * 64
+        a = torch.empty(S * hw, Kp, dtype=BF, device=dev)
+        ops.patchify(imgs.contiguous(), a, ph, _RESNET_MEAN, _RESNET_STD)
+        y = torch.empty(S * hw, C, dtype=BF, device=dev)
+        ops.gemm(a, engine.weight_bf16(pe_mod.proj, pad_k=64), engine.bias_for(pe_mod.proj, "bf16"), y, kind=SR_EPI_BIAS)
+        X0.view(S, P, C)[:, psi:] = y.view(S, hw, C)
+        return EmbedSaved(a, [], None, S, P, hw, (H, W))
+    vit = pe_mod
+    D, R = vit.embed_dim, vit.num_register_tokens
+    ph = vit.patch_size
+    hw = (H // ph) * (W // ph)
+    Pd = 1 + R + hw
+    if Pd != P or D != C:
+        raise NotImplementedError("sailrecon_b200: the ViT patch embed must have the aggregator's width and register count")
+    pe = vit.interpolated_pos_embed(H, W)
+    K = 3 * ph * ph
+    Kp = (K + 63) // 64 * 64
+    a = torch.empty(S * hw, Kp, dtype=BF, device=dev)
+    ops.patchify(imgs.contiguous(), a, ph, _RESNET_MEAN, _RESNET_STD)
+    x = torch.empty(S * Pd, D, dtype=torch.float32, device=dev)
+    proj = vit.patch_embed.proj
+    from ._lib import SR_EPI_LS_RESIDUAL
+    for s_ in range(S):                                                  # x[s, 1+R:] = pos_embed[1:] + proj(patches)
+        ops.gemm(a[s_ * hw:(s_ + 1) * hw], engine.weight_bf16(proj, pad_k=64), engine.bias_for(proj, "bf16"),
+                 x[s_ * Pd + 1 + R:(s_ + 1) * Pd], kind=SR_EPI_LS_RESIDUAL, gamma=None, resid=pe[1:])
+    xv = x.view(S, Pd, D)
+    xv[:, 0] = vit.cls_token.detach()[0, 0] + pe[0]
+    if R:
+        xv[:, 1:1 + R] = vit.register_tokens.detach()[0]
+    calls = engine.full_segments(S, Pd)
+    saved = []
+    for blk in vit.blocks:
+        sb = block_forward_saving(blk, x, calls, None)
+        x = block_output(blk, sb)
+        saved.append(sb)
+    w, b, eps = engine.ln_params(vit.norm)
+    y = torch.empty(S * Pd, D, dtype=torch.float32, device=dev)
+    ops.layernorm(x, w, b, eps, y)
+    X0.view(S, P, C)[:, psi:] = y.view(S, Pd, D)[:, 1 + R:]
+    return EmbedSaved(a, saved, x, S, Pd, hw, (H, W))
+
+
+def _proj_wgrad(proj: nn.Module, a: torch.Tensor, dz: torch.Tensor, grads: Dict[nn.Parameter, torch.Tensor]) -> None:
+    """Conv2d(3, D, 14, stride 14) as a Linear on im2col rows: dW += dz^T a (a zero-padded to Kp columns), db += colsum(dz)."""
+    D = dz.shape[1]
+    K = proj.weight[0].numel()
+    gb = _acc(grads, proj.bias) if proj.bias is not None else None
+    dzT = ops.transpose_bf16(dz, colsum=gb)
+    aT = ops.transpose_bf16(a)                                           # [Kp, T_pad]
+    tmp = torch.empty(D, a.shape[1], dtype=torch.float32, device=dz.device)
+    ops.gemm(dzT, aT, None, tmp, kind=SR_EPI_BIAS)
+    _acc(grads, proj.weight).view(D, K).add_(tmp[:, :K])
+
+
+def embed_backward(agg: nn.Module, sv: EmbedSaved, dX0: torch.Tensor, grads: Dict[nn.Parameter, torch.Tensor]) -> None:
+    """dX0 [S*P, C] = gradient of the token rows the stack starts from; its patch rows flow into the patch embed."""
+    from .layers.patch_embed import PatchEmbed
+    pe_mod = agg.patch_embed
+    S, P, hw = sv.S, sv.Pd, sv.hw
+    C = dX0.shape[1]
+    psi = agg.patch_start_idx
+    dev = dX0.device
+    if isinstance(pe_mod, PatchEmbed):
+        dz = ops.cast_bf16(dX0.view(S, P, C)[:, psi:].reshape(S * hw, C))
+        _proj_wgrad(pe_mod.proj, sv.a, dz, grads)
+        return
+    vit = pe_mod
+    D, R = vit.embed_dim, vit.num_register_tokens
+    dY = dX0.clone().view(S, P, D)
+    dY[:, :1 + R] = 0                                                    # only x_norm_patchtokens is consumed (aggregator.py:273-274)
+    dy16 = ops.cast_bf16(dY.view(S * P, D))
+    w, _, eps = engine.ln_params(vit.norm)
+    dX = torch.zeros(S * P, D, dtype=torch.float32, device=dev)
+    ops.layernorm_bwd(sv.x_final, w, dy16, dX, _acc(grads, vit.norm.weight), _acc(grads, vit.norm.bias), eps)
+    for blk, sb in zip(reversed(list(vit.blocks)), reversed(sv.blocks)):
+        dX = block_backward(blk, sb, dX, grads)
+    # rows: patch tokens -> projection + pos_embed[1:], row 0 -> cls_token + pos_embed[0], rows 1..R -> register tokens;
+    # the sums over the S frames are one column-sum over the [S, Pd * D] view
+    gsum = torch.zeros(P * D, dtype=torch.float32, device=dev)
+    ops.colsum(dX.view(S, P * D), None, gsum)
+    gsum = gsum.view(P, D)
+    _acc(grads, vit.cls_token).view(D).add_(gsum[0])
+    if R:
+        _acc(grads, vit.register_tokens).view(R, D).add_(gsum[1:1 + R])
+    H, W = sv.HW
+    N = vit.pos_embed.shape[1] - 1
+    gpe = _acc(grads, vit.pos_embed)
+    if hw == N and H == W:
+        gpe[0, 0].add_(gsum[0])
+        gpe[0, 1:].add_(gsum[1 + R:])
+    else:
+        # bicubic / antialias resampling of the parameter grid (vision_transformer.py:206-240) is a function of the parameter
+        # alone, evaluated once per image size: its (linear) adjoint is taken from the same torch op
+        import math
+        M = int(math.sqrt(N))
+        h0, w0 = H // vit.patch_size, W // vit.patch_size
+        with torch.enable_grad():
+            leaf = vit.pos_embed.detach().float()[:, 1:].reshape(1, M, M, D).permute(0, 3, 1, 2).clone().requires_grad_(True)
+            kw = {"scale_factor": (float(h0 + vit.interpolate_offset) / M, float(w0 + vit.interpolate_offset) / M)} \
+                if vit.interpolate_offset else {"size": (h0, w0)}
+            grid = nn.functional.interpolate(leaf, mode="bicubic", antialias=vit.interpolate_antialias, **kw)
+            grid.backward(gsum[1 + R:].view(1, h0, w0, D).permute(0, 3, 1, 2))
+        gpe[0, 0].add_(gsum[0])
+        gpe[0, 1:].add_(leaf.grad.permute(0, 2, 3, 1).reshape(N, D))
+    dz = ops.cast_bf16(dX.view(S, P, D)[:, 1 + R:].reshape(S * hw, D))
+    _proj_wgrad(vit.patch_embed.proj, sv.a, dz, grads)
+
+
 # ------------------------------------------------------------------------------------------------ autograd bridge
 class AggregatorFunction(torch.autograd.Function):
     """Aggregator.forward as ONE autograd node, so the reference's training loop runs unchanged through the overlay
     (train_imc.py:361-381: `predictions = model(...)` under autocast(bf16), `scaler.scale(loss).backward()`, DDP hooks,
     `scaler.step(optimizer)`): forward = patch embed + stack_forward on the C-ABI kernels, backward = stack_backward.
-    Differentiated: the 3 x depth aggregator blocks and the four special-token parameters (the gradient of the token rows
-    the stack starts from).  NOT differentiated here: the patch embed (DINOv2 / conv) — its parameters receive no gradient
-     — and the images.  Inputs after the six non-tensor arguments are exactly the tensors that receive
-    gradients, in `AggregatorFunction.parameters_of(agg)` order."""
+    Differentiated: the patch embed (DINOv2 ViT blocks + patch projection + position embedding / cls / register tokens, or
+    the "conv" projection; embed_forward_saving / embed_backward), the four special-token parameters and the 3 x depth
+    aggregator blocks — every parameter of the Aggregator except the ViT's unused mask_token.  Not differentiated: the
+    images.  Inputs after the six non-tensor arguments are exactly the tensors that receive gradients, in
+    `AggregatorFunction.parameters_of(agg)` order."""
 
     @staticmethod
     def parameters_of(agg: nn.Module) -> List[nn.Parameter]:
         ps = [agg.camera_token, agg.register_token, agg.camera_token_reloc, agg.register_token_reloc]
+        ps.extend(p for p in agg.patch_embed.parameters() if p.requires_grad)
         for i in range(agg.depth):
             for blk in (agg.frame_blocks[i], agg.global_blocks[i], agg.global_reloc_blocks[i]):
                 ps.extend(blk.parameters())
@@ -582,7 +718,7 @@ class AggregatorFunction(torch.autograd.Function):
         imgs = images[0] if order == list(range(S)) else images[0][torch.tensor(order, device=dev)]
         T = S * P
         X0 = torch.empty(T, C, dtype=torch.float32, device=dev)
-        agg._embed(imgs.contiguous(), "bf16", X0, S, P, C)
+        ctx.embed = embed_forward_saving(agg, imgs.contiguous(), X0, S, P, C)
         X0.view(S, P, C)[:, :psi] = agg._special_rows(order, set(reloc_list), False)
         rows_pos, frame_pos_cpu = agg._positions(S, h, w, dev)
         lctx = LayerCtx(Na, Nq, P, rows_pos)
@@ -642,6 +778,8 @@ class AggregatorFunction(torch.autograd.Function):
         grads: Dict[nn.Parameter, torch.Tensor] = {}
         dX0 = stack_backward(agg, ctx.ck, d_out, lctx, grads)
         ctx.ck = None
+        embed_backward(agg, ctx.embed, dX0, grads)                  # DINOv2 ViT blocks / conv projection, pos-embed, cls, registers
+        ctx.embed = None
         # gradient of the special-token rows (aggregator.py:287-299): frame 0 -> slot 0, other anchors -> slot 1, queries -> *_reloc
         d_sp = dX0.view(S, P, C)[:, :psi]
         g_cam_tok = torch.zeros_like(agg.camera_token)
