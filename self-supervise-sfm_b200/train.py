@@ -504,7 +504,8 @@ def choose_keep_activations(ctx: LayerCtx, depth: int, C: int, scene_rows: int, 
 
 
 def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: LayerCtx, draw_scene, d_out: Dict[int, tuple],
-                  world: int = 1, fwd_bwd=None, optimizer_step=None, keep_activations: Optional[bool] = None) -> torch.Tensor:
+                  world: int = 1, fwd_bwd=None, optimizer_step=None, keep_activations: Optional[bool] = None,
+                  skip_nonfinite: bool = False) -> torch.Tensor:
     """zero_grad + forward + backward + gradient all-reduce + Adam for the block stacks on one scene per rank
     (train_imc.py:361-381 with DDP, :472).  The all-reduce of layer i's bucket (sum; the 1 / world of DDP's mean is
     folded into the Adam kernel) is issued as soon as layer i's backward is enqueued and overlaps the layers below it.
@@ -513,7 +514,13 @@ def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: Laye
     False is the reference's torch.utils.checkpoint schedule (block inputs only, each block re-run inside the backward);
     None (default) keeps them when activation_bytes() fits the free HBM of X0's device (choose_keep_activations).
     fwd_bwd(on_layer_done) -> dX0 and optimizer_step(grad_scale) replace the CUDA kernels in the CPU (gloo) tests of this
-    schedule; the product path leaves them None."""
+    schedule; the product path leaves them None.
+    skip_nonfinite: GradScaler.step semantics (train_imc.py:380-381) — after the all-reduce the gradient buckets are checked
+    and the optimizer step is SKIPPED (returning with `state.skipped_steps` incremented) when any gradient is inf / nan, so
+    one bad scene cannot corrupt the fp32 masters and the Adam moments; costs one read of the gradient buckets (host sync).
+    Learning-rate schedules (the reference's CosineWarmupScheduler, train_imc.py:62-90,384) drive `state.lr` between steps.
+    Note: Adam runs over whole layer buckets; with no query frames (Nq = 0) the reloc blocks' gradients are zero, not None,
+    so their moments decay where torch.optim would skip them (no reference script trains without queries)."""
     import torch.distributed as dist
     state.zero_grad()
     works = []
@@ -535,6 +542,9 @@ def training_step(agg: nn.Module, state: TrainState, X0: torch.Tensor, ctx: Laye
         dX0 = fwd_bwd(reduce_layer)
     for w in works:
         w.wait()
+    if skip_nonfinite and not all(bool(torch.isfinite(g).all()) for g in state.grad):
+        state.skipped_steps = getattr(state, "skipped_steps", 0) + 1
+        return dX0
     (optimizer_step or state.adam_step)(grad_scale=1.0 / world)
     return dX0
 

@@ -398,6 +398,15 @@ def test_training_step_two_layers_matches_fp32_autograd_and_adam(keep_activation
     # the cached bf16 weights follow the update
     w = agg.frame_blocks[0].mlp.fc1
     assert torch.equal(engine.weight_bf16(w), w.weight.detach().to(torch.bfloat16))
+    # GradScaler.step semantics (train_imc.py:380-381): a non-finite gradient skips the optimizer step entirely
+    snap = [p_.clone() for p_ in state.param]
+    step_before = state.step
+    bad = {0: d_out[0], 1: (None, d_out[1][1].clone())}
+    bad[1][1][7, 3] = float("inf")
+    it = iter(draws)
+    train.training_step(agg, state, X0, ctx, draw_scene, bad, keep_activations=keep_activations, skip_nonfinite=True)
+    assert state.step == step_before and state.skipped_steps == 1
+    assert all(torch.equal(a, b) for a, b in zip(snap, state.param))
 
 
 # ------------------------------------------------------------------------------------------------ data parallel over NCCL
