@@ -544,7 +544,10 @@ extern "C" int sr_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t l
   }
 
   CUtensorMap ta, tb;
-  const int BN = (N % 256 == 0) ? 256 : 128;
+  // 128 x 256 tiles by default; when that leaves most SMs idle (few rows: one query image of the localisation workload, the
+  // coarse DPT feature maps) the 128 x 128 tiling doubles the tile count
+  const int64_t tiles256 = ((M + kBM - 1) / kBM) * (N / 256);
+  const int BN = (N % 256 == 0 && tiles256 >= kNumSMs / 2) ? 256 : 128;
   {
     uint64_t dims[2] = {static_cast<uint64_t>(K), static_cast<uint64_t>(M)};
     uint64_t strides[1] = {static_cast<uint64_t>(lda) * 2};
