@@ -15,7 +15,7 @@ H, D, C = 16, 64, 1024
 dev = "cuda"
 
 
-def bench(name, batch, L, prefix_len=0, iters=10, check=False):
+def bench(name, batch, L, prefix_len=0, iters=10, check=False, variant=0):
     T = batch * L
     g = torch.Generator(device=dev).manual_seed(0)
     nbuf = 4 if T * 3 * C * 2 < 600e6 else 1
@@ -29,7 +29,7 @@ def bench(name, batch, L, prefix_len=0, iters=10, check=False):
         qkv = qkvs[i % nbuf]
         ops.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], out, H, D, batch, L, L, L, L,
                       prefix_k=None if pre is None else pre[:, :C], prefix_v=None if pre is None else pre[:, C:],
-                      prefix_len=prefix_len)
+                      prefix_len=prefix_len, variant=variant)
     for i in range(3):
         run(i)
     torch.cuda.synchronize()
@@ -41,7 +41,7 @@ def bench(name, batch, L, prefix_len=0, iters=10, check=False):
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / iters
     flops = 4.0 * batch * L * (prefix_len + L) * C
-    rec = {"shape": name, "batch": batch, "L": L, "prefix": prefix_len, "ms": round(ms, 4), "tflops": round(flops / ms / 1e9, 1)}
+    rec = {"shape": name, "variant": variant, "batch": batch, "L": L, "prefix": prefix_len, "ms": round(ms, 4), "tflops": round(flops / ms / 1e9, 1)}
     if check:
         # fp32 reference on a few heads / segments (bf16 inputs, fp32 math)
         qkv = qkvs[(iters - 1) % nbuf].float()
@@ -64,8 +64,11 @@ def bench(name, batch, L, prefix_len=0, iters=10, check=False):
 
 if __name__ == "__main__":
     check = "--check" in sys.argv
-    bench("global16", 1, 16 * 1374, check=check)
-    bench("frame32", 32, 1374, check=check)
-    bench("reloc16", 16, 1374, prefix_len=16 * 305, check=check)
+    for variant in (0, 4, 3):                      # 0 = mixed four- / three-tile decomposition (default), 4 / 3 = uniform
+        bench("global16", 1, 16 * 1374, check=check, variant=variant)
+        bench("frame32", 32, 1374, check=check, variant=variant)
+        bench("reloc16", 16, 1374, prefix_len=16 * 305, check=check, variant=variant)
+        bench("global12", 1, 12 * 1374, variant=variant)
+        bench("reloc1x100", 1, 1374, prefix_len=100 * 305, variant=variant)
     if "--big" in sys.argv:
         bench("global64", 1, 64 * 1374, iters=3)

@@ -51,11 +51,12 @@ def _compare(ro, oo, tol, pose_tol=1e-2):
         assert o_out[k].dtype == torch.float32 and o_out[k].shape == r_out[k].shape
         errs[k] = rel_l2(o_out[k], r_out[k].float())
     errs["cam"] = rel_l2(o_cam, r_cam.float())
-    if r_poses is not None:
-        errs["pose"] = max(float((a - b).abs().max()) for a, b in zip(o_poses, r_poses))
+    if r_poses is not None:      # pose encodings within 1e-2 RELATIVE (their scale is arbitrary at random init); max-abs printed too
+        errs["pose"] = max(rel_l2(a, b) for a, b in zip(o_poses, r_poses))
+        errs["pose_max_abs"] = max(float((a - b).abs().max()) for a, b in zip(o_poses, r_poses))
     print("parity", {k: f"{v:.2e}" for k, v in errs.items()})
     for k, v in errs.items():
-        assert v < (pose_tol if k == "pose" else tol), (k, v, errs)
+        assert v < (pose_tol if k == "pose" else (5 * pose_tol if k == "pose_max_abs" else tol)), (k, v, errs)
     return errs
 
 
@@ -105,7 +106,7 @@ def test_depth4_order_one_layerscale_permuted_lists(bf16):
     images = _images(4, 518, 518, 4)
     ro = ref_live.run_reference(r_agg, r_head, images, [0, 2], [3, 1], 300, bf16)
     oo = ref_live.run_ours(o_agg, o_head, images, [0, 2], [3, 1], 300, bf16)
-    _compare(ro, oo, 2e-2 if bf16 else 1e-4, pose_tol=5e-2 if bf16 else 1e-2)
+    _compare(ro, oo, 2e-2 if bf16 else 1e-4)
 
 
 @pytest.mark.parametrize("bf16", [False, True])
