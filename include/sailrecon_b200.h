@@ -122,6 +122,10 @@ typedef struct sr_attn {
   /* kernel variant of the tcgen05 path: 0 = chosen per launch by wave quantisation (default), 3 / 4 = force the
    * three- / four-query-tile kernel.  Every variant computes the same function; ignored by the fp32 path.    */
   int32_t variant;
+  /* optional scratch for split-KV (under-filled launches: few query rows against a long K/V range, e.g. one query frame
+   * against a cached 100-anchor scene): sr_attn_workspace_bytes() says how much this call can use (0 = none); NULL or
+   * too small = the call runs un-split.  fp32 partial (m, l, O) per K/V chunk, combined by a second small kernel.      */
+  void* workspace; int64_t workspace_bytes;
 } sr_attn_t;
 
 /* Profiling aid, -DSR_DEBUG builds of the library only (the shipped build never reads the environment and returns an
@@ -133,6 +137,8 @@ int sr_attn_fwd_bf16(const sr_attn_t* p, void* stream);  /* tcgen05 flash attent
 /* Host-only query (no GPU needed): the work decomposition sr_attn_fwd_bf16 uses for a launch of num_heads x batch
  * (head, segment) rows of q_len query rows on num_sms SMs — n4 CTAs of four 128-row query tiles and n3 CTAs of three per
  * row; all four-tile CTAs are dispatched first, so the lighter ones fill the tail wave.                           */
+/* Host-only: bytes of sr_attn_t.workspace the bf16 path would use for this call on a device with num_sms SMs (0 = no split). */
+int64_t sr_attn_workspace_bytes(const sr_attn_t* p, int32_t num_sms);
 int sr_attn_plan(int64_t q_len, int32_t num_heads, int32_t batch, int32_t num_sms, int32_t* n4, int32_t* n3);
 int sr_attn_fwd_f32(const sr_attn_t* p, void* stream);   /* fp32 SIMT, head_dim <= 128 (check mode, camera) */
 

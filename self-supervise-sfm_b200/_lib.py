@@ -44,6 +44,7 @@ class SrAttn(C.Structure):
         ("carry_m", _vp), ("carry_l", _vp), ("carry_acc", _vp), ("carry_in", _i32), ("carry_out", _i32),
         ("lse", _vp), ("lse_pad", _i64),
         ("variant", _i32),
+        ("workspace", _vp), ("workspace_bytes", _i64),
     ]
 
 
@@ -79,6 +80,7 @@ SIGNATURES = {
     "sr_debug_trace_read": (C.c_int, [C.POINTER(C.c_longlong), _i64]),
     "sr_attn_fwd_bf16": (C.c_int, [C.POINTER(SrAttn), _vp]),
     "sr_attn_fwd_f32": (C.c_int, [C.POINTER(SrAttn), _vp]),
+    "sr_attn_workspace_bytes": (_i64, [C.POINTER(SrAttn), _i32]),
     "sr_attn_plan": (C.c_int, [_i64, _i32, _i32, _i32, C.POINTER(_i32), C.POINTER(_i32)]),
     "sr_attn_bwd_bf16": (C.c_int, [C.POINTER(SrAttnBwd), _vp]),
     "sr_transpose_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _vp, _vp]),

@@ -66,6 +66,11 @@ struct Attn4Params {
   // (16-anchor global shape: 172 tiles per head = 37 x 4 + 8 x 3 -> 592 heavy CTAs = exactly 4 waves of 148 SMs + 128 light
   // ones = 19 tile-steps of makespan instead of the 20 of 688 uniform four-tile CTAs; chosen per shape by choose_mix()).
   int n_rows, n4, n3, batch;
+  // Split-KV (under-filled launches, e.g. ONE query frame against a 100-anchor scene prefix = 48 CTAs on 148 SMs): the
+  // K/V tile range is cut into n_split chunks, each (row, query-group, chunk) is its own CTA writing its partial
+  // (m, l, un-normalised O) into per-chunk carry buffers inside the caller's workspace; attn_split_merge_kernel combines them.
+  int n_split;
+  int64_t split_stride_ml, split_stride_acc;   // floats between consecutive chunks' (m | l) and acc buffers
 };
 
 template <int kPoly>
@@ -88,8 +93,10 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   uint8_t* sK0 = sV + k4Stages * k4KvTile;                           // K(0)
 
   int row, q0, nq_cap;                                               // see Attn4Params: heavy CTAs first, light CTAs last
+  const int base_ctas = p.n_rows * (p.n4 + p.n3);
+  const int split = blockIdx.x / base_ctas;                          // 0 unless the launch is split over the K/V range
   {
-    const int lin = blockIdx.x, heavy = p.n_rows * p.n4;
+    const int lin = blockIdx.x - split * base_ctas, heavy = p.n_rows * p.n4;
     if (lin < heavy) {
       row = lin / p.n4;
       q0 = (lin - row * p.n4) * 512;
@@ -104,7 +111,13 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   const int b = row / p.num_heads;
   const int head = row - b * p.num_heads;
   const int nq_valid = min(nq_cap, (p.q_len - q0 + 127) / 128);      // query tiles that hold at least one row
-  const int n_tiles = p.n_prefix_tiles + p.n_own_tiles;
+  const int n_all = p.n_prefix_tiles + p.n_own_tiles;                // K/V tiles of the whole problem
+  const int t_chunk = (n_all + p.n_split - 1) / p.n_split;
+  const int t0 = split * t_chunk;                                    // this CTA walks tiles [t0, t0 + n_tiles)
+  const int n_tiles = min(n_all, t0 + t_chunk) - t0;
+  float* const carry_m = p.carry_m + split * p.split_stride_ml;
+  float* const carry_l = p.carry_l + split * p.split_stride_ml;
+  float* const carry_acc = p.carry_acc + split * p.split_stride_acc;
   const bool trace_on = kDebugBuild && p.trace && blockIdx.x == 0 && lane == 0;
 
   if (warp == 0 && lane == 0) {
@@ -152,7 +165,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     if (elect_one()) {
       mbar_arrive_expect_tx(&q_full, nq_valid * k4QTile + k4KvTile);
       for (int q = 0; q < nq_valid; ++q) tma_load_3d(sQ + q * k4QTile, &tmap_q, &q_full, head * 64, q0 + q * 128, b);
-      load_tile(sK0, &q_full, 0, true);
+      load_tile(sK0, &q_full, t0, true);
     }
     __syncwarp();
     for (int j = 0; j < n_tiles; ++j) {
@@ -161,8 +174,8 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       if (elect_one()) {
         const bool has_k = j + 1 < n_tiles;
         mbar_arrive_expect_tx(&kv_full[s], has_k ? 2 * k4KvTile : k4KvTile);
-        load_tile(sV + s * k4KvTile, &kv_full[s], j, false);
-        if (has_k) load_tile(sK + s * k4KvTile, &kv_full[s], j + 1, true);
+        load_tile(sV + s * k4KvTile, &kv_full[s], t0 + j, false);
+        if (has_k) load_tile(sK + s * k4KvTile, &kv_full[s], t0 + j + 1, true);
       }
       __syncwarp();
     }
@@ -243,11 +256,11 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       float m = -INFINITY, l = 0.f;
       if (p.carry_in) {
         if (row_ok) {
-          m = p.carry_m[static_cast<int64_t>(head) * p.total_q_rows + g_row];
-          l = p.carry_l[static_cast<int64_t>(head) * p.total_q_rows + g_row];
+          m = carry_m[static_cast<int64_t>(head) * p.total_q_rows + g_row];
+          l = carry_l[static_cast<int64_t>(head) * p.total_q_rows + g_row];
         }
         // seed O with the carried un-normalised accumulator
-        const float* src = p.carry_acc + g_row * (static_cast<int64_t>(p.num_heads) * 64) + head * 64;
+        const float* src = carry_acc + g_row * (static_cast<int64_t>(p.num_heads) * 64) + head * 64;
 #pragma unroll
         for (int hlf = 0; hlf < 2; ++hlf) {
           uint32_t o[32];
@@ -260,9 +273,9 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
       const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
 
       // valid kv columns of tile j (only the last tile of the prefix / own range is partial)
-      auto valid_cols = [&](int j) {
-        if (j < p.n_prefix_tiles) return j == p.n_prefix_tiles - 1 ? p.prefix_len - j * 64 : 64;
-        return j == n_tiles - 1 ? p.kv_len - (j - p.n_prefix_tiles) * 64 : 64;
+      auto valid_cols = [&](int t) {                       // t = tile index in the whole problem
+        if (t < p.n_prefix_tiles) return t == p.n_prefix_tiles - 1 ? p.prefix_len - t * 64 : 64;
+        return t == n_all - 1 ? p.kv_len - (t - p.n_prefix_tiles) * 64 : 64;
       };
       uint32_t sraw[64];
       auto row_max = [&](int valid) {
@@ -295,7 +308,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         tmem_ld32(tS, *reinterpret_cast<uint32_t(*)[32]>(&sraw[0]));
         tmem_ld32(tS + 32, *reinterpret_cast<uint32_t(*)[32]>(&sraw[32]));
         tmem_ld_wait();
-        const float mx = row_max(valid_cols(j)) * p.scale_log2;            // scale > 0
+        const float mx = row_max(valid_cols(t0 + j)) * p.scale_log2;       // scale > 0
         if (tr_role >= 0 && mx == mx) SR_TRACE4(tr_role, j, 2);
         float m_new = m;
         if (mx > m + k4LazyRescaleLog2) m_new = mx;                        // also the first tile (m = -inf)
@@ -362,7 +375,7 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
         tmem_ld_wait();
         if (row_ok) {
           if (p.carry_out) {
-            float* dst = p.carry_acc + g_row * (static_cast<int64_t>(p.num_heads) * 64) + head * 64 + hlf * 32;
+            float* dst = carry_acc + g_row * (static_cast<int64_t>(p.num_heads) * 64) + head * 64 + hlf * 32;
 #pragma unroll
             for (int i = 0; i < 32; i += 4) *reinterpret_cast<uint4*>(dst + i) = make_uint4(o[i], o[i + 1], o[i + 2], o[i + 3]);
           } else {
@@ -379,11 +392,11 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
           }
         }
       }
-      if (row_ok && p.lse != nullptr)
+      if (row_ok && p.lse != nullptr && p.n_split == 1)
         p.lse[(static_cast<int64_t>(head) * p.batch + b) * p.lse_pad + q_row] = m + log2f(l);
       if (row_ok && p.carry_out) {
-        p.carry_m[static_cast<int64_t>(head) * p.total_q_rows + g_row] = m;
-        p.carry_l[static_cast<int64_t>(head) * p.total_q_rows + g_row] = l;
+        carry_m[static_cast<int64_t>(head) * p.total_q_rows + g_row] = m;
+        carry_l[static_cast<int64_t>(head) * p.total_q_rows + g_row] = l;
       }
     }
   }
@@ -394,6 +407,48 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
     tc_fence_after();
     tmem_dealloc<512>(tmem_base);
   }
+}
+
+// Combines the n_split partial results of a split-KV launch: one warp per (segment, query row, head), lane = 2 of the 64
+// output features.  m, l in the log2 domain; acc un-normalised.
+__global__ void __launch_bounds__(256)
+attn_split_merge_kernel(const float* __restrict__ ws_m, const float* __restrict__ ws_l, const float* __restrict__ ws_acc,
+                        int n_split, int64_t stride_ml, int64_t stride_acc, __nv_bfloat16* __restrict__ out, int64_t ldo,
+                        float* __restrict__ lse, int lse_pad, int num_heads, int batch, int q_len, int q_batch_stride,
+                        int64_t total_q_rows) {
+  const int lane = threadIdx.x & 31;
+  const int64_t w = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (w >= static_cast<int64_t>(batch) * q_len * num_heads) return;
+  const int head = static_cast<int>(w % num_heads);
+  const int64_t r = w / num_heads;
+  const int q_row = static_cast<int>(r % q_len), b = static_cast<int>(r / q_len);
+  const int64_t g_row = static_cast<int64_t>(b) * q_batch_stride + q_row;
+  const int64_t ml = static_cast<int64_t>(head) * total_q_rows + g_row;
+  float M = -INFINITY;
+  for (int s = 0; s < n_split; ++s) M = fmaxf(M, ws_m[s * stride_ml + ml]);
+  float L = 0.f, o0 = 0.f, o1 = 0.f;
+  for (int s = 0; s < n_split; ++s) {
+    const float wgt = exp2f(ws_m[s * stride_ml + ml] - M);
+    L = fmaf(ws_l[s * stride_ml + ml], wgt, L);
+    const float2 a = *reinterpret_cast<const float2*>(ws_acc + s * stride_acc + g_row * (static_cast<int64_t>(num_heads) * 64) +
+                                                      head * 64 + lane * 2);
+    o0 = fmaf(a.x, wgt, o0);
+    o1 = fmaf(a.y, wgt, o1);
+  }
+  const float inv = 1.0f / L;
+  *reinterpret_cast<uint32_t*>(out + g_row * ldo + head * 64 + lane * 2) = pack_bf16x2(o0 * inv, o1 * inv);
+  if (lse != nullptr && lane == 0) lse[(static_cast<int64_t>(head) * batch + b) * lse_pad + q_row] = M + log2f(L);
+}
+
+// Number of K/V chunks for a launch: only when the un-split grid leaves more than half of the SMs idle and every chunk
+// keeps >= 8 tiles (the per-CTA prologue / epilogue is ~2 tile periods).
+static int choose_split(const sr_attn_t* a, int base_ctas, int n_all_tiles, int num_sms) {
+  if (a->carry_in || a->carry_out || base_ctas * 2 > num_sms) return 1;
+  int ks = num_sms / base_ctas;
+  ks = std::min(ks, n_all_tiles / 8);
+  if (ks <= 1) return 1;
+  const int chunk = (n_all_tiles + ks - 1) / ks;           // tiles per chunk; re-derive the count so that no chunk is empty
+  return (n_all_tiles + chunk - 1) / chunk;
 }
 
 template <int kPoly>
@@ -521,9 +576,38 @@ int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
   p.n_rows = a->num_heads * a->batch;
   const int t_tiles = static_cast<int>((a->q_len + 127) / 128);
   choose_mix(t_tiles, p.n_rows, num_sms, a->variant == 4, &p.n4, &p.n3);
-  const int64_t n_ctas = static_cast<int64_t>(p.n_rows) * (p.n4 + p.n3);
-  SR_REQUIRE(n_ctas < (1ll << 31), "sr_attn_fwd_bf16: too many CTAs");
-  dim3 grid(static_cast<unsigned>(n_ctas), 1, 1);
+  const int64_t base_ctas = static_cast<int64_t>(p.n_rows) * (p.n4 + p.n3);
+  SR_REQUIRE(base_ctas < (1ll << 31), "sr_attn_fwd_bf16: too many CTAs");
+  p.n_split = 1;
+  p.split_stride_ml = p.split_stride_acc = 0;
+  if (a->workspace != nullptr) {
+    const int ks = choose_split(a, static_cast<int>(base_ctas), p.n_prefix_tiles + p.n_own_tiles, num_sms);
+    const int64_t per_split = p.total_q_rows * a->num_heads * (2 + 64);            // floats: m, l, acc
+    if (ks > 1 && a->workspace_bytes >= ks * per_split * 4) {
+      p.n_split = ks;
+      p.split_stride_ml = p.total_q_rows * a->num_heads;
+      p.split_stride_acc = p.total_q_rows * a->num_heads * 64;
+      float* ws = reinterpret_cast<float*>(a->workspace);
+      p.carry_m = ws;
+      p.carry_l = ws + ks * p.split_stride_ml;
+      p.carry_acc = ws + 2 * ks * p.split_stride_ml;
+      p.carry_in = 0;
+      p.carry_out = 1;
+    }
+  }
+  dim3 grid(static_cast<unsigned>(base_ctas * p.n_split), 1, 1);
+  if (p.n_split > 1) {
+    SR_REQUIRE(poly == 2, "sr_attn_fwd_bf16: split-KV runs the product kernel only");
+    if (int rc = launch4<2>(grid, st, tq, tk, tv, tpk, tpv, p)) return rc;
+    const int64_t warps = static_cast<int64_t>(a->batch) * a->q_len * a->num_heads;
+    attn_split_merge_kernel<<<static_cast<unsigned>((warps + 7) / 8), 256, 0, st>>>(
+        p.carry_m, p.carry_l, p.carry_acc, p.n_split, p.split_stride_ml, p.split_stride_acc,
+        reinterpret_cast<__nv_bfloat16*>(a->out), a->ldo, a->lse, static_cast<int>(a->lse_pad), a->num_heads, a->batch,
+        static_cast<int>(a->q_len), static_cast<int>(qbs), p.total_q_rows);
+    ++g_launch_count;
+    SR_CHECK_CUDA(cudaGetLastError());
+    return SR_OK;
+  }
   switch (poly) {
     case 2: return launch4<2>(grid, st, tq, tk, tv, tpk, tpv, p);
 #ifdef SR_DEBUG
@@ -538,6 +622,19 @@ int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
 }
 
 }  // namespace sr
+
+extern "C" int64_t sr_attn_workspace_bytes(const sr_attn_t* a, int32_t num_sms) {
+  using namespace sr;
+  if (a == nullptr || a->head_dim != 64 || a->variant == 3 || num_sms <= 0 || a->q_len <= 0 || a->kv_len <= 0) return 0;
+  int n4 = 0, n3 = 0;
+  const int rows = a->num_heads * a->batch;
+  choose_mix(static_cast<int>((a->q_len + 127) / 128), rows, num_sms, a->variant == 4, &n4, &n3);
+  const int64_t pre = a->pk != nullptr && a->prefix_len > 0 ? (a->prefix_len + 63) / 64 : 0;
+  const int ks = choose_split(a, rows * (n4 + n3), static_cast<int>(pre + (a->kv_len + 63) / 64), num_sms);
+  if (ks <= 1) return 0;
+  const int64_t total_q_rows = a->batch > 1 ? static_cast<int64_t>(a->batch - 1) * a->q_batch_stride + a->q_len : a->q_len;
+  return ks * total_q_rows * a->num_heads * (2 + 64) * 4;
+}
 
 extern "C" int sr_attn_plan(int64_t q_len, int32_t num_heads, int32_t batch, int32_t num_sms, int32_t* n4, int32_t* n3) {
   using namespace sr;

@@ -232,6 +232,11 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[t
             raise ValueError("sailrecon_b200: lse must be contiguous fp32 [num_heads, batch, q_pad] (bf16 attention only)")
         a.lse, a.lse_pad = lse.data_ptr(), lse.shape[2]
     lib = _lib.load()
+    if dt == torch.bfloat16 and out is not None and carry is None:
+        need = int(lib.sr_attn_workspace_bytes(C.byref(a), _num_sms(q.device)))
+        if need > 0:                                        # under-filled launch: split the K/V range over more CTAs
+            ws = _attn_workspace(need, q.device)
+            a.workspace, a.workspace_bytes = ws.data_ptr(), need
     fn = lib.sr_attn_fwd_bf16 if dt == torch.bfloat16 else lib.sr_attn_fwd_f32
     hd = num_heads * head_dim
     t = _Timed("attn_tc" if dt == torch.bfloat16 else "attn_f32", 4.0 * batch * q_len * (prefix_len + kv_len) * hd,
@@ -239,6 +244,28 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[t
     _lib.check(fn(C.byref(a), _stream()), "attention")
     t.done()
     return out
+
+
+_SMS: dict = {}
+_ATTN_WS: dict = {}
+
+
+def _num_sms(device) -> int:
+    d = torch.device(device)
+    if d not in _SMS:
+        _SMS[d] = torch.cuda.get_device_properties(d).multi_processor_count
+    return _SMS[d]
+
+
+def _attn_workspace(nbytes: int, device) -> torch.Tensor:
+    """Split-KV scratch, one growing buffer per (device, stream) — launches on a stream are ordered, so it is reusable."""
+    d = torch.device(device)
+    key = (d, torch.cuda.current_stream(d).cuda_stream)
+    buf = _ATTN_WS.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=d)
+        _ATTN_WS[key] = buf
+    return buf
 
 
 def new_lse(num_heads: int, batch: int, q_len: int, device) -> torch.Tensor:

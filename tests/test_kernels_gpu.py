@@ -259,7 +259,9 @@ def test_attention_bf16_every_kernel_variant(variant, monkeypatch):
     ops = type("V", (), {"attention": staticmethod(functools.partial(ops.attention, variant=variant))})
     H, d = 16, 64
     g = _g(40 + variant)
-    for batch, L, prefix_len in ((2, 1374, 0), (1, 600, 0), (3, 70, 0), (2, 333, 305), (1, 129, 64)):
+    # the last three cases under-fill the GPU (<= 48 CTAs) with a long K/V range: variant 0 / 4 split it over more CTAs
+    for batch, L, prefix_len in ((2, 1374, 0), (1, 600, 0), (3, 70, 0), (2, 333, 305), (1, 129, 64), (1, 300, 5000), (1, 1374, 6200),
+                                 (2, 100, 777)):
         qkv = torch.randn(batch * L, 3 * H * d, generator=g)
         pkv = torch.randn(max(prefix_len, 1), 2 * H * d, generator=g)
         qkv_d, pkv_d = bf(qkv).to(DEV), bf(pkv).to(DEV)
@@ -334,7 +336,8 @@ def _attn_grad_ref(q, k, v, dout, H, d, batch, L, prefix=None):
     return out.detach(), torch.stack(lses, dim=1), g
 
 
-@pytest.mark.parametrize("batch,L,prefix_len", [(1, 128, 0), (2, 200, 0), (1, 1374, 0), (3, 333, 0), (2, 150, 100), (3, 333, 305)])
+@pytest.mark.parametrize("batch,L,prefix_len", [(1, 128, 0), (2, 200, 0), (1, 1374, 0), (3, 333, 0), (2, 150, 100), (3, 333, 305),
+                                                (1, 200, 5000)])      # the last one: split-KV forward writes lse in its merge kernel
 def test_attention_bwd_bf16(batch, L, prefix_len):
     """sr_attn_bwd_bf16 (csrc/attn_bwd.cu) against fp32 autograd on the same bf16-rounded inputs: dq, dk, dv (and the
     gradient of the shared scene prefix, summed over the segments) within 2e-2 relative L2; the forward's lse exact to 1e-3.
