@@ -84,6 +84,14 @@ typedef struct sr_epilogue {
  * Requirements: K % 64 == 0, N % 128 == 0, lda/ldw multiples of 8, 16-byte aligned pointers.              */
 int sr_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int64_t M, int64_t N, int64_t K,
                  const sr_epilogue_t* epi, void* stream);
+/* The same tensor-core kernel with operands as the Linear GRADIENTS find them in memory (no transposed copies):
+ *   out[M, N] = op(A) W   with W bf16 [K, N] (row stride ldw; "MN-major": the contraction index runs over rows) and
+ *   a_mn_major = 0: A bf16 [M, K] (row stride lda)      dX[T, K_in]    = dY[T, N_out] W[N_out, K_in]
+ *   a_mn_major = 1: A bf16 [K, M] (row stride lda)      dW[N_out, K_in] = dY[T, N_out]^T X[T, K_in]   (K = T, any length)
+ * Epilogues: SR_EPI_BIAS (bf16 or fp32 out) and SR_EPI_LS_RESIDUAL (with exact_residual = 1: fp32 accumulate into out).
+ * Requirements: N % 128 == 0; M % 64 == 0 (a_mn_major = 1) or K % 64 == 0 (a_mn_major = 0); b_mn_major must be 1.   */
+int sr_gemm_bf16_t(const void* A, int64_t lda, int32_t a_mn_major, const void* W, int64_t ldw, int32_t b_mn_major,
+                   int64_t M, int64_t N, int64_t K, const sr_epilogue_t* epi, void* stream);
 /* fp32 SIMT path (fp32-check mode and the autocast-disabled camera head, sail_recon.py:119): no rounding.  */
 int sr_gemm_f32(const float* A, int64_t lda, const float* W, int64_t ldw, int64_t M, int64_t N, int64_t K,
                 const sr_epilogue_t* epi, void* stream);

@@ -76,6 +76,7 @@ SIGNATURES = {
     "sr_layernorm_fwd": (C.c_int, [_vp, _i64, _vp, _vp, _vp, C.c_int, _i64, _i64, _i64, _f32, _vp]),
     "sr_layernorm_gather_fwd": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, C.c_int, _i64, _i64, _i64, _f32, _vp]),
     "sr_gemm_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, C.POINTER(SrEpilogue), _vp]),
+    "sr_gemm_bf16_t": (C.c_int, [_vp, _i64, _i32, _vp, _i64, _i32, _i64, _i64, _i64, C.POINTER(SrEpilogue), _vp]),
     "sr_gemm_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, C.POINTER(SrEpilogue), _vp]),
     "sr_debug_trace_read": (C.c_int, [C.POINTER(C.c_longlong), _i64]),
     "sr_attn_fwd_bf16": (C.c_int, [C.POINTER(SrAttn), _vp]),

@@ -222,7 +222,12 @@ __device__ __forceinline__ void epi_qkv_head(const GemmParams& p, int col, int w
 }
 
 // ---------------------------------------------------------------------------------------------- kernel
-template <int BN, int EPI, bool OUT_BF16>
+// AMN / BMN = 1: that operand is MN-major in global memory, i.e. stored [K (contraction) rows, M or N contiguous] — the layout
+// the gradients of a Linear have (dW = dY^T X reads dY [T, N] and X [T, K] as they lie; dX = dY W reads W [N, K] as it lies),
+// so the training step needs no transposed copies.  A stage then holds [64-wide block][64 contraction rows][128 B] per
+// operand (SWIZZLE_128B, one 2-D TMA box {64 features, 64 rows} per block); the UMMA descriptors walk it with start + 2048 B per K = 16
+// step, SBO = 1024 (8-row atom), LBO = 8192 (next 64-wide block) and the MN-major bits of the instruction descriptor.
+template <int BN, int EPI, bool OUT_BF16, int AMN = 0, int BMN = 0>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const GemmParams p) {
@@ -241,7 +246,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
   const int num_m = (p.M + kBM - 1) / kBM;
   const int num_n = p.N / BN;
   const int num_tiles = num_m * num_n;
-  const int num_kb = p.K / kBK;
+  const int num_kb = (p.K + kBK - 1) / kBK;             // a ragged K tail only with two MN-major operands (TMA zero-fills both)
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -280,8 +285,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         uint8_t* sb = sa + Cfg::kABytes;
         if (elect_one()) {
           mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
-          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kBK, n_blk * BN);
+          if (AMN) {        // one {64 features, 64 contraction rows} box per 64-wide block, 8 KB apart
+#pragma unroll
+            for (int b = 0; b < kBM / 64; ++b) tma_load_2d(sa + b * 8192, &tmap_a, &full_bar[stage], m_blk * kBM + b * 64, kb * kBK);
+          } else {
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
+          }
+          if (BMN) {
+#pragma unroll
+            for (int b = 0; b < BN / 64; ++b) tma_load_2d(sb + b * 8192, &tmap_b, &full_bar[stage], n_blk * BN + b * 64, kb * kBK);
+          } else {
+            tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kBK, n_blk * BN);
+          }
         }
         __syncwarp();
         if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
@@ -289,7 +304,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (whole warp, one elected lane issues)
-    constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, 0, 0);
+    constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, AMN, BMN);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -303,14 +318,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
         const uint32_t sb = sa + Cfg::kABytes;
-        const uint64_t da = umma_desc_sw128(sa, 16, 1024);
-        const uint64_t db = umma_desc_sw128(sb, 16, 1024);
+        // K-major: +32 bytes per K = 16 slice inside the 128 B swizzle atom -> +2 in the (addr >> 4) field;
+        // MN-major: +16 contraction rows x 128 B = 2048 bytes -> +128
+        const uint64_t da = AMN ? umma_desc_sw128(sa, 8192, 1024) : umma_desc_sw128(sa, 16, 1024);
+        const uint64_t db = BMN ? umma_desc_sw128(sb, 8192, 1024) : umma_desc_sw128(sb, 16, 1024);
         if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            // +32 bytes per K=16 slice inside the 128B swizzle atom -> +2 in the (addr >> 4) field
-            umma_ss(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          }
+          for (int k = 0; k < kBK / 16; ++k)
+            umma_ss(tmem_d, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0 ? 1u : 0u);
           umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
@@ -476,10 +491,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 // ---------------------------------------------------------------------------------------------- host
 extern int g_launch_count;
 
-template <int BN, int EPI, bool OUT_BF16>
+template <int BN, int EPI, bool OUT_BF16, int AMN = 0, int BMN = 0>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
   using Cfg = GemmCfg<BN>;
-  auto kern = gemm_tc_kernel<BN, EPI, OUT_BF16>;
+  auto kern = gemm_tc_kernel<BN, EPI, OUT_BF16, AMN, BMN>;
   static bool configured = false;  // per instantiation
   if (!configured) {
     SR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
@@ -511,7 +526,72 @@ static int dispatch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const Gem
   return fail(SR_ERR_SHAPE, "sr_gemm_bf16: unknown epilogue kind %d", e.kind);
 }
 
+// Linear gradients (operands as they lie in memory): only the epilogues those use.
+template <int BN, int AMN, int BMN>
+static int dispatch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+  const sr_epilogue_t& e = p.e;
+  switch (e.kind) {
+    case SR_EPI_BIAS:
+      return e.out_bf16 ? launch_gemm<BN, SR_EPI_BIAS, true, AMN, BMN>(ta, tb, p, st)
+                        : launch_gemm<BN, SR_EPI_BIAS, false, AMN, BMN>(ta, tb, p, st);
+    case SR_EPI_LS_RESIDUAL:
+      return launch_gemm<BN, SR_EPI_LS_RESIDUAL, false, AMN, BMN>(ta, tb, p, st);
+  }
+  return fail(SR_ERR_SHAPE, "sr_gemm_bf16_t: epilogue kind %d is not available with MN-major operands (BIAS, LS_RESIDUAL)", e.kind);
+}
+
 }  // namespace sr
+
+extern "C" int sr_gemm_bf16_t(const void* A, int64_t lda, int32_t a_mn_major, const void* W, int64_t ldw, int32_t b_mn_major,
+                              int64_t M, int64_t N, int64_t K, const sr_epilogue_t* epi, void* stream) {
+  using namespace sr;
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(A && W && epi && epi->out, "sr_gemm_bf16_t: null pointer");
+  SR_REQUIRE(b_mn_major == 1 && (a_mn_major == 0 || a_mn_major == 1),
+             "sr_gemm_bf16_t: W must be MN-major ([K, N] rows); A K-major or MN-major (plain layouts: sr_gemm_bf16)");
+  SR_REQUIRE(M > 0 && N > 0 && K > 0 && M < (1ll << 31) && N < (1ll << 31) && K < (1ll << 31), "sr_gemm_bf16_t: bad sizes");
+  SR_REQUIRE(N % 128 == 0, "sr_gemm_bf16_t: N=%lld must be a multiple of 128", (long long)N);
+  if (a_mn_major) SR_REQUIRE(M % 64 == 0 && lda >= M, "sr_gemm_bf16_t: MN-major A needs M %% 64 == 0 and lda >= M");
+  else SR_REQUIRE(K % kBK == 0 && lda >= K, "sr_gemm_bf16_t: K-major A needs K %% 64 == 0 and lda >= K");
+  SR_REQUIRE(ldw >= N && lda % 8 == 0 && ldw % 8 == 0, "sr_gemm_bf16_t: row strides must be multiples of 8 and cover the rows");
+  SR_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(W) & 15) == 0,
+             "sr_gemm_bf16_t: A and W must be 16-byte aligned");
+  const sr_epilogue_t& e = *epi;
+  const int out_elt = (e.kind == SR_EPI_LS_RESIDUAL || !e.out_bf16) ? 4 : 2;
+  SR_REQUIRE((reinterpret_cast<uintptr_t>(e.out) & 15) == 0 && (e.ldo * out_elt) % 16 == 0 && e.ldo >= N,
+             "sr_gemm_bf16_t: out must be 16-byte aligned with a 16-byte multiple row stride >= N");
+  if (e.kind == SR_EPI_LS_RESIDUAL)
+    SR_REQUIRE(e.resid && (reinterpret_cast<uintptr_t>(e.resid) & 15) == 0 && e.ldr % 4 == 0,
+               "sr_gemm_bf16_t: LS_RESIDUAL needs a 16-byte aligned fp32 residual");
+  const int64_t tiles256 = ((M + kBM - 1) / kBM) * (N / 256);
+  const int BN = (N % 256 == 0 && tiles256 >= kNumSMs / 2) ? 256 : 128;
+  CUtensorMap ta, tb;
+  if (a_mn_major) {       // [K, M] rows: boxes of 64 features x 64 contraction rows (rows / features past the end zero-fill)
+    uint64_t dims[2] = {static_cast<uint64_t>(M), static_cast<uint64_t>(K)};
+    uint64_t strides[1] = {static_cast<uint64_t>(lda) * 2};
+    uint32_t box[2] = {64, kBK};
+    if (int rc = make_tmap_bf16(&ta, A, 2, dims, strides, box)) return rc;
+  } else {
+    uint64_t dims[2] = {static_cast<uint64_t>(K), static_cast<uint64_t>(M)};
+    uint64_t strides[1] = {static_cast<uint64_t>(lda) * 2};
+    uint32_t box[2] = {kBK, kBM};
+    if (int rc = make_tmap_bf16(&ta, A, 2, dims, strides, box)) return rc;
+  }
+  {
+    uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(K)};
+    uint64_t strides[1] = {static_cast<uint64_t>(ldw) * 2};
+    uint32_t box[2] = {64, kBK};
+    if (int rc = make_tmap_bf16(&tb, W, 2, dims, strides, box)) return rc;
+  }
+  GemmParams p;
+  p.M = static_cast<int>(M);
+  p.N = static_cast<int>(N);
+  p.K = static_cast<int>(K);
+  p.e = e;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (a_mn_major) return BN == 256 ? dispatch_gemm_t<256, 1, 1>(ta, tb, p, st) : dispatch_gemm_t<128, 1, 1>(ta, tb, p, st);
+  return BN == 256 ? dispatch_gemm_t<256, 0, 1>(ta, tb, p, st) : dispatch_gemm_t<128, 0, 1>(ta, tb, p, st);
+}
 
 extern "C" int sr_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int64_t M, int64_t N, int64_t K,
                             const sr_epilogue_t* epi, void* stream) {

@@ -188,6 +188,34 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], out: to
     return out
 
 
+def gemm_t(a: torch.Tensor, w: torch.Tensor, out: torch.Tensor, a_mn_major: bool, accumulate: bool = False) -> torch.Tensor:
+    """The tensor-core GEMM on operands as the Linear gradients find them (sr_gemm_bf16_t), no transposed copies:
+        a_mn_major False:  out[M, N] = a[M, K] @ w[K, N]            (dX = dY W,  w = the Linear's weight [N_out, K_in])
+        a_mn_major True:   out[M, N] = a[K, M]^T @ w[K, N]          (dW = dY^T X, K = token rows, any length)
+    bf16 operands; out bf16 or fp32; accumulate (fp32 out only): out += (exact fp32 accumulate)."""
+    _rows2d(a, torch.bfloat16, "a")
+    _rows2d(w, torch.bfloat16, "w")
+    _rows2d(out, out.dtype, "out")
+    K, N = w.shape
+    M = a.shape[1] if a_mn_major else a.shape[0]
+    if (a.shape[0] if a_mn_major else a.shape[1]) != K or out.shape != (M, N):
+        raise ValueError(f"sailrecon_b200: gemm_t shape mismatch a{tuple(a.shape)} w{tuple(w.shape)} out{tuple(out.shape)}")
+    e = SrEpilogue()
+    e.out_bf16 = int(out.dtype == torch.bfloat16)
+    e.out, e.ldo = out.data_ptr(), out.stride(0)
+    if accumulate:
+        if out.dtype != torch.float32:
+            raise ValueError("sailrecon_b200: gemm_t accumulates into fp32 outputs only")
+        e.kind, e.resid, e.ldr, e.exact_residual = SR_EPI_LS_RESIDUAL, out.data_ptr(), out.stride(0), 1
+    else:
+        e.kind = SR_EPI_BIAS
+    t = _Timed("gemm_tc", 2.0 * M * N * K, (M * K + N * K) * 2 + M * N * out.element_size())
+    _lib.check(_lib.load().sr_gemm_bf16_t(a.data_ptr(), a.stride(0), int(a_mn_major), w.data_ptr(), w.stride(0), 1, M, N, K,
+                                          C.byref(e), _stream()), "gemm_t")
+    t.done()
+    return out
+
+
 # ------------------------------------------------------------------------------------------------ attention
 def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: Optional[torch.Tensor], num_heads: int,
               head_dim: int, batch: int, q_len: int, kv_len: int, q_batch_stride: int = 0, kv_batch_stride: int = 0,

@@ -9,8 +9,9 @@ only the block input survives the forward pass, the block is re-run inside backw
     backward pass     saved = block_forward_saving(blk, x, ...)   (re-run with un-fused epilogues that keep u, z, raw qkv, lse)
                       dx = block_backward(blk, saved, dy, grads)
 
-Every contraction runs on the tcgen05 kernels: dX = dY W and dW = dY^T X are sr_gemm_bf16 calls on transposed bf16
-operands (ops.transpose_bf16), attention on sr_attn_bwd_bf16; the rest are the row kernels of csrc/train_rows.cu.
+Every contraction runs on the tcgen05 kernels: dX = dY W and dW = dY^T X read dY, X and W as they lie in memory
+(sr_gemm_bf16_t: MN-major operand descriptors, no transposed copies), attention on sr_attn_bwd_bf16; the rest are the row
+kernels of csrc/train_rows.cu.
 Parameter gradients are accumulated in fp32 into `grads[param]` (the role of .grad under DDP, train_imc.py:472).
 There is no torch fallback.  Blocks whose attention call reads an external K/V prefix (the reloc blocks: query frames
 against the scene tokens, aggregator.py:672-741) return the prefix gradient in `saved.dprefix`; scene_forward_saving /
@@ -138,32 +139,44 @@ def _acc(grads: Dict[nn.Parameter, torch.Tensor], p: Optional[nn.Parameter]) -> 
 
 
 def linear_backward(lin: nn.Module, a_in: torch.Tensor, dz: torch.Tensor, grads: Dict[nn.Parameter, torch.Tensor],
-                    need_input_grad: bool = True) -> Optional[torch.Tensor]:
+                    need_input_grad: bool = True, use_transposes: bool = False) -> Optional[torch.Tensor]:
     """Gradients of z = a_in W^T + b (nn.Linear): dW += dz^T a_in, db += colsum(dz) (fp32 accumulators in `grads`), returns
-    d a_in = dz W (bf16).  a_in [T, K] bf16, dz [T, N] bf16 — both GEMMs on the tcgen05 kernel."""
+    d a_in = dz W (bf16).  a_in [T, K] bf16, dz [T, N] bf16 — both GEMMs on the tcgen05 kernel, reading dz, a_in and W AS THEY
+    LIE in memory (MN-major operand descriptors, sr_gemm_bf16_t): no transposed copies, and dW accumulates in fp32 straight
+    into the gradient bucket.  use_transposes=True is the round-1 path (explicit bf16 transposes + the K-major kernel), kept
+    as the A/B reference of tests/test_train_gpu.py."""
     T, K = a_in.shape
     N = dz.shape[1]
     dev = a_in.device
     gb = _acc(grads, lin.bias) if lin.bias is not None else None
-    dzT = ops.transpose_bf16(dz, colsum=gb)                        # [N, T_pad]; db += colsum(dz) in the same pass
-    aT = ops.transpose_bf16(a_in)                                  # [K, T_pad]
     gw = _acc(grads, lin.weight)
-    if N % 128 == 0 and K % 128 == 0:
-        fresh = getattr(grads, "fresh", None)
-        if fresh is not None and lin.weight in fresh:              # first contribution since zero_grad: write, do not add
-            fresh.discard(lin.weight)
+    if N % 128 or K % 128:
+        raise NotImplementedError("sailrecon_b200: Linear gradients need in / out features that are multiples of 128")
+    fresh = getattr(grads, "fresh", None)
+    first = fresh is not None and lin.weight in fresh              # first contribution since zero_grad: write, do not add
+    if first:
+        fresh.discard(lin.weight)
+    if use_transposes:
+        dzT = ops.transpose_bf16(dz, colsum=gb)                    # [N, T_pad]; db += colsum(dz) in the same pass
+        aT = ops.transpose_bf16(a_in)                              # [K, T_pad]
+        if first:
             ops.gemm(dzT, aT, None, gw.view(N, K), kind=SR_EPI_BIAS)   # [N, T_pad] x [K, T_pad]^T
         else:
             tmp = torch.empty(N, K, dtype=torch.float32, device=dev)
             ops.gemm(dzT, aT, None, tmp, kind=SR_EPI_BIAS)
             gw.view(N, K).add_(tmp)
     else:
-        raise NotImplementedError("sailrecon_b200: Linear gradients need in / out features that are multiples of 128")
+        if gb is not None:
+            ops.colsum(dz, None, gb, accumulate=True)
+        ops.gemm_t(dz, a_in, gw.view(N, K), a_mn_major=True, accumulate=not first)    # dW[N, K] (+)= dz[T, N]^T a_in[T, K]
     if not need_input_grad:
         return None
-    wT = engine._cached(lin, "wT_bf16", lin.weight, lambda w: ops.transpose_bf16(engine.weight_bf16(lin)))   # [K, N]
     da = torch.empty(T, K, dtype=BF, device=dev)
-    ops.gemm(dz, wT, None, da, kind=SR_EPI_BIAS)
+    if use_transposes:
+        wT = engine._cached(lin, "wT_bf16", lin.weight, lambda w: ops.transpose_bf16(engine.weight_bf16(lin)))   # [K, N]
+        ops.gemm(dz, wT, None, da, kind=SR_EPI_BIAS)
+    else:
+        ops.gemm_t(dz, engine.weight_bf16(lin), da, a_mn_major=False)                # da[T, K] = dz[T, N] W[N, K]
     return da
 
 
@@ -621,11 +634,10 @@ def _proj_wgrad(proj: nn.Module, a: torch.Tensor, dz: torch.Tensor, grads: Dict[
     """Conv2d(3, D, 14, stride 14) as a Linear on im2col rows: dW += dz^T a (a zero-padded to Kp columns), db += colsum(dz)."""
     D = dz.shape[1]
     K = proj.weight[0].numel()
-    gb = _acc(grads, proj.bias) if proj.bias is not None else None
-    dzT = ops.transpose_bf16(dz, colsum=gb)
-    aT = ops.transpose_bf16(a)                                           # [Kp, T_pad]
+    if proj.bias is not None:
+        ops.colsum(dz, None, _acc(grads, proj.bias), accumulate=True)
     tmp = torch.empty(D, a.shape[1], dtype=torch.float32, device=dz.device)
-    ops.gemm(dzT, aT, None, tmp, kind=SR_EPI_BIAS)
+    ops.gemm_t(dz, a, tmp, a_mn_major=True)                              # [D, Kp] = dz[T, D]^T a[T, Kp], operands in place
     _acc(grads, proj.weight).view(D, K).add_(tmp[:, :K])
 
 

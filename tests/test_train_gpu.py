@@ -149,10 +149,13 @@ def test_qknorm_rope_fwd_equals_fused_epilogue_and_bwd_matches_autograd():
         assert rel_l2(got.cpu(), want.grad.cpu()) < 2e-3
 
 
-def test_linear_backward_on_tensor_cores():
+@pytest.mark.parametrize("T,K,N", [(333, 1024, 3072), (2748, 1024, 4096), (1374, 4096, 1024), (70, 1024, 1024)])
+def test_linear_backward_on_tensor_cores(T, K, N):
+    """dW = dz^T a and da = dz W on the tensor-core GEMM reading its operands in place (MN-major descriptors, sr_gemm_bf16_t)
+    against fp32 torch, and against the round-1 path (explicit transposes + the K-major kernel): same products, same fp32
+    accumulation order along the token axis -> identical up to the last bit of the accumulate."""
     import torch.nn as nn
     from sailrecon_b200 import train
-    T, K, N = 333, 1024, 3072
     lin = nn.Linear(K, N).to(DEV)
     a = _randn(T, K, seed=17).to(BF)
     dz = _randn(T, N, seed=18).to(BF)
@@ -162,8 +165,12 @@ def test_linear_backward_on_tensor_cores():
     assert rel_l2(da.float().cpu(), (dz.float() @ w).cpu()) < 6e-3
     assert rel_l2(grads[lin.weight].cpu(), (dz.float().t() @ a.float()).cpu()) < 1e-3
     assert rel_l2(grads[lin.bias].cpu(), dz.float().sum(0).cpu()) < 1e-4
-    train.linear_backward(lin, a, dz, grads)                                   # accumulates
+    old = {}
+    da_old = train.linear_backward(lin, a, dz, old, use_transposes=True)
+    assert rel_l2(da.float(), da_old.float()) < 1e-6 and rel_l2(grads[lin.weight], old[lin.weight]) < 1e-6
+    train.linear_backward(lin, a, dz, grads)                                   # accumulates (exact fp32 add in the epilogue)
     assert rel_l2(grads[lin.weight].cpu(), (2 * dz.float().t() @ a.float()).cpu()) < 1e-3
+    assert rel_l2(grads[lin.bias].cpu(), 2 * dz.float().sum(0).cpu()) < 1e-4
 
 
 # ------------------------------------------------------------------------------------------------ whole block
