@@ -127,8 +127,9 @@ typedef struct sr_attn {
    * (lse_pad >= q_len, a multiple of 64; the caller pre-fills the buffer with +inf so padding rows stay +inf).
    * NULL = inference.  Consumed by sr_attn_bwd_bf16.  bf16 tensor-core path only.                           */
   float* lse; int64_t lse_pad;
-  /* kernel variant of the tcgen05 path: 0 = chosen per launch by wave quantisation (default), 3 / 4 = force the
-   * three- / four-query-tile kernel.  Every variant computes the same function; ignored by the fp32 path.    */
+  /* kernel variant of the tcgen05 path: 0 = default (four-tile kernel, mixed four- / three-tile CTAs, grid order chosen per
+   * launch), 3 = three-tile kernel, 4 = uniform four-tile CTAs, 5 / 6 = mixed CTAs with the heavy-first / row-major grid
+   * order forced (A/B timing).  Every variant computes the same function; ignored by the fp32 path.          */
   int32_t variant;
   /* optional scratch for split-KV (under-filled launches: few query rows against a long K/V range, e.g. one query frame
    * against a cached 100-anchor scene): sr_attn_workspace_bytes() says how much this call can use (0 = none); NULL or

@@ -64,7 +64,7 @@ def bench(name, batch, L, prefix_len=0, iters=10, check=False, variant=0):
 
 if __name__ == "__main__":
     check = "--check" in sys.argv
-    for variant in (0, 4, 3):                      # 0 = mixed four- / three-tile decomposition (default), 4 / 3 = uniform
+    for variant in (0, 5, 6, 4, 3):                      # 0 = mixed four- / three-tile decomposition (default), 4 / 3 = uniform
         bench("global16", 1, 16 * 1374, check=check, variant=variant)
         bench("frame32", 32, 1374, check=check, variant=variant)
         bench("reloc16", 16, 1374, prefix_len=16 * 305, check=check, variant=variant)

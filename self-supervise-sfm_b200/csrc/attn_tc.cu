@@ -505,12 +505,12 @@ extern "C" int sr_attn_fwd_bf16(const sr_attn_t* a, void* stream) {
     if (const char* env = dbg_env("SR_ATTN_POLY")) poly = atoi(env);
     if (a->lse != nullptr) {
       SR_REQUIRE(a->lse_pad >= a->q_len && a->lse_pad % 64 == 0, "sr_attn_fwd_bf16: lse_pad must be a multiple of 64 >= q_len");
-      SR_REQUIRE(variant == 3 || variant == 4, "sr_attn_fwd_bf16: the two-tile kernel (SR_ATTN_KERNEL=2) does not write lse");
+      SR_REQUIRE(variant >= 3 && variant <= 6, "sr_attn_fwd_bf16: the two-tile kernel (SR_ATTN_KERNEL=2) does not write lse");
     }
-    if (variant == 4) return attn_tc4_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
+    if (variant == 4 || variant == 5 || variant == 6) return attn_tc4_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
     if (variant == 3) return attn_tc3_launch(a, poly, reinterpret_cast<cudaStream_t>(stream));
 #ifndef SR_DEBUG
-    return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16: kernel variant must be 0 (auto), 3 or 4 (got %d)", variant);
+    return fail(SR_ERR_SHAPE, "sr_attn_fwd_bf16: kernel variant must be 0 (auto) or 3 .. 6 (got %d)", variant);
 #endif
   }
 #ifdef SR_DEBUG

@@ -66,6 +66,10 @@ struct Attn4Params {
   // (16-anchor global shape: 172 tiles per head = 37 x 4 + 8 x 3 -> 592 heavy CTAs = exactly 4 waves of 148 SMs + 128 light
   // ones = 19 tile-steps of makespan instead of the 20 of 688 uniform four-tile CTAs; chosen per shape by choose_mix()).
   int n_rows, n4, n3, batch;
+  // row_major = 1: a row's CTAs are adjacent in the grid (its K/V stay L2-resident between them) — used when the launch has
+  // at least one row per SM, where K/V of all rows exceed the L2 and the tail wave is short anyway (frame / reloc shapes:
+  // the heavy-first order made every light CTA re-read its row's K/V from HBM, +50 % DRAM traffic, profiles/r02_ncu_attn_tc.txt)
+  int row_major;
   // Split-KV (under-filled launches, e.g. ONE query frame against a 100-anchor scene prefix = 48 CTAs on 148 SMs): the
   // K/V tile range is cut into n_split chunks, each (row, query-group, chunk) is its own CTA writing its partial
   // (m, l, un-normalised O) into per-chunk carry buffers inside the caller's workspace; attn_split_merge_kernel combines them.
@@ -97,7 +101,13 @@ attn_tc4_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constan
   const int split = blockIdx.x / base_ctas;                          // 0 unless the launch is split over the K/V range
   {
     const int lin = blockIdx.x - split * base_ctas, heavy = p.n_rows * p.n4;
-    if (lin < heavy) {
+    if (p.row_major) {
+      const int per_row = p.n4 + p.n3;
+      row = lin / per_row;
+      const int x = lin - row * per_row;
+      q0 = x < p.n4 ? x * 512 : p.n4 * 512 + (x - p.n4) * 384;
+      nq_cap = x < p.n4 ? 4 : 3;
+    } else if (lin < heavy) {
       row = lin / p.n4;
       q0 = (lin - row * p.n4) * 512;
       nq_cap = 4;
@@ -576,6 +586,7 @@ int attn_tc4_launch(const sr_attn_t* a, int poly, cudaStream_t st) {
   p.n_rows = a->num_heads * a->batch;
   const int t_tiles = static_cast<int>((a->q_len + 127) / 128);
   choose_mix(t_tiles, p.n_rows, num_sms, a->variant == 4, &p.n4, &p.n3);
+  p.row_major = a->variant == 6 ? 1 : (a->variant == 5 ? 0 : (p.n_rows >= num_sms ? 1 : 0));
   const int64_t base_ctas = static_cast<int64_t>(p.n_rows) * (p.n4 + p.n3);
   SR_REQUIRE(base_ctas < (1ll << 31), "sr_attn_fwd_bf16: too many CTAs");
   p.n_split = 1;

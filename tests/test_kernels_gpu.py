@@ -245,7 +245,7 @@ def test_attention_bf16_carry_equals_single_pass():
     assert rel_l2(two.float().cpu(), one.float().cpu()) < 4e-3
 
 
-@pytest.mark.parametrize("variant", [0, 3, 4])
+@pytest.mark.parametrize("variant", [0, 3, 4, 5, 6])
 def test_attention_bf16_every_kernel_variant(variant, monkeypatch):
     """sr_attn_fwd_bf16 picks the three- or four-tile kernel per launch by wave quantisation (attn_tc.cu); sr_attn_t.variant
     forces one.  Every variant must pass the segment, ragged-tail, prefix and carry cases on its own: partial last query
