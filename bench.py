@@ -28,6 +28,8 @@ Workload "ring" (BASELINE.json configs[3]): the sequence-sharded global-attentio
 Workload "train" (BASELINE.json configs[4]): one training step of the 3 x 24 aggregator blocks on a 24-frame scene
 (12 anchors + 12 queries, train_imc.py shape): zero_grad, forward, backward, per-layer NCCL gradient
 all-reduce across the ranks (one scene per rank, DDP's decomposition), Adam — see sailrecon_b200/train.py.
+Workload "dense": the whole SailRecon.forward (aggregator + camera head + both DPT heads + pose / unprojection) with the
+reference's own DPTHead timed beside ours on the same tokens.
 Workload "reloc": the demo_imc.py two-phase localisation (tmp_forward over --anchors frames, then one reloc call per
 query image against the HBM-resident scene K/V cache); ms per localised image.
 
@@ -530,13 +532,146 @@ def train_line(r: dict, world: int) -> dict:
     }
 
 
+# ------------------------------------------------------------------------------------------------ whole SailRecon.forward
+def bench_dense(args, rank: int, world: int, local: int) -> None:
+    """SailRecon.forward (sail_recon.py:70-159) on the kernel library: aggregator (autocast bf16) + camera head + pose ->
+    extrinsics / intrinsics + the two DPT dense heads (point map, depth + confidence) + depth unprojection, all fp32 after the
+    aggregator as the reference runs them (autocast disabled, :119).  16 anchors + 16 queries at 518 px, one scene per rank.
+    Also times the reference's own DPTHead (oracle/_ref, cuDNN with its default TF32) on the same tokens."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a B200: sailrecon_b200 has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from sailrecon_b200 import ops
+    from sailrecon_b200.heads import DPTHead
+    from sailrecon_b200.utils import pose_encoding_to_extri_intri, unproject_depth_map_to_point_map
+    Na = Nq = args.frames // 2
+    S, H, W = Na + Nq, args.size, args.size
+    agg, head = build_models(dev)
+    torch.manual_seed(1)
+    with torch.device(dev):
+        point_head = DPTHead(dim_in=2 * C, output_dim=4, activation="inv_log", conf_activation="expp1").eval()
+        depth_head = DPTHead(dim_in=2 * C, output_dim=2, activation="exp", conf_activation="expp1").eval()
+    host_images = torch.rand(1, S, 3, H, W, generator=torch.Generator().manual_seed(1 + rank)).pin_memory()
+    images = host_images.to(dev)
+
+    def forward(imgs):
+        with torch.no_grad():
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                out, psi, cam = agg(imgs, list(range(Na)), list(range(Na, S)), fix_rank=300)
+            with torch.autocast("cuda", enabled=False):
+                poses = head(out, cam)
+                ext, intr = pose_encoding_to_extri_intri(poses[-1], (H, W))
+                q_imgs = imgs[:, Na:]
+                xyz, xyz_cnf = point_head(out, images=q_imgs, patch_start_idx=psi)
+                dpt, dpt_cnf = depth_head(out, images=q_imgs, patch_start_idx=psi)
+                pts = unproject_depth_map_to_point_map(dpt[0], ext[0], intr[0], as_numpy=False)
+        return out, ext, xyz, dpt, pts
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        agg.generator.manual_seed(1234)
+        forward(images)
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    n0 = ops.num_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        agg.generator.manual_seed(1234)
+        out, ext, xyz, dpt, pts = forward(images)
+    e1.record()
+    barrier()
+    launches = ops.num_kernel_launches() - n0
+    clk = clocks.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    ops.PROFILE = []
+    agg.generator.manual_seed(1234)
+    forward(images)
+    barrier()
+    records, ops.PROFILE = ops.PROFILE, None
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        agg.generator.manual_seed(1234)
+        out, ext, xyz, dpt, pts = forward(host_images.to(dev, non_blocking=True))
+        host_ext, host_depth = ext.cpu(), dpt.cpu()
+    e1.record()
+    barrier()
+    ms_e2e = e0.elapsed_time(e1) / args.steps
+    # the dense heads alone, ours vs the reference's module (cuDNN, TF32 allowed = its default) on the same tokens
+    def time_heads(fn, n=3):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(n):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / n
+    q_imgs = images[:, Na:]
+    with torch.no_grad():
+        ours_ms = time_heads(lambda: (point_head(out, images=q_imgs, patch_start_idx=5), depth_head(out, images=q_imgs, patch_start_idx=5)))
+    lib = {"unavailable": "oracle/_ref absent"}
+    if reference_classes() is not None and rank == 0:
+        from sailrecon.heads.dpt_head import DPTHead as RefDPT
+        with torch.device(dev):
+            r_point = RefDPT(dim_in=2 * C, output_dim=4, activation="inv_log", conf_activation="expp1").eval().to(dev)
+            r_depth = RefDPT(dim_in=2 * C, output_dim=2, activation="exp", conf_activation="expp1").eval().to(dev)
+        r_point.load_state_dict(point_head.state_dict())
+        r_depth.load_state_dict(depth_head.state_dict())
+        with torch.no_grad():
+            ref_ms = time_heads(lambda: (r_point(out, images=q_imgs, patch_start_idx=5), r_depth(out, images=q_imgs, patch_start_idx=5)))
+            rp, _ = r_point(out, images=q_imgs, patch_start_idx=5)
+            op_, _ = point_head(out, images=q_imgs, patch_start_idx=5)
+        lib = {"ms_both_heads": ref_ms, "what": "reference DPTHead x 2 (oracle/_ref) on the same tokens: cuDNN / cuBLAS fp32 with TF32 allowed "
+               "(torch default)", "point_map_rel_l2_vs_ours": float((op_.double() - rp.double()).norm() / rp.double().norm())}
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(tt[0]), float(tt[1])
+    if rank == 0:
+        prof = summarize_profile(records)
+        kern = {k: {"launches_per_step": v["launches"], "ms_per_step": v["ms"],
+                    "tflops": (v["flops"] / (v["ms"] * 1e-3) / 1e12) if v["flops"] else None,
+                    "gbs": v["bytes"] / (v["ms"] * 1e-3) / 1e9} for k, v in prof.items()}
+        peak_tf, peak_src = load_peak_tf()
+        line = {"metric": f"SailRecon.forward frames/s at N={S} ({H}px): aggregator + camera head + 2 DPT heads + unprojection",
+                "value": world * S / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16 aggregator / fp32 heads",
+                "data": "synthetic",
+                "config": {"workload": f"dense{S}: {Na} anchors + {Nq} queries, {H}x{W}, fix_rank 300, SailRecon.forward semantics "
+                                       "(sail_recon.py:70-159), dense maps for the query frames, one scene per GPU",
+                           "l2": "per-layer activations and the im2col rows of the dense heads exceed the 126 MB L2; no flush needed"},
+                "e2e": {"value": world * S / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": host_images.numel() * 4,
+                        "d2h_bytes_per_step": int(host_ext.numel() * 4 + host_depth.numel() * 4)},
+                "gpu_launches": launches, "clocks": clk, "kernels": kern,
+                "dense_heads_ms": ours_ms, "dense_heads_library_baseline": lib,
+                "roofline": {"bound": "tensor", "kernel": "attn_tc", "achieved": kern["attn_tc"]["tflops"], "peak": peak_tf,
+                             "unit": "TFLOP/s", "frac": kern["attn_tc"]["tflops"] / peak_tf, "traffic": None, "peak_source": peak_src},
+                "outputs_finite": bool(torch.isfinite(host_ext).all() and torch.isfinite(xyz).all())}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="agg32", choices=["agg32", "imc", "ring", "scene", "train", "reloc"])
+    ap.add_argument("--workload", default="agg32", choices=["agg32", "imc", "ring", "scene", "train", "reloc", "dense"])
     ap.add_argument("--anchors", type=int, default=100, help="workload imc / reloc: anchor frames (build the scene tokens)")
     ap.add_argument("--queries", type=int, default=200, help="workload imc / reloc: query frames localised against the anchors")
     ap.add_argument("--frames", type=int, default=32)
@@ -572,6 +707,9 @@ def main():
         return
     if args.workload == "train":
         bench_train(args, rank, world, local)
+        return
+    if args.workload == "dense":
+        bench_dense(args, rank, world, local)
         return
     if args.workload == "reloc":
         from sailrecon_b200 import localize
