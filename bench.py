@@ -634,8 +634,19 @@ def bench_dense(args, rank: int, world: int, local: int) -> None:
             ref_ms = time_heads(lambda: (r_point(out, images=q_imgs, patch_start_idx=5), r_depth(out, images=q_imgs, patch_start_idx=5)))
             rp, _ = r_point(out, images=q_imgs, patch_start_idx=5)
             op_, _ = point_head(out, images=q_imgs, patch_start_idx=5)
-        lib = {"ms_both_heads": ref_ms, "what": "reference DPTHead x 2 (oracle/_ref) on the same tokens: cuDNN / cuBLAS fp32 with TF32 allowed "
-               "(torch default)", "point_map_rel_l2_vs_ours": float((op_.double() - rp.double()).norm() / rp.double().norm())}
+        old_tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+        torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+        try:
+            with torch.no_grad():
+                ref32_ms = time_heads(lambda: (r_point(out, images=q_imgs, patch_start_idx=5), r_depth(out, images=q_imgs, patch_start_idx=5)))
+                rp32, _ = r_point(out, images=q_imgs, patch_start_idx=5)
+        finally:
+            torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old_tf32
+        rel = lambda a, b: float((a.double() - b.double()).norm() / b.double().norm())
+        lib = {"ms_both_heads_tf32": ref_ms, "ms_both_heads_fp32": ref32_ms,
+               "what": "reference DPTHead x 2 (oracle/_ref) on the same tokens through cuDNN / cuBLAS: with TF32 allowed (torch's default, "
+                       "10-bit mantissa) and with TF32 off (the fp32 semantics the 1e-4 parity check is made against)",
+               "point_map_rel_l2": {"ours_vs_reference_fp32": rel(op_, rp32), "reference_tf32_vs_its_fp32": rel(rp, rp32)}}
     if world > 1:
         tt = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)

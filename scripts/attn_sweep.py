@@ -62,8 +62,46 @@ def bench(name, batch, L, prefix_len=0, iters=10, check=False, variant=0):
     print(json.dumps(rec), flush=True)
 
 
+def interleaved(shapes, variants, reps=6, iters=8):
+    """A/B that is fair under clock / power drift: the variants alternate inside every repetition (a sweep that times one
+    variant after the other favours whichever runs first, at boost clocks); reports the median of the per-repetition times."""
+    import statistics
+    for name, batch, L, prefix_len in shapes:
+        T = batch * L
+        g = torch.Generator(device=dev).manual_seed(0)
+        qkvs = [(torch.randn(T, 3 * C, device=dev, generator=g)).to(torch.bfloat16) for _ in range(4 if T * 3 * C * 2 < 600e6 else 1)]
+        pre = torch.randn(prefix_len, 2 * C, device=dev, generator=g).to(torch.bfloat16) if prefix_len else None
+        out = torch.empty(T, C, device=dev, dtype=torch.bfloat16)
+
+        def run(i, variant):
+            qkv = qkvs[i % len(qkvs)]
+            ops.attention(qkv[:, :C], qkv[:, C:2 * C], qkv[:, 2 * C:], out, H, D, batch, L, L, L, L,
+                          prefix_k=None if pre is None else pre[:, :C], prefix_v=None if pre is None else pre[:, C:],
+                          prefix_len=prefix_len, variant=variant)
+        for i in range(30):                                  # reach the steady power / clock state first
+            run(i, variants[i % len(variants)])
+        torch.cuda.synchronize()
+        times = {v: [] for v in variants}
+        for rep in range(reps):
+            for v in (variants if rep % 2 == 0 else variants[::-1]):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for i in range(iters):
+                    run(i, v)
+                e1.record()
+                torch.cuda.synchronize()
+                times[v].append(e0.elapsed_time(e1) / iters)
+        flops = 4.0 * batch * L * (prefix_len + L) * C
+        print(json.dumps({"shape": name, "interleaved": True,
+                          "tflops_median": {str(v): round(flops / statistics.median(t) / 1e9, 1) for v, t in times.items()}}), flush=True)
+
+
 if __name__ == "__main__":
     check = "--check" in sys.argv
+    if "--interleaved" in sys.argv:
+        interleaved([("global16", 1, 16 * 1374, 0), ("frame32", 32, 1374, 0), ("reloc16", 16, 1374, 16 * 305), ("global12", 1, 12 * 1374, 0)],
+                    [4, 5, 6, 3])
+        sys.exit(0)
     for variant in (0, 5, 6, 4, 3):                      # 0 = mixed four- / three-tile decomposition (default), 4 / 3 = uniform
         bench("global16", 1, 16 * 1374, check=check, variant=variant)
         bench("frame32", 32, 1374, check=check, variant=variant)
