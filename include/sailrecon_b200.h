@@ -175,9 +175,6 @@ typedef struct sr_attn_bwd {
   int64_t q_len, q_batch_stride;
   int64_t kv_len, kv_batch_stride;
   float scale;
-  /* 0 = default; 10 + k (k = 0..3): evaluate k of every 8 exponential pairs with the FMA-pipe polynomial instead of
-   * MUFU.EX2 (A/B timing; every value computes the same function within the bf16 rounding of P)             */
-  int32_t variant;
 } sr_attn_bwd_t;
 int sr_attn_bwd_bf16(const sr_attn_bwd_t* p, void* stream);
 

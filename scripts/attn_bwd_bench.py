@@ -15,47 +15,6 @@ H, d, P = 16, 64, 1374
 C = H * d
 dev = torch.device("cuda")
 cases = [("frame24", 24, P, 0), ("global12", 1, 12 * P, 0), ("reloc12", 12, P, 12 * 305)]
-if "--poly" in sys.argv:
-    # fair A/B of the polynomial-exp2 share in the backward (variants alternate inside every repetition, steady clocks)
-    import statistics
-    for name, batch, L, pre in cases:
-        g = torch.Generator(device="cuda").manual_seed(1)
-        qkv = torch.randn(batch * L, 3 * C, device=dev, generator=g).bfloat16()
-        dout = torch.randn(batch * L, C, device=dev, generator=g).bfloat16()
-        pkv = torch.randn(max(pre, 1), 2 * C, device=dev, generator=g).bfloat16()
-        q, k, v = (qkv[:, i * C:(i + 1) * C] for i in range(3))
-        out = torch.empty(batch * L, C, dtype=torch.bfloat16, device=dev)
-        lse = ops.new_lse(H, batch, L, dev)
-        dqkv, dpkv = torch.empty_like(qkv), torch.empty_like(pkv)
-        kw = dict(prefix_k=pkv[:, :C], prefix_v=pkv[:, C:], prefix_len=pre) if pre else {}
-        kwb = dict(dprefix_k=dpkv[:, :C], dprefix_v=dpkv[:, C:], **kw) if pre else {}
-        ops.attention(q, k, v, out, H, d, batch, L, L, L, L, lse=lse, **kw)
-        run = lambda var: ops.attention_bwd(q, k, v, out, dout, lse, dqkv[:, :C], dqkv[:, C:2 * C], dqkv[:, 2 * C:], H, d, batch, L,
-                                            L, L, L, variant=var, **kwb)
-        variants = [10, 11, 12, 13]
-        for i in range(16):
-            run(variants[i % 4])
-        torch.cuda.synchronize()
-        ref = None
-        times = {v_: [] for v_ in variants}
-        for rep in range(6):
-            for v_ in (variants if rep % 2 == 0 else variants[::-1]):
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                for _ in range(5):
-                    run(v_)
-                e1.record()
-                torch.cuda.synchronize()
-                times[v_].append(e0.elapsed_time(e1) / 5)
-        fl = 10.0 * batch * L * (L + pre) * C
-        errs = {}
-        run(10)
-        base = dqkv.float().clone()
-        for v_ in variants[1:]:
-            run(v_)
-            errs[v_ - 10] = float((dqkv.float() - base).norm() / base.norm())
-        print(name, {f"poly{v_ - 10}": round(fl / statistics.median(t) / 1e9, 1) for v_, t in times.items()}, "rel diff vs poly0", errs, flush=True)
-    sys.exit(0)
 for name, batch, L, pre in cases:
     g = torch.Generator(device="cuda").manual_seed(1)
     qkv = torch.randn(batch * L, 3 * C, device=dev, generator=g).bfloat16()

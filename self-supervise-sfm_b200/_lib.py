@@ -64,7 +64,6 @@ class SrAttnBwd(C.Structure):
         ("num_heads", _i32), ("head_dim", _i32), ("batch", _i32),
         ("q_len", _i64), ("q_batch_stride", _i64), ("kv_len", _i64), ("kv_batch_stride", _i64),
         ("scale", _f32),
-        ("variant", _i32),
     ]
 
 

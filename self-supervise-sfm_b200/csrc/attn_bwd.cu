@@ -58,9 +58,7 @@ __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, u
                : "memory");
 }
 
-// kPoly = how many of every 8 element pairs evaluate exp2 with the degree-3 polynomial on the FMA pipe instead of MUFU.EX2
-// (attn_math.cuh ex2_poly2; same trick as the forward kernel: the XU pipe is the busiest one in this loop)
-template <int kMode, int kPoly>
+template <int kMode>
 __global__ void __launch_bounds__(kBwThreads, 2)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant__ CUtensorMap tm_y,
                 const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
@@ -287,18 +285,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_x, const __grid_constant_
           // dS' = P (dP - delta): the softmax scale is applied once to the dQ / dK accumulators in the epilogue
           float pv[4], ds[4];
 #pragma unroll
-          for (int u = 0; u < 4; u += 2) {
-            const float x0 = fmaf(__uint_as_float(sv[i + u]), p.scale_log2, -ls[u]);
-            const float x1 = fmaf(__uint_as_float(sv[i + u + 1]), p.scale_log2, -ls[u + 1]);
-            if ((((i + u) >> 1) & 7) < kPoly) {
-              ex2_poly2(pack2(x0, x1), pv[u], pv[u + 1]);
-            } else {
-              pv[u] = ex2_approx(x0);
-              pv[u + 1] = ex2_approx(x1);
-            }
+          for (int u = 0; u < 4; ++u) {
+            pv[u] = ex2_approx(fmaf(__uint_as_float(sv[i + u]), p.scale_log2, -ls[u]));
+            ds[u] = pv[u] * (__uint_as_float(dv[i + u]) - dl[u]);
           }
-#pragma unroll
-          for (int u = 0; u < 4; ++u) ds[u] = pv[u] * (__uint_as_float(dv[i + u]) - dl[u]);
           if (kMode == 0 && col + 4 > valid) {              // only the last, partial K/V tile of a segment masks
 #pragma unroll
             for (int u = 0; u < 4; ++u)
@@ -386,10 +376,10 @@ __global__ void attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ out, int
   delta[(static_cast<int64_t>(h) * batch + b) * stat_pad + r] = acc;
 }
 
-template <int kMode, int kPoly>
-static int launch_bwd_k(dim3 grid, cudaStream_t st, const CUtensorMap& tx, const CUtensorMap& ty, const CUtensorMap& ta,
+template <int kMode>
+static int launch_bwd(dim3 grid, cudaStream_t st, const CUtensorMap& tx, const CUtensorMap& ty, const CUtensorMap& ta,
                       const CUtensorMap& tb, const CUtensorMap& tpa, const CUtensorMap& tpb, const BwdParams& p) {
-  auto kern = attn_bwd_kernel<kMode, kPoly>;
+  auto kern = attn_bwd_kernel<kMode>;
   static bool configured = false;
   if (!configured) {
     SR_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwSmem));
@@ -399,19 +389,6 @@ static int launch_bwd_k(dim3 grid, cudaStream_t st, const CUtensorMap& tx, const
   ++g_launch_count;
   SR_CHECK_CUDA(cudaGetLastError());
   return SR_OK;
-}
-
-constexpr int kBwPolyDefault = 0;      // pairs of 8 on the polynomial (set from the A/B of scripts/attn_bwd_bench.py --poly)
-static int g_bw_poly = kBwPolyDefault;
-template <int kMode>
-static int launch_bwd(dim3 grid, cudaStream_t st, const CUtensorMap& tx, const CUtensorMap& ty, const CUtensorMap& ta,
-                      const CUtensorMap& tb, const CUtensorMap& tpa, const CUtensorMap& tpb, const BwdParams& p) {
-  switch (g_bw_poly) {
-    case 1: return launch_bwd_k<kMode, 1>(grid, st, tx, ty, ta, tb, tpa, tpb, p);
-    case 2: return launch_bwd_k<kMode, 2>(grid, st, tx, ty, ta, tb, tpa, tpb, p);
-    case 3: return launch_bwd_k<kMode, 3>(grid, st, tx, ty, ta, tb, tpa, tpb, p);
-    default: return launch_bwd_k<kMode, 0>(grid, st, tx, ty, ta, tb, tpa, tpb, p);
-  }
 }
 
 // 3-D bf16 map over rows of `base` ([hd columns, len rows, nseg segments]), box = 64 columns x box_rows rows.
@@ -490,7 +467,6 @@ extern "C" int sr_attn_bwd_bf16(const sr_attn_bwd_t* a, void* stream) {
     pk_st = k_st; pv_st = v_st; pk_sm = k_sm; pv_sm = v_sm;
   }
 
-  g_bw_poly = (a->variant >= 10 && a->variant <= 13) ? a->variant - 10 : kBwPolyDefault;   // 10 + k: A/B timing of the exp2 split
   BwdParams p{};
   p.lse = a->lse;
   p.delta = a->delta;

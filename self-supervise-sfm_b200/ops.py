@@ -305,7 +305,7 @@ def attention_bwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.
                   dq: torch.Tensor, dk: torch.Tensor, dv: torch.Tensor, num_heads: int, head_dim: int, batch: int, q_len: int,
                   kv_len: int, q_batch_stride: int = 0, kv_batch_stride: int = 0, prefix_k: Optional[torch.Tensor] = None,
                   prefix_v: Optional[torch.Tensor] = None, prefix_len: int = 0, dprefix_k: Optional[torch.Tensor] = None,
-                  dprefix_v: Optional[torch.Tensor] = None, scale: Optional[float] = None, variant: int = 0) -> None:
+                  dprefix_v: Optional[torch.Tensor] = None, scale: Optional[float] = None) -> None:
     """Gradient of attention() (sr_attn_bwd in the header): all tensors bf16 2-D row views, lse from the forward."""
     bf = torch.bfloat16
     for name, t in (("q", q), ("k", k), ("v", v), ("out", out), ("dout", dout), ("dq", dq), ("dk", dk), ("dv", dv)):
@@ -344,7 +344,6 @@ def attention_bwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, out: torch.
     delta = torch.empty_like(lse)
     a.lse, a.delta, a.lse_pad = lse.data_ptr(), delta.data_ptr(), lse.shape[2]
     a.scale = float(scale if scale is not None else head_dim ** -0.5)
-    a.variant = int(variant)
     hd = num_heads * head_dim
     t = _Timed("attn_bwd", 10.0 * batch * q_len * (prefix_len + kv_len) * hd,
                (4 * batch * q_len + 4 * batch * kv_len + 4 * prefix_len) * hd * 2)
