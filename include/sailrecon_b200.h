@@ -285,9 +285,24 @@ int sr_modulate_f32(const float* x, int64_t ldx, const float* shift, int64_t lds
  * (ky*k + kx)*C + c; k = 1 (stride 1, pad 0: a plain split) or 3; relu = 1 applies max(x, 0) first.                */
 int sr_im2col_split_bf16(const float* x, int64_t ldx, void* out, int64_t N, int64_t H, int64_t W, int64_t C, int32_t k,
                          int32_t stride, int32_t pad, int32_t relu, void* stream);
-/* F.interpolate(mode="bilinear", align_corners=True) (custom_interpolate, dpt_head.py:565-594), x [N,Hi,Wi,C] -> [N,Ho,Wo,C] */
+/* 3x3 / stride 1 / padding 1 convolution WITHOUT an im2col matrix ("shifted GEMM"): xs = sr_split_pad_bf16 output, the
+ * zero-bordered map as rows [S*(H+2)*(W+2), hi(C) | lo(C)]; output row r (same padded row numbering; border rows hold
+ * garbage and are ignored / re-zeroed by the consumers) = sum over taps of xs[r + (ky-1)*(W+2) + (kx-1)] x W_tap.  w bf16
+ * [N, 27*C] = (Whi | Whi | Wlo), each [N, (ky, kx, c)]: the three split-precision parts run inside ONE launch, fp32
+ * accumulation.  epi: SR_EPI_BIAS with fp32 out, or SR_EPI_LS_RESIDUAL (exact_residual) adding a residual in padded rows.   */
+int sr_conv3x3_bf16(const void* xs, int64_t ld_xs, int64_t C, int64_t padded_width, const void* w, int64_t ldw, int64_t rows,
+                    int64_t N, const sr_epilogue_t* epi, void* stream);
+/* x fp32 channels-last [S, H + 2*in_pad, W + 2*in_pad, ldx] -> out bf16 [S, H+2, W+2, hi(C) | lo(C)], zero border; relu first */
+int sr_split_pad_bf16(const float* x, int64_t ldx, int32_t in_pad, void* out, int64_t S, int64_t H, int64_t W, int64_t C,
+                      int32_t relu, void* stream);
+/* out = act(a + b) between maps [S, H, W, C] that may carry the one-pixel border (pad_* in {0, 1}); b may be NULL; border
+ * pixels of a padded output are written as 0; relu = 1: act = ReLU                                                            */
+int sr_map_add_f32(const float* a, int32_t pad_a, const float* b, int32_t pad_b, float* out, int32_t pad_out, int64_t S, int64_t H,
+                   int64_t W, int64_t C, int32_t relu, void* stream);
+/* F.interpolate(mode="bilinear", align_corners=True) (custom_interpolate, dpt_head.py:565-594), x [N,Hi(+2),Wi(+2),C] (in_pad = 1:
+ * the source carries the border) -> dense [N,Ho,Wo,C]                                                                           */
 int sr_bilinear_nhwc_f32(const float* x, float* out, int64_t N, int64_t Hi, int64_t Wi, int64_t Ho, int64_t Wo, int64_t C,
-                         void* stream);
+                         int32_t in_pad, void* stream);
 /* ConvTranspose2d(kernel = stride = k) epilogue (dpt_head.py:85-102): g [N*H*W, k*k*C] (GEMM output, columns (ky, kx, c))
  * -> out [N, H*k, W*k, C] + bias[c] (NULL = none)                                                                  */
 int sr_pixel_shuffle_f32(const float* g, const float* bias, float* out, int64_t N, int64_t H, int64_t W, int64_t C, int32_t k,
@@ -301,7 +316,8 @@ int sr_uv_posembed_table(float* out, int64_t H, int64_t W, int64_t C, double asp
 /* ReLU -> 1x1 conv (hid -> out_dim) -> activate_head (dpt_head.py:150-160, head_act.py:63-114): h [px, ldh] -> pred
  * [px, out_dim - 1], conf [px].  act: 0 inv_log, 1 exp, 2 linear, 3 relu, 4 sigmoid; conf_act: 0 expp1, 1 expp0, 2 sigmoid */
 int sr_dpt_out_head_f32(const float* h, int64_t ldh, const float* w, const float* bias, float* pred, float* conf, int64_t px,
-                        int32_t hid, int32_t out_dim, int32_t act, int32_t conf_act, void* stream);
+                        int32_t hid, int32_t out_dim, int32_t act, int32_t conf_act, int32_t map_h, int32_t map_w, int32_t pad,
+                        void* stream);   /* pad = 1: h is a zero-bordered map [S, map_h + 2, map_w + 2, ldh] */
 
 #ifdef __cplusplus
 }

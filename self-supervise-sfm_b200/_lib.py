@@ -107,11 +107,14 @@ SIGNATURES = {
     "sr_pose_to_extri_intri": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
     "sr_unproject_depth": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp]),
     "sr_im2col_split_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _vp]),
-    "sr_bilinear_nhwc_f32": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _vp]),
+    "sr_bilinear_nhwc_f32": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _i32, _vp]),
+    "sr_conv3x3_bf16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _i64, C.POINTER(SrEpilogue), _vp]),
+    "sr_split_pad_bf16": (C.c_int, [_vp, _i64, _i32, _vp, _i64, _i64, _i64, _i64, _i32, _vp]),
+    "sr_map_add_f32": (C.c_int, [_vp, _i32, _vp, _i32, _vp, _i32, _i64, _i64, _i64, _i64, _i32, _vp]),
     "sr_pixel_shuffle_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _i64, _i32, _vp]),
     "sr_add_bcast_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _f32, _i32, _vp]),
     "sr_uv_posembed_table": (C.c_int, [_vp, _i64, _i64, _i64, C.c_double, C.c_double, _vp]),
-    "sr_dpt_out_head_f32": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "sr_dpt_out_head_f32": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "sr_modulate_f32": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _vp]),
 }
 

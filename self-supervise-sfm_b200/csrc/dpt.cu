@@ -73,7 +73,7 @@ im2col_split_kernel(const float* __restrict__ x, int64_t ldx, __nv_bfloat16* __r
 // F.interpolate(mode="bilinear", align_corners=True) on channels-last maps (custom_interpolate, dpt_head.py:565-594).
 __global__ void __launch_bounds__(256)
 bilinear_nhwc_kernel(const float* __restrict__ x, float* __restrict__ out, int N, int Hi, int Wi, int Ho, int Wo, int C,
-                     float sy, float sx) {
+                     float sy, float sx, int in_pad) {
   const int c4 = C >> 2;
   const int64_t total = static_cast<int64_t>(N) * Ho * Wo * c4;
   const int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
@@ -88,11 +88,12 @@ bilinear_nhwc_kernel(const float* __restrict__ x, float* __restrict__ out, int N
   const int y0 = static_cast<int>(fy), x0 = static_cast<int>(fx);
   const int y1 = y0 + (y0 < Hi - 1 ? 1 : 0), x1 = x0 + (x0 < Wi - 1 ? 1 : 0);
   const float ly1 = fy - y0, lx1 = fx - x0, ly0 = 1.f - ly1, lx0 = 1.f - lx1;
-  const float* base = x + static_cast<int64_t>(n) * Hi * Wi * C + cg * 4;
-  const float4 v00 = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(y0) * Wi + x0) * C));
-  const float4 v01 = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(y0) * Wi + x1) * C));
-  const float4 v10 = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(y1) * Wi + x0) * C));
-  const float4 v11 = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(y1) * Wi + x1) * C));
+  const int Wp = Wi + 2 * in_pad;                           // the source may carry the zero border of the shifted-GEMM convolutions
+  const float* base = x + (static_cast<int64_t>(n) * (Hi + 2 * in_pad) * Wp + static_cast<int64_t>(in_pad) * Wp + in_pad) * C + cg * 4;
+  const float4 v00 = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(y0) * Wp + x0) * C));
+  const float4 v01 = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(y0) * Wp + x1) * C));
+  const float4 v10 = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(y1) * Wp + x0) * C));
+  const float4 v11 = __ldg(reinterpret_cast<const float4*>(base + (static_cast<int64_t>(y1) * Wp + x1) * C));
   float4 o;
   o.x = ly0 * (lx0 * v00.x + lx1 * v01.x) + ly1 * (lx0 * v10.x + lx1 * v11.x);
   o.y = ly0 * (lx0 * v00.y + lx1 * v01.y) + ly1 * (lx0 * v10.y + lx1 * v11.y);
@@ -178,7 +179,8 @@ __global__ void uv_posembed_kernel(float* __restrict__ out, int H, int W, int C,
 template <int OUT>
 __global__ void __launch_bounds__(256)
 dpt_out_kernel(const float* __restrict__ h, int64_t ldh, const float* __restrict__ w, const float* __restrict__ bias,
-               float* __restrict__ pred, float* __restrict__ conf, int64_t px, int hid, int act, int conf_act) {
+               float* __restrict__ pred, float* __restrict__ conf, int64_t px, int hid, int act, int conf_act, int map_h, int map_w,
+               int pad) {
   extern __shared__ float sw[];                             // [OUT, hid] + [OUT]
   for (int i = threadIdx.x; i < OUT * hid + OUT; i += blockDim.x) sw[i] = i < OUT * hid ? w[i] : bias[i - OUT * hid];
   __syncthreads();
@@ -187,7 +189,14 @@ dpt_out_kernel(const float* __restrict__ h, int64_t ldh, const float* __restrict
   float acc[OUT];
 #pragma unroll
   for (int o = 0; o < OUT; ++o) acc[o] = 0.f;
-  const float4* src = reinterpret_cast<const float4*>(h + p * ldh);
+  int64_t row = p;                                          // h may be a zero-bordered map [S, H + 2, W + 2, ldh]
+  if (pad) {
+    const int64_t hw = static_cast<int64_t>(map_h) * map_w;
+    const int64_t s_ = p / hw, r_ = p - s_ * hw;
+    const int y = static_cast<int>(r_ / map_w), x = static_cast<int>(r_ - static_cast<int64_t>(y) * map_w);
+    row = (s_ * (map_h + 2) + y + 1) * (map_w + 2) + x + 1;
+  }
+  const float4* src = reinterpret_cast<const float4*>(h + row * ldh);
   for (int c = 0; c < hid; c += 4) {
     float4 v = __ldg(src + (c >> 2));
     v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
@@ -208,6 +217,72 @@ dpt_out_kernel(const float* __restrict__ h, int64_t ldh, const float* __restrict
   }
   const float yc = acc[OUT - 1] + sw[OUT * hid + OUT - 1];
   conf[p] = conf_act == 0 ? 1.f + expf(yc) : (conf_act == 1 ? expf(yc) : 1.f / (1.f + expf(-yc)));
+}
+
+// x fp32 channels-last [S, H + 2 in_pad, W + 2 in_pad, ldx >= C] -> out bf16 [S, H + 2, W + 2, hi(C) | lo(C)] with a ZERO
+// border: the operand layout of the shifted-GEMM 3x3 convolution (gemm_tc.cu, AMN == 2).  8 B per element moved instead of the
+// 4 + 36 B of a materialised im2col.  relu: max(x, 0) first.
+__global__ void __launch_bounds__(256)
+split_pad_kernel(const float* __restrict__ x, int64_t ldx, int in_pad, __nv_bfloat16* __restrict__ out, int S, int H, int W, int C,
+                 int relu) {
+  const int c8 = C >> 3;
+  const int Hp = H + 2, Wp = W + 2;
+  const int64_t total = static_cast<int64_t>(S) * Hp * Wp * c8;
+  const int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (idx >= total) return;
+  const int cg = static_cast<int>(idx % c8);
+  const int64_t r = idx / c8;                                // padded output pixel
+  const int xp = static_cast<int>(r % Wp);
+  const int64_t r2 = r / Wp;
+  const int yp = static_cast<int>(r2 % Hp);
+  const int s = static_cast<int>(r2 / Hp);
+  float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (yp >= 1 && yp <= H && xp >= 1 && xp <= W) {
+    const int Wi = W + 2 * in_pad;
+    const int64_t src_px = (static_cast<int64_t>(s) * (H + 2 * in_pad) + (yp - 1 + in_pad)) * Wi + (xp - 1 + in_pad);
+    const float4* src = reinterpret_cast<const float4*>(x + src_px * ldx + cg * 8);
+    const float4 a = __ldg(src), b = __ldg(src + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    if (relu) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+    }
+  }
+  uint4 hi, lo;
+  split8(v, hi, lo);
+  __nv_bfloat16* dst = out + r * (2 * static_cast<int64_t>(C)) + cg * 8;
+  *reinterpret_cast<uint4*>(dst) = hi;
+  *reinterpret_cast<uint4*>(dst + C) = lo;
+}
+
+// out = act(a + b) between channels-last maps of one spatial size that may or may not carry the one-pixel border
+// (pad_a / pad_b / pad_out in {0, 1}; b may be NULL; border pixels of a padded output are written as 0).
+__global__ void __launch_bounds__(256)
+map_add_kernel(const float* __restrict__ a, int pad_a, const float* __restrict__ b, int pad_b, float* __restrict__ out, int pad_out,
+               int S, int H, int W, int C, int relu) {
+  const int c4 = C >> 2;
+  const int Ho = H + 2 * pad_out, Wo = W + 2 * pad_out;
+  const int64_t total = static_cast<int64_t>(S) * Ho * Wo * c4;
+  const int64_t idx = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (idx >= total) return;
+  const int cg = static_cast<int>(idx % c4);
+  const int64_t r = idx / c4;
+  const int xo = static_cast<int>(r % Wo) - pad_out;
+  const int64_t r2 = r / Wo;
+  const int yo = static_cast<int>(r2 % Ho) - pad_out;
+  const int s = static_cast<int>(r2 / Ho);
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (yo >= 0 && yo < H && xo >= 0 && xo < W) {
+    const int64_t pa = (static_cast<int64_t>(s) * (H + 2 * pad_a) + yo + pad_a) * (W + 2 * pad_a) + xo + pad_a;
+    v = __ldg(reinterpret_cast<const float4*>(a + pa * C + cg * 4));
+    if (b != nullptr) {
+      const int64_t pb = (static_cast<int64_t>(s) * (H + 2 * pad_b) + yo + pad_b) * (W + 2 * pad_b) + xo + pad_b;
+      const float4 w = __ldg(reinterpret_cast<const float4*>(b + pb * C + cg * 4));
+      v = make_float4(v.x + w.x, v.y + w.y, v.z + w.z, v.w + w.w);
+    }
+    if (relu) v = make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
+  }
+  *reinterpret_cast<float4*>(out + r * C + cg * 4) = v;
 }
 
 static inline unsigned blocks_for(int64_t n) { return static_cast<unsigned>((n + 255) / 256); }
@@ -234,8 +309,41 @@ extern "C" int sr_im2col_split_bf16(const float* x, int64_t ldx, void* out, int6
   return SR_OK;
 }
 
+extern "C" int sr_split_pad_bf16(const float* x, int64_t ldx, int32_t in_pad, void* out, int64_t S, int64_t H, int64_t W, int64_t C,
+                                 int32_t relu, void* stream) {
+  using namespace sr;
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(x && out && C > 0 && C % 8 == 0 && ldx >= C && ldx % 4 == 0 && S > 0 && H > 0 && W > 0, "sr_split_pad_bf16: bad argument");
+  SR_REQUIRE(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) == 0, "sr_split_pad_bf16: 16-byte alignment");
+  const int64_t total = S * (H + 2) * (W + 2) * (C / 8);
+  SR_REQUIRE((total + 255) / 256 < (1ll << 31), "sr_split_pad_bf16: too many elements");
+  split_pad_kernel<<<blocks_for(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      x, ldx, in_pad ? 1 : 0, reinterpret_cast<__nv_bfloat16*>(out), static_cast<int>(S), static_cast<int>(H), static_cast<int>(W),
+      static_cast<int>(C), relu);
+  ++g_launch_count;
+  SR_CHECK_CUDA(cudaGetLastError());
+  return SR_OK;
+}
+
+extern "C" int sr_map_add_f32(const float* a, int32_t pad_a, const float* b, int32_t pad_b, float* out, int32_t pad_out, int64_t S,
+                              int64_t H, int64_t W, int64_t C, int32_t relu, void* stream) {
+  using namespace sr;
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(a && out && C > 0 && C % 4 == 0 && S > 0 && H > 0 && W > 0, "sr_map_add_f32: bad argument");
+  SR_REQUIRE(((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
+             "sr_map_add_f32: 16-byte alignment");
+  const int po = pad_out ? 1 : 0;
+  const int64_t total = S * (H + 2 * po) * (W + 2 * po) * (C / 4);
+  SR_REQUIRE((total + 255) / 256 < (1ll << 31), "sr_map_add_f32: too many elements");
+  map_add_kernel<<<blocks_for(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      a, pad_a ? 1 : 0, b, pad_b ? 1 : 0, out, po, static_cast<int>(S), static_cast<int>(H), static_cast<int>(W), static_cast<int>(C), relu);
+  ++g_launch_count;
+  SR_CHECK_CUDA(cudaGetLastError());
+  return SR_OK;
+}
+
 extern "C" int sr_bilinear_nhwc_f32(const float* x, float* out, int64_t N, int64_t Hi, int64_t Wi, int64_t Ho, int64_t Wo, int64_t C,
-                                    void* stream) {
+                                    int32_t in_pad, void* stream) {
   using namespace sr;
   if (int rc = require_sm100()) return rc;
   SR_REQUIRE(x && out && C > 0 && C % 4 == 0 && Hi > 0 && Wi > 0 && Ho > 0 && Wo > 0, "sr_bilinear_nhwc_f32: bad argument");
@@ -246,7 +354,7 @@ extern "C" int sr_bilinear_nhwc_f32(const float* x, float* out, int64_t N, int64
   const float sx = Wo > 1 ? static_cast<float>(Wi - 1) / static_cast<float>(Wo - 1) : 0.f;
   bilinear_nhwc_kernel<<<blocks_for(total), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       x, out, static_cast<int>(N), static_cast<int>(Hi), static_cast<int>(Wi), static_cast<int>(Ho), static_cast<int>(Wo),
-      static_cast<int>(C), sy, sx);
+      static_cast<int>(C), sy, sx, in_pad ? 1 : 0);
   ++g_launch_count;
   SR_CHECK_CUDA(cudaGetLastError());
   return SR_OK;
@@ -296,19 +404,21 @@ extern "C" int sr_uv_posembed_table(float* out, int64_t H, int64_t W, int64_t C,
 }
 
 extern "C" int sr_dpt_out_head_f32(const float* h, int64_t ldh, const float* w, const float* bias, float* pred, float* conf,
-                                   int64_t px, int32_t hid, int32_t out_dim, int32_t act, int32_t conf_act, void* stream) {
+                                   int64_t px, int32_t hid, int32_t out_dim, int32_t act, int32_t conf_act, int32_t map_h,
+                                   int32_t map_w, int32_t pad, void* stream) {
   using namespace sr;
   if (int rc = require_sm100()) return rc;
   SR_REQUIRE(h && w && bias && pred && conf, "sr_dpt_out_head_f32: null pointer");
   SR_REQUIRE(hid > 0 && hid % 4 == 0 && ldh >= hid && ldh % 4 == 0 && (out_dim == 2 || out_dim == 4),
              "sr_dpt_out_head_f32: hid must be a multiple of 4 and out_dim 2 (depth + conf) or 4 (xyz + conf)");
   SR_REQUIRE(act >= 0 && act <= 4 && conf_act >= 0 && conf_act <= 2, "sr_dpt_out_head_f32: unknown activation code");
+  SR_REQUIRE(!pad || (map_h > 0 && map_w > 0 && px % (static_cast<int64_t>(map_h) * map_w) == 0), "sr_dpt_out_head_f32: bad padded map");
   if (px == 0) return SR_OK;
   SR_REQUIRE((px + 255) / 256 < (1ll << 31), "sr_dpt_out_head_f32: too many pixels");
   const size_t smem = static_cast<size_t>(out_dim) * (hid + 1) * sizeof(float);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (out_dim == 4) dpt_out_kernel<4><<<blocks_for(px), 256, smem, st>>>(h, ldh, w, bias, pred, conf, px, hid, act, conf_act);
-  else dpt_out_kernel<2><<<blocks_for(px), 256, smem, st>>>(h, ldh, w, bias, pred, conf, px, hid, act, conf_act);
+  if (out_dim == 4) dpt_out_kernel<4><<<blocks_for(px), 256, smem, st>>>(h, ldh, w, bias, pred, conf, px, hid, act, conf_act, map_h, map_w, pad);
+  else dpt_out_kernel<2><<<blocks_for(px), 256, smem, st>>>(h, ldh, w, bias, pred, conf, px, hid, act, conf_act, map_h, map_w, pad);
   ++g_launch_count;
   SR_CHECK_CUDA(cudaGetLastError());
   return SR_OK;

@@ -31,6 +31,7 @@ constexpr int kNumEpiWarps = 8;
 struct GemmParams {
   int M, N, K;
   sr_epilogue_t e;
+  int conv_c, conv_wp;     // AMN == 2 (3x3 convolution as a shifted GEMM): channels per pixel, padded row width W + 2
 };
 
 template <int BN>
@@ -285,9 +286,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         uint8_t* sb = sa + Cfg::kABytes;
         if (elect_one()) {
           mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
-          if (AMN) {        // one {64 features, 64 contraction rows} box per 64-wide block, 8 KB apart
+          if (AMN == 1) {   // one {64 features, 64 contraction rows} box per 64-wide block, 8 KB apart
 #pragma unroll
             for (int b = 0; b < kBM / 64; ++b) tma_load_2d(sa + b * 8192, &tmap_a, &full_bar[stage], m_blk * kBM + b * 64, kb * kBK);
+          } else if (AMN == 2) {
+            // 3x3 / stride 1 / pad 1 convolution on a zero-bordered channels-last map [S, H + 2, W + 2, hi(C) | lo(C)]: output
+            // row r needs input row r + (ky - 1) (W + 2) + (kx - 1) for tap (ky, kx) — a ROW SHIFT of the same matrix, so the
+            // im2col matrix is never materialised.  K loop = 3 split-precision parts (hi x Whi, lo x Whi, hi x Wlo) x 9 taps x
+            // C / 64 blocks; rows shifted past either end of the matrix are zero-filled by TMA.
+            const int bpt = p.conv_c >> 6;
+            const int idx = kb / bpt, cb = kb - idx * bpt;
+            const int part = idx / 9, tap = idx - part * 9;
+            const int ky = tap / 3, kx = tap - ky * 3;
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], (part == 1 ? p.conv_c : 0) + cb * kBK,
+                        m_blk * kBM + (ky - 1) * p.conv_wp + (kx - 1));
           } else {
             tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kBK, m_blk * kBM);
           }
@@ -304,7 +316,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (whole warp, one elected lane issues)
-    constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, AMN, BMN);
+    constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN, AMN == 1 ? 1 : 0, BMN);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -320,12 +332,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const uint32_t sb = sa + Cfg::kABytes;
         // K-major: +32 bytes per K = 16 slice inside the 128 B swizzle atom -> +2 in the (addr >> 4) field;
         // MN-major: +16 contraction rows x 128 B = 2048 bytes -> +128
-        const uint64_t da = AMN ? umma_desc_sw128(sa, 8192, 1024) : umma_desc_sw128(sa, 16, 1024);
+        const uint64_t da = AMN == 1 ? umma_desc_sw128(sa, 8192, 1024) : umma_desc_sw128(sa, 16, 1024);
         const uint64_t db = BMN ? umma_desc_sw128(sb, 8192, 1024) : umma_desc_sw128(sb, 16, 1024);
         if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < kBK / 16; ++k)
-            umma_ss(tmem_d, da + (AMN ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_ss(tmem_d, da + (AMN == 1 ? 128 : 2) * k, db + (BMN ? 128 : 2) * k, idesc, (kb | k) != 0 ? 1u : 0u);
           umma_commit(&empty_bar[stage]);
         }
         __syncwarp();
@@ -542,6 +554,49 @@ static int dispatch_gemm_t(const CUtensorMap& ta, const CUtensorMap& tb, const G
 
 }  // namespace sr
 
+extern "C" int sr_conv3x3_bf16(const void* xs, int64_t ld_xs, int64_t C, int64_t padded_width, const void* w, int64_t ldw,
+                               int64_t rows, int64_t N, const sr_epilogue_t* epi, void* stream) {
+  using namespace sr;
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(xs && w && epi && epi->out, "sr_conv3x3_bf16: null pointer");
+  SR_REQUIRE(C > 0 && C % 64 == 0 && ld_xs >= 2 * C && ld_xs % 8 == 0, "sr_conv3x3_bf16: C must be a multiple of 64, rows [hi(C) | lo(C)]");
+  SR_REQUIRE(N > 0 && N % 128 == 0 && ldw >= 27 * C && ldw % 8 == 0, "sr_conv3x3_bf16: weights [N %% 128 == 0, 27 C] = (Whi | Whi | Wlo) x (tap, c)");
+  SR_REQUIRE(rows > 0 && rows < (1ll << 31) && padded_width >= 3 && padded_width < (1 << 20), "sr_conv3x3_bf16: bad map size");
+  SR_REQUIRE((reinterpret_cast<uintptr_t>(xs) & 15) == 0 && (reinterpret_cast<uintptr_t>(w) & 15) == 0, "sr_conv3x3_bf16: 16-byte alignment");
+  const sr_epilogue_t& e = *epi;
+  SR_REQUIRE((e.kind == SR_EPI_BIAS && !e.out_bf16) || e.kind == SR_EPI_LS_RESIDUAL, "sr_conv3x3_bf16: fp32 output (BIAS or LS_RESIDUAL)");
+  SR_REQUIRE((reinterpret_cast<uintptr_t>(e.out) & 15) == 0 && e.ldo % 4 == 0 && e.ldo >= N, "sr_conv3x3_bf16: bad output");
+  if (e.kind == SR_EPI_LS_RESIDUAL)
+    SR_REQUIRE(e.resid && (reinterpret_cast<uintptr_t>(e.resid) & 15) == 0 && e.ldr % 4 == 0, "sr_conv3x3_bf16: bad residual");
+  const int64_t tiles256 = ((rows + kBM - 1) / kBM) * (N / 256);
+  const int BN = (N % 256 == 0 && tiles256 >= kNumSMs / 2) ? 256 : 128;
+  CUtensorMap ta, tb;
+  {
+    uint64_t dims[2] = {static_cast<uint64_t>(2 * C), static_cast<uint64_t>(rows)};
+    uint64_t strides[1] = {static_cast<uint64_t>(ld_xs) * 2};
+    uint32_t box[2] = {kBK, kBM};
+    if (int rc = make_tmap_bf16(&ta, xs, 2, dims, strides, box)) return rc;
+  }
+  {
+    uint64_t dims[2] = {static_cast<uint64_t>(27 * C), static_cast<uint64_t>(N)};
+    uint64_t strides[1] = {static_cast<uint64_t>(ldw) * 2};
+    uint32_t box[2] = {kBK, static_cast<uint32_t>(BN)};
+    if (int rc = make_tmap_bf16(&tb, w, 2, dims, strides, box)) return rc;
+  }
+  GemmParams p;
+  p.M = static_cast<int>(rows);
+  p.N = static_cast<int>(N);
+  p.K = static_cast<int>(27 * C);
+  p.e = e;
+  p.conv_c = static_cast<int>(C);
+  p.conv_wp = static_cast<int>(padded_width);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (e.kind == SR_EPI_BIAS)
+    return BN == 256 ? launch_gemm<256, SR_EPI_BIAS, false, 2, 0>(ta, tb, p, st) : launch_gemm<128, SR_EPI_BIAS, false, 2, 0>(ta, tb, p, st);
+  return BN == 256 ? launch_gemm<256, SR_EPI_LS_RESIDUAL, false, 2, 0>(ta, tb, p, st)
+                   : launch_gemm<128, SR_EPI_LS_RESIDUAL, false, 2, 0>(ta, tb, p, st);
+}
+
 extern "C" int sr_gemm_bf16_t(const void* A, int64_t lda, int32_t a_mn_major, const void* W, int64_t ldw, int32_t b_mn_major,
                               int64_t M, int64_t N, int64_t K, const sr_epilogue_t* epi, void* stream) {
   using namespace sr;
@@ -588,6 +643,7 @@ extern "C" int sr_gemm_bf16_t(const void* A, int64_t lda, int32_t a_mn_major, co
   p.N = static_cast<int>(N);
   p.K = static_cast<int>(K);
   p.e = e;
+  p.conv_c = p.conv_wp = 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (a_mn_major) return BN == 256 ? dispatch_gemm_t<256, 1, 1>(ta, tb, p, st) : dispatch_gemm_t<128, 1, 1>(ta, tb, p, st);
   return BN == 256 ? dispatch_gemm_t<256, 0, 1>(ta, tb, p, st) : dispatch_gemm_t<128, 0, 1>(ta, tb, p, st);
@@ -645,6 +701,7 @@ extern "C" int sr_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t l
   p.N = static_cast<int>(N);
   p.K = static_cast<int>(K);
   p.e = e;
+  p.conv_c = p.conv_wp = 0;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   return BN == 256 ? dispatch_gemm<256>(ta, tb, p, st) : dispatch_gemm<128>(ta, tb, p, st);
 }

@@ -64,6 +64,16 @@ def conv_rows(conv: nn.Module, x: torch.Tensor, relu_in: bool = False, resid: to
     return y if npad == n else y[..., :n]
 
 
+def conv3_pad(conv: nn.Module, x: torch.Tensor, in_pad: bool, relu_in: bool = False, resid: torch.Tensor = None) -> torch.Tensor:
+    """nn.Conv2d(kernel 3, stride 1, padding 1) WITHOUT an im2col matrix: x fp32 [S, H (+2), W (+2), Cin] (in_pad: it carries the
+    one-pixel border) -> fp32 [S, H+2, W+2, Np] in the padded row numbering (Np = Cout rounded up to 128; border rows are
+    garbage).  One split pass (8 B per element) + one shifted-GEMM launch with the three split-precision parts inside."""
+    w_hh, w_lo, bias, n = _conv_weights(conv)
+    w27 = engine._cached(conv, "w27", conv.weight, lambda w: torch.cat([w_hh, w_lo], dim=1).contiguous())   # Whi | Whi | Wlo
+    xs = ops.split_pad(x, in_pad, relu_in)
+    return ops.conv3x3(xs, w27, bias, resid)
+
+
 class ResidualConvUnit(nn.Module):
     """dpt_head.py:430-482.  The reference's activation is nn.ReLU(inplace=True) (:357), so `out = self.activation(x)`
     rectifies x IN PLACE and the skip connection adds the RECTIFIED input: RCU(x) = relu(x) + conv2(relu(conv1(relu(x)))).
@@ -79,8 +89,9 @@ class ResidualConvUnit(nn.Module):
         self.norm1 = self.norm2 = None
 
     def rows(self, xr: torch.Tensor) -> torch.Tensor:
-        h = conv_rows(self.conv1, xr)
-        return conv_rows(self.conv2, h, relu_in=True, resid=xr)         # skip_add fused into the GEMM epilogue
+        """xr = relu(x) as a zero-bordered map [S, H+2, W+2, C] -> RCU(x) in the same padded layout."""
+        h = conv3_pad(self.conv1, xr, in_pad=True)
+        return conv3_pad(self.conv2, h, in_pad=True, relu_in=True, resid=xr)     # skip_add fused into the GEMM epilogue
 
 
 class FeatureFusionBlock(nn.Module):
@@ -99,18 +110,21 @@ class FeatureFusionBlock(nn.Module):
         self.resConfUnit2 = ResidualConvUnit(features, activation, bn, groups)
         self.size = size
 
-    def rows(self, *xs, size=None) -> torch.Tensor:
+    def rows(self, x0: torch.Tensor, x0_padded: bool, x1: torch.Tensor = None, size=None) -> torch.Tensor:
+        """forward(*xs, size) (dpt_head.py:536-563): x0 = xs[0] (dense, or padded when x0_padded), x1 = xs[1] = a layer_rn output
+        in the padded layout.  Returns the DENSE map after interpolation + out_conv."""
         if self.has_residual:
-            res = self.resConfUnit1.rows(ops.add_bcast(xs[1].contiguous(), None, relu=True))
-            out_r = ops.add_bcast(xs[0].contiguous(), res.contiguous(), relu=True)       # relu(xs[0] + res): all RCU2 reads
+            res = self.resConfUnit1.rows(ops.map_add(x1, True, None, False, True, relu=True))
+            out_r = ops.map_add(x0, x0_padded, res, True, True, relu=True)                # relu(xs[0] + res): all RCU2 reads
         else:
-            out_r = ops.add_bcast(xs[0].contiguous(), None, relu=True)
-        output = self.resConfUnit2.rows(out_r)
+            out_r = ops.map_add(x0, x0_padded, None, False, True, relu=True)
+        output = self.resConfUnit2.rows(out_r)                                           # padded
+        Hh, Ww = output.shape[1] - 2, output.shape[2] - 2
         if size is None and self.size is None:
-            Ho, Wo = int(output.shape[1] * 2), int(output.shape[2] * 2)
+            Ho, Wo = int(Hh * 2), int(Ww * 2)
         else:
             Ho, Wo = (self.size if size is None else size)
-        output = ops.bilinear_nhwc(output.contiguous(), int(Ho), int(Wo))
+        output = ops.bilinear_nhwc(output, int(Ho), int(Wo), in_pad=True)
         return conv_rows(self.out_conv, output)
 
 
@@ -218,29 +232,28 @@ class DPTHead(nn.Module):
             elif isinstance(rl, nn.Conv2d):
                 x = conv_rows(rl, x.contiguous())
             out.append(x)
-        out = self.scratch_forward(out)
+        out = self.scratch_forward(out)                                               # padded [S, h1*2 + 2, w1*2 + 2, 128 | 256]
         Ho, Wo = int(ph * self.patch_size / self.down_ratio), int(pw * self.patch_size / self.down_ratio)
-        out = ops.bilinear_nhwc(out.contiguous(), Ho, Wo)
+        out = ops.bilinear_nhwc(out, Ho, Wo, in_pad=True)
         if self.pos_embed:
             out = self._add_pos(out, W, H)
         if self.feature_only:
             return out.permute(0, 3, 1, 2)[None]                                     # [B, S, C, H, W] view, as the reference
         conv_a, conv_b = self.scratch.output_conv2[0], self.scratch.output_conv2[2]
-        hmap = conv_rows(conv_a, out)                                                 # [S, Ho, Wo, 32] view of a 128-wide buffer
-        hid = conv_a.out_channels
-        h2 = hmap.reshape(S * Ho * Wo, -1) if hmap.is_contiguous() else torch.as_strided(
-            hmap, (S * Ho * Wo, hid), (hmap.stride(2), 1), hmap.storage_offset())
-        pred, conf = ops.dpt_out_head(h2, hid, conv_b.weight.detach(), conv_b.bias.detach(), self.activation, self.conf_activation)
+        hmap = conv3_pad(conv_a, out, in_pad=False)                                   # [S, Ho+2, Wo+2, 128]: 32 valid channels
+        pred, conf = ops.dpt_out_head(hmap.view(-1, hmap.shape[-1]), conv_a.out_channels, conv_b.weight.detach(),
+                                      conv_b.bias.detach(), self.activation, self.conf_activation, padded_map=(S, Ho, Wo))
         return pred.view(1, S, Ho, Wo, -1), conf.view(1, S, Ho, Wo)
 
     def scratch_forward(self, features: List[torch.Tensor]) -> torch.Tensor:
-        """dpt_head.py:313-344 on channels-last maps."""
+        """dpt_head.py:313-344 on channels-last maps; the 3x3 convolutions keep their maps in the zero-bordered layout."""
         l1, l2, l3, l4 = features
         sc = self.scratch
-        l1rn, l2rn = conv_rows(sc.layer1_rn, l1.contiguous()), conv_rows(sc.layer2_rn, l2.contiguous())
-        l3rn, l4rn = conv_rows(sc.layer3_rn, l3.contiguous()), conv_rows(sc.layer4_rn, l4.contiguous())
-        out = sc.refinenet4.rows(l4rn, size=l3rn.shape[1:3])
-        out = sc.refinenet3.rows(out, l3rn, size=l2rn.shape[1:3])
-        out = sc.refinenet2.rows(out, l2rn, size=l1rn.shape[1:3])
-        out = sc.refinenet1.rows(out, l1rn)
-        return conv_rows(sc.output_conv1, out.contiguous())
+        l1rn, l2rn = conv3_pad(sc.layer1_rn, l1.contiguous(), False), conv3_pad(sc.layer2_rn, l2.contiguous(), False)
+        l3rn, l4rn = conv3_pad(sc.layer3_rn, l3.contiguous(), False), conv3_pad(sc.layer4_rn, l4.contiguous(), False)
+        dense = lambda t: (t.shape[1] - 2, t.shape[2] - 2)
+        out = sc.refinenet4.rows(l4rn, True, None, size=dense(l3rn))
+        out = sc.refinenet3.rows(out, False, l3rn, size=dense(l2rn))
+        out = sc.refinenet2.rows(out, False, l2rn, size=dense(l1rn))
+        out = sc.refinenet1.rows(out, False, l1rn)
+        return conv3_pad(sc.output_conv1, out.contiguous(), False)

@@ -689,15 +689,79 @@ def gemm_split(a2: torch.Tensor, w_hh: torch.Tensor, w_lo: torch.Tensor, bias: O
     return out
 
 
-def bilinear_nhwc(x: torch.Tensor, Ho: int, Wo: int) -> torch.Tensor:
-    """F.interpolate(bilinear, align_corners=True) on channels-last fp32 [N, Hi, Wi, C]."""
+def bilinear_nhwc(x: torch.Tensor, Ho: int, Wo: int, in_pad: bool = False) -> torch.Tensor:
+    """F.interpolate(bilinear, align_corners=True) on channels-last fp32 [N, Hi (+2), Wi (+2), C] -> dense [N, Ho, Wo, C];
+    in_pad: the source carries the one-pixel border of the shifted-GEMM convolutions."""
     if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.is_contiguous()):
         raise ValueError("sailrecon_b200: bilinear_nhwc needs a contiguous fp32 CUDA tensor [N, H, W, C]")
     N, Hi, Wi, Cc = x.shape
+    if in_pad:
+        Hi, Wi = Hi - 2, Wi - 2
     out = torch.empty(N, Ho, Wo, Cc, dtype=torch.float32, device=x.device)
     t = _Timed("bilinear", 0.0, (x.numel() + out.numel()) * 4)
-    _lib.check(_lib.load().sr_bilinear_nhwc_f32(x.data_ptr(), out.data_ptr(), N, Hi, Wi, Ho, Wo, Cc, _stream()), "bilinear_nhwc")
+    _lib.check(_lib.load().sr_bilinear_nhwc_f32(x.data_ptr(), out.data_ptr(), N, Hi, Wi, Ho, Wo, Cc, int(in_pad), _stream()),
+               "bilinear_nhwc")
     t.done()
+    return out
+
+
+def split_pad(x: torch.Tensor, in_pad: bool, relu: bool = False) -> torch.Tensor:
+    """x fp32 channels-last [S, H (+2), W (+2), >= C] (pixel stride x.stride(2)) -> bf16 [S, H+2, W+2, 2C] = [hi | lo] with a zero
+    border: the operand of conv3x3 (csrc/dpt.cu split_pad_kernel)."""
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.stride(3) == 1
+            and x.stride(1) == x.shape[2] * x.stride(2) and x.stride(0) == x.shape[1] * x.stride(1)):
+        raise ValueError("sailrecon_b200: split_pad needs a dense channels-last fp32 CUDA tensor [S, H, W, C]")
+    S, Hh, Ww, Cc = x.shape
+    if in_pad:
+        Hh, Ww = Hh - 2, Ww - 2
+    out = torch.empty(S, Hh + 2, Ww + 2, 2 * Cc, dtype=torch.bfloat16, device=x.device)
+    t = _Timed("split_pad", 0.0, x.shape[0] * x.shape[1] * x.shape[2] * Cc * 4 + out.numel() * 2)
+    _lib.check(_lib.load().sr_split_pad_bf16(x.data_ptr(), x.stride(2), int(in_pad), out.data_ptr(), S, Hh, Ww, Cc, int(relu), _stream()),
+               "split_pad")
+    t.done()
+    return out
+
+
+def conv3x3(xs: torch.Tensor, w27: torch.Tensor, bias: Optional[torch.Tensor], resid: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """3x3 / stride 1 / pad 1 convolution as a shifted GEMM (sr_conv3x3_bf16): xs = split_pad output [S, H+2, W+2, 2C], w27 bf16
+    [N, 27C] = (Whi | Whi | Wlo) x (tap, c); returns fp32 [S, H+2, W+2, N] in the SAME padded row numbering (border rows are
+    garbage: consumers ignore or re-zero them); resid fp32 [S, H+2, W+2, N] is added in the epilogue (exact fp32)."""
+    S, Hp, Wp, C2 = xs.shape
+    Cc = C2 // 2
+    N = w27.shape[0]
+    if xs.dtype != torch.bfloat16 or not xs.is_contiguous() or w27.dtype != torch.bfloat16 or w27.shape[1] != 27 * Cc or not w27.is_contiguous():
+        raise ValueError("sailrecon_b200: conv3x3 operands must be contiguous bf16 [S, H+2, W+2, 2C] and [N, 27C]")
+    rows = S * Hp * Wp
+    out = torch.empty(S, Hp, Wp, N, dtype=torch.float32, device=xs.device)
+    _vec(bias, N, "bias")
+    e = SrEpilogue()
+    e.out, e.ldo, e.bias = out.data_ptr(), N, _ptr(bias)
+    if resid is None:
+        e.kind = SR_EPI_BIAS
+    else:
+        if resid.shape != out.shape or resid.dtype != torch.float32 or not resid.is_contiguous():
+            raise ValueError("sailrecon_b200: conv3x3 residual must be a contiguous fp32 map in the padded layout of the output")
+        e.kind, e.resid, e.ldr, e.exact_residual = SR_EPI_LS_RESIDUAL, resid.data_ptr(), N, 1
+    t = _Timed("gemm_tc", 2.0 * rows * N * 27 * Cc, rows * 2 * Cc * 2 + N * 27 * Cc * 2 + rows * N * 4)
+    _lib.check(_lib.load().sr_conv3x3_bf16(xs.data_ptr(), 2 * Cc, Cc, Wp, w27.data_ptr(), 27 * Cc, rows, N, C.byref(e), _stream()),
+               "conv3x3")
+    t.done()
+    return out
+
+
+def map_add(a: torch.Tensor, pad_a: bool, b: Optional[torch.Tensor], pad_b: bool, pad_out: bool, relu: bool = False) -> torch.Tensor:
+    """act(a + b) between channels-last fp32 maps of one spatial size with / without the one-pixel border (b may be None)."""
+    for t_ in (a, b):
+        if t_ is not None and not (t_.is_cuda and t_.dtype == torch.float32 and t_.dim() == 4 and t_.is_contiguous()):
+            raise ValueError("sailrecon_b200: map_add needs contiguous fp32 CUDA maps [S, H, W, C]")
+    S, Ha, Wa, Cc = a.shape
+    Hh, Ww = (Ha - 2, Wa - 2) if pad_a else (Ha, Wa)
+    if b is not None and tuple(b.shape) != (S, Hh + 2 * int(pad_b), Ww + 2 * int(pad_b), Cc):
+        raise ValueError("sailrecon_b200: map_add shape mismatch")
+    po = int(pad_out)
+    out = torch.empty(S, Hh + 2 * po, Ww + 2 * po, Cc, dtype=torch.float32, device=a.device)
+    _lib.check(_lib.load().sr_map_add_f32(a.data_ptr(), int(pad_a), _ptr(b), int(pad_b), out.data_ptr(), po, S, Hh, Ww, Cc, int(relu),
+                                          _stream()), "map_add")
     return out
 
 
@@ -741,17 +805,25 @@ _DPT_ACT = {"inv_log": 0, "exp": 1, "linear": 2, "relu": 3, "sigmoid": 4}
 _DPT_CONF = {"expp1": 0, "expp0": 1, "sigmoid": 2}
 
 
-def dpt_out_head(h: torch.Tensor, hid: int, w: torch.Tensor, bias: torch.Tensor, activation: str, conf_activation: str):
-    """ReLU -> 1x1 conv -> activate_head: h fp32 [px, >= hid] -> (pred [px, out_dim - 1], conf [px])."""
+def dpt_out_head(h: torch.Tensor, hid: int, w: torch.Tensor, bias: torch.Tensor, activation: str, conf_activation: str,
+                 padded_map=None):
+    """ReLU -> 1x1 conv -> activate_head: h fp32 rows [px or padded px, >= hid] -> (pred [px, out_dim - 1], conf [px]).
+    padded_map = (S, H, W): h is a zero-bordered map [S, H+2, W+2, ld] and px = S*H*W interior pixels are produced."""
     _rows2d(h, torch.float32, "h")
     if activation not in _DPT_ACT or conf_activation not in _DPT_CONF:
         raise ValueError(f"Unknown activation: {activation} / {conf_activation}")
     w2 = w.reshape(w.shape[0], -1).contiguous()
     out_dim = w2.shape[0]
-    px = h.shape[0]
+    if padded_map is None:
+        px, mh, mw, pad = h.shape[0], 0, 0, 0
+    else:
+        S_, mh, mw = padded_map
+        px, pad = S_ * mh * mw, 1
+        if h.shape[0] != S_ * (mh + 2) * (mw + 2):
+            raise ValueError("sailrecon_b200: dpt_out_head padded map size mismatch")
     pred = torch.empty(px, out_dim - 1, dtype=torch.float32, device=h.device)
     conf = torch.empty(px, dtype=torch.float32, device=h.device)
     _lib.check(_lib.load().sr_dpt_out_head_f32(h.data_ptr(), h.stride(0), w2.data_ptr(), bias.data_ptr(), pred.data_ptr(),
                                                conf.data_ptr(), px, hid, out_dim, _DPT_ACT[activation], _DPT_CONF[conf_activation],
-                                               _stream()), "dpt_out_head")
+                                               mh, mw, pad, _stream()), "dpt_out_head")
     return pred, conf

@@ -75,6 +75,28 @@ def test_dpt_row_kernels():
         assert got.shape == ref.shape and rel_l2(got, ref) < 2e-5, (k, s, cout)
         got_r = conv_rows(conv, x, relu_in=True)
         assert rel_l2(got_r, F.conv2d(x.relu().permute(0, 3, 1, 2), conv.weight, conv.bias, s, k // 2).permute(0, 2, 3, 1)) < 2e-5
+    # the same 3x3 convolutions WITHOUT an im2col matrix: zero-bordered split layout + shifted GEMM (interior of the padded output)
+    from sailrecon_b200.heads.dpt_head import conv3_pad
+    for cout in (256, 128, 32):
+        conv = torch.nn.Conv2d(128, cout, 3, 1, 1).to(DEV)
+        ref = F.conv2d(x.permute(0, 3, 1, 2), conv.weight, conv.bias, 1, 1).permute(0, 2, 3, 1)
+        got = conv3_pad(conv, x, in_pad=False)
+        assert got.shape[:3] == (2, 21, 25) and rel_l2(got[:, 1:-1, 1:-1, :cout], ref) < 2e-5, cout
+        xp = ops.map_add(x, False, None, False, True)                       # the same input carried in the padded layout
+        assert torch.equal(xp[:, 1:-1, 1:-1], x) and float(xp[:, 0].abs().max()) == 0.0 and float(xp[:, :, -1].abs().max()) == 0.0
+        got_p = conv3_pad(conv, xp, in_pad=True, relu_in=True)
+        ref_r = F.conv2d(x.relu().permute(0, 3, 1, 2), conv.weight, conv.bias, 1, 1).permute(0, 2, 3, 1)
+        assert rel_l2(got_p[:, 1:-1, 1:-1, :cout], ref_r) < 2e-5
+        if cout == 256:
+            res = torch.randn(2, 21, 25, 256, device=DEV, generator=g)
+            got_res = conv3_pad(conv, xp, in_pad=True, resid=res)
+            assert rel_l2(got_res[:, 1:-1, 1:-1], ref + res[:, 1:-1, 1:-1]) < 2e-5
+    y = torch.randn(2, 19, 23, 128, device=DEV, generator=g)
+    yp = ops.map_add(y, False, None, False, True)
+    s_ = ops.map_add(x, False, yp, True, False, relu=True)
+    assert torch.allclose(s_, (x + y).relu(), atol=1e-6)
+    up_p = ops.bilinear_nhwc(yp, 37, 50, in_pad=True)
+    assert rel_l2(up_p, F.interpolate(y.permute(0, 3, 1, 2), size=(37, 50), mode="bilinear", align_corners=True).permute(0, 2, 3, 1)) < 1e-6
     up = ops.bilinear_nhwc(x, 37, 50)
     ref = F.interpolate(x.permute(0, 3, 1, 2), size=(37, 50), mode="bilinear", align_corners=True).permute(0, 2, 3, 1)
     assert rel_l2(up, ref) < 1e-6
