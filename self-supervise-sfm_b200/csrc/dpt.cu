@@ -4,7 +4,8 @@
 // Layout: every feature map is CHANNELS-LAST fp32, i.e. a row matrix [N*H*W, C] — the same row-matrix convention as the
 // token buffers of the aggregator, so every convolution is a GEMM on the tcgen05 kernel of gemm_tc.cu:
 //   1x1 conv / ConvTranspose(k = stride)      rows as they are               x  W[Cout(*k*k), Cin]
-//   3x3 conv (stride 1 or 2, padding 1)       im2col rows [.., 9*Cin]        x  W[Cout, (ky, kx, Cin)]
+//   3x3 conv, stride 1, padding 1             zero-bordered map, SHIFTED rows (gemm_tc.cu AMN == 2, sr_conv3x3_bf16): no im2col
+//   3x3 conv, stride 2 (one small layer)      im2col rows [.., 9*Cin]        x  W[Cout, (ky, kx, Cin)]
 // fp32 semantics on a bf16 tensor core: each fp32 operand is split into hi = bf16(x) and lo = bf16(x - hi); the product is
 // hi*hi + lo*hi + hi*lo accumulated in fp32 (the dropped lo*lo term is 2^-16 relative), evaluated as TWO GEMMs:
 //   out  = [A_hi | A_lo] x [W_hi | W_hi]^T (+ bias, + residual)      K' = 2K
