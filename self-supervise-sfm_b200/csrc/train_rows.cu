@@ -111,6 +111,45 @@ colsum_kernel(const void* __restrict__ a_, int64_t lda, const __nv_bfloat16* __r
   atomicAdd(out + c, acc);
 }
 
+// Bias gradient db = colsum(dY) on bf16 dY (round 2: no longer fused into a transpose, the wgrad GEMM reads dY in place): 256
+// columns x 256 rows per block; a thread owns 8 adjacent columns (16-byte loads: a warp reads 512 contiguous bytes per row),
+// the 8 warps take rows r0 + w, r0 + w + 8, ... (4 rows in flight), partials meet in shared memory, one atomic per column.
+__global__ void __launch_bounds__(256)
+colsum_bf16_kernel(const __nv_bfloat16* __restrict__ a, int64_t lda, float* __restrict__ out, int R, int C) {
+  __shared__ float part[8][256 + 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c0 = blockIdx.x * 256 + lane * 8;
+  const int r0 = blockIdx.y * 256, r1 = min(R, r0 + 256);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c0 < C) {
+    for (int r = r0 + warp; r < r1; r += 32) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int rr = r + u * 8;
+        v[u] = rr < r1 ? __ldg(reinterpret_cast<const uint4*>(a + static_cast<int64_t>(rr) * lda + c0)) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        acc[0] += bf16_lo(v[u].x); acc[1] += bf16_hi(v[u].x);
+        acc[2] += bf16_lo(v[u].y); acc[3] += bf16_hi(v[u].y);
+        acc[4] += bf16_lo(v[u].z); acc[5] += bf16_hi(v[u].z);
+        acc[6] += bf16_lo(v[u].w); acc[7] += bf16_hi(v[u].w);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) part[warp][lane * 8 + i] = acc[i];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < C) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += part[w][threadIdx.x];
+    atomicAdd(out + c, s);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ elementwise
 __global__ void __launch_bounds__(256)
 scale_cast_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ gamma, __nv_bfloat16* __restrict__ out,
@@ -539,7 +578,10 @@ extern "C" int sr_colsum(const void* a, int a_bf16, int64_t lda, const void* b, 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (!accumulate) SR_CHECK_CUDA(cudaMemsetAsync(out, 0, static_cast<size_t>(C) * sizeof(float), st));
   dim3 grid(static_cast<unsigned>((C + 127) / 128), static_cast<unsigned>((R + 127) / 128));
-  if (a_bf16)
+  if (a_bf16 && b == nullptr && C % 8 == 0 && lda % 8 == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0) {
+    dim3 g2(static_cast<unsigned>((C + 255) / 256), static_cast<unsigned>((R + 255) / 256));
+    colsum_bf16_kernel<<<g2, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(a), lda, out, static_cast<int>(R), static_cast<int>(C));
+  } else if (a_bf16)
     colsum_kernel<true><<<grid, 128, 0, st>>>(a, lda, reinterpret_cast<const __nv_bfloat16*>(b), ldb, out, static_cast<int>(R),
                                               static_cast<int>(C));
   else
