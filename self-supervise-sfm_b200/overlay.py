@@ -9,6 +9,10 @@ Replaced: sailrecon.models.aggregator, sailrecon.layers.{attention, block, rope,
 vision_transformer}, sailrecon.heads.camera_head, sailrecon.heads.dpt_head (dpt=True) and the two functions SailRecon binds
 from sailrecon.utils (pose_encoding_to_extri_intri, unproject_depth_map_to_point_map; geometry=True).  SailRecon itself —
 forward / tmp_forward / reloc / clear_cache — stays the reference's code.
+TRAINING (train/train_imc.py:361-381 unchanged): `install(geometry=False, dpt=False, camera_head=False, layers=False)`
+replaces the aggregator only (the reference's heads keep the reference's layers).  Its forward is then one autograd node (train.AggregatorFunction); the reference's own heads, pose / geometry
+functions and loss stay in torch autograd and hand their gradient to that node, so `scaler.scale(loss).backward()` trains
+every parameter of the model (tests/test_overlay_gpu.py::test_training_step_through_overlay).
 Only `sys.modules` aliases are installed; the reference tree is not modified.
 """
 from __future__ import annotations
@@ -19,16 +23,18 @@ import sys
 _LAYER_MODULES = ("attention", "block", "rope", "mlp", "layer_scale", "patch_embed", "vision_transformer")
 
 
-def install(geometry: bool = True, dpt: bool = True) -> None:
+def install(geometry: bool = True, dpt: bool = True, camera_head: bool = True, layers: bool = True) -> None:
     if "sailrecon.models.sail_recon" in sys.modules:
         raise RuntimeError("sailrecon_b200.overlay.install() must run before sailrecon.models.sail_recon is imported")
     pkg = __name__.rsplit(".", 1)[0]
     sys.modules["sailrecon.models.aggregator"] = importlib.import_module(pkg + ".models.aggregator")
-    sys.modules["sailrecon.heads.camera_head"] = importlib.import_module(pkg + ".heads.camera_head")
+    if camera_head:
+        sys.modules["sailrecon.heads.camera_head"] = importlib.import_module(pkg + ".heads.camera_head")
     if dpt:                                          # N1: the two dense heads (sail_recon.py:46-66,129-136,246-252)
         sys.modules["sailrecon.heads.dpt_head"] = importlib.import_module(pkg + ".heads.dpt_head")
-    for name in _LAYER_MODULES:
-        sys.modules[f"sailrecon.layers.{name}"] = importlib.import_module(f"{pkg}.layers.{name}")
+    if layers:       # this package's Aggregator / heads import their layers directly; the aliases serve code that imports
+        for name in _LAYER_MODULES:                  # sailrecon.layers.* itself (and must stay off when reference heads are kept)
+            sys.modules[f"sailrecon.layers.{name}"] = importlib.import_module(f"{pkg}.layers.{name}")
     if geometry:
         # N3: the pose / unprojection step right after the camera head (sail_recon.py:122-124, 139-141).  Only the two
         # names SailRecon binds are replaced; the reference modules keep everything else they define.

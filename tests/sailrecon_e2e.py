@@ -37,8 +37,61 @@ def reinit(model: torch.nn.Module, seed: int) -> None:
                 p.copy_(0.02 * r)
 
 
+PROBES = ("aggregator.frame_blocks.0.attn.qkv.weight", "aggregator.frame_blocks.23.mlp.fc2.weight",
+          "aggregator.global_blocks.11.attn.proj.weight", "aggregator.global_reloc_blocks.5.mlp.fc1.weight",
+          "aggregator.global_reloc_blocks.23.attn.k_norm.weight", "aggregator.patch_embed.blocks.3.attn.qkv.weight",
+          "aggregator.patch_embed.patch_embed.proj.weight", "aggregator.patch_embed.pos_embed", "aggregator.camera_token_reloc",
+          "aggregator.register_token", "camera_head.trunk.0.attn.qkv.weight", "camera_head.pose_branch.fc2.weight",
+          "depth_head.scratch.output_conv1.weight", "point_head.projects.0.weight")
+
+
+def train_main(mode, out_path, Na, Nq, size):
+    """One training forward + backward of the reference's SailRecon exactly as train/train_imc.py:361-381 drives it
+    (model.train(), autocast(bf16) around model.forward, loss.backward()), pure reference vs the aggregator-only overlay."""
+    import make_ref
+    sys.path.insert(0, make_ref.import_path())
+    if mode == "overlay_train":
+        import sailrecon_b200.overlay as overlay
+        overlay.install(geometry=False, dpt=False, camera_head=False, layers=False)
+    from sailrecon.models.sail_recon import SailRecon
+    dev = "cuda"
+    torch.manual_seed(0)
+    with torch.device(dev):
+        model = SailRecon(kv_cache=False).to(dev)
+    reinit(model, 78)
+    model.train()
+    if mode == "overlay_train":
+        import sailrecon_b200.models.aggregator as A
+        assert type(model.aggregator) is A.Aggregator and type(model.camera_head).__module__ == "sailrecon.heads.camera_head"
+    g = torch.Generator().manual_seed(6)
+    images = torch.rand(Na + Nq, 3, size, size, generator=g).to(dev)
+    model.aggregator.generator.manual_seed(1234)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        preds = model.forward(images, no_reloc_list=list(range(Na)), reloc_list=list(range(Na, Na + Nq)), fix_rank=300)
+    gl = torch.Generator(device=dev).manual_seed(7)
+    loss = 0.0
+    for pr in preds:
+        for k in ("extrinsic", "depth_map", "point_map", "xyz_cnf", "dpt_cnf"):
+            v = pr[k].float()
+            loss = loss + (v * torch.randn(v.shape, device=dev, generator=gl)).mean()
+    (1024.0 * loss).backward()                      # GradScaler-style scaling
+    named = dict(model.named_parameters())
+    res = {"loss": np.array(float(loss))}
+    n_grad = sum(1 for p in model.parameters() if p.grad is not None)
+    res["params_with_grad"] = np.array(n_grad)
+    for n in PROBES:
+        gr = named[n].grad
+        assert gr is not None, n
+        res["grad." + n] = (gr.float() / 1024.0).flatten()[:: max(1, gr.numel() // 65536)].cpu().numpy()
+        res["gnorm." + n] = np.array(float(gr.float().norm() / 1024.0))
+    np.savez(out_path, **res)
+    print("e2e ok", mode, n_grad)
+
+
 def main():
     mode, out_path = sys.argv[1], sys.argv[2]
+    if mode.endswith("train"):
+        return train_main(mode, out_path, int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]))
     Na = int(sys.argv[3]) if len(sys.argv) > 3 else 3
     Nq = int(sys.argv[4]) if len(sys.argv) > 4 else 2
     size = int(sys.argv[5]) if len(sys.argv) > 5 else 518
