@@ -232,9 +232,9 @@ static int launch_skinny(const GemmF32Params& p, cudaStream_t st) {
 // Pure weight streaming: a warp owns kTyCols rows of W, lanes split K in float4s (512 contiguous bytes per row and step,
 // kTyUnroll steps in flight), the M rows of A come through L1 (they are re-read by every warp and total <= 256 KB), partial
 // sums are reduced with shuffles.  Grid = N / (kTyCols * kTyWarps) CTAs = 256 ... 1024 for the camera-head shapes.
-constexpr int kTyCols = 2, kTyWarps = 4, kTyUnroll = 4;
+constexpr int kTyWarps = 4, kTyUnroll = 4;   // kTyCols (W rows per warp): 2, or 1 when 2 would leave the grid under ~4 CTAs per SM
 
-template <int EPI, int MR>
+template <int EPI, int MR, int kTyCols>
 __global__ void __launch_bounds__(kTyWarps * 32)
 gemm_f32_tiny_kernel(const GemmF32Params p) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -291,14 +291,19 @@ gemm_f32_tiny_kernel(const GemmF32Params p) {
     }
 }
 
+template <int EPI, int kTyCols>
+static int launch_tiny_c(const GemmF32Params& p, cudaStream_t st) {
+  const unsigned grid = static_cast<unsigned>((p.N + kTyCols * kTyWarps - 1) / (kTyCols * kTyWarps));
+  if (p.M == 1) gemm_f32_tiny_kernel<EPI, 1, kTyCols><<<grid, kTyWarps * 32, 0, st>>>(p);
+  else if (p.M == 2) gemm_f32_tiny_kernel<EPI, 2, kTyCols><<<grid, kTyWarps * 32, 0, st>>>(p);
+  else if (p.M <= 4) gemm_f32_tiny_kernel<EPI, 4, kTyCols><<<grid, kTyWarps * 32, 0, st>>>(p);
+  else gemm_f32_tiny_kernel<EPI, 8, kTyCols><<<grid, kTyWarps * 32, 0, st>>>(p);
+  return SR_OK;
+}
 template <int EPI>
 static int launch_tiny(const GemmF32Params& p, cudaStream_t st) {
-  const unsigned grid = static_cast<unsigned>((p.N + kTyCols * kTyWarps - 1) / (kTyCols * kTyWarps));
-  if (p.M == 1) gemm_f32_tiny_kernel<EPI, 1><<<grid, kTyWarps * 32, 0, st>>>(p);
-  else if (p.M == 2) gemm_f32_tiny_kernel<EPI, 2><<<grid, kTyWarps * 32, 0, st>>>(p);
-  else if (p.M <= 4) gemm_f32_tiny_kernel<EPI, 4><<<grid, kTyWarps * 32, 0, st>>>(p);
-  else gemm_f32_tiny_kernel<EPI, 8><<<grid, kTyWarps * 32, 0, st>>>(p);
-  return SR_OK;
+  // N = 2048 with two columns per warp is 256 CTAs: too few bytes in flight to fill HBM (ncu: 2.0 TB/s against 3.3 TB/s at 1024 CTAs)
+  return p.N <= 4096 ? launch_tiny_c<EPI, 1>(p, st) : launch_tiny_c<EPI, 2>(p, st);
 }
 
 // In-place q/k LayerNorm(d) + 2D RoPE on an fp32 [M, 3C] qkv buffer (check mode; attention.py:78-82).
