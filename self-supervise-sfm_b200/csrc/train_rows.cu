@@ -150,6 +150,50 @@ colsum_bf16_kernel(const __nv_bfloat16* __restrict__ a, int64_t lda, float* __re
   }
 }
 
+// LayerScale gamma gradient: out[c] += sum_r a[r, c] * b[r, c] with a fp32 (the incoming gradient) and b bf16 (the saved Linear
+// output); same 256 x 256 block shape as colsum_bf16_kernel, 2 rows in flight per warp (48 B per lane and row).
+__global__ void __launch_bounds__(256)
+colsum_f32xbf16_kernel(const float* __restrict__ a, int64_t lda, const __nv_bfloat16* __restrict__ b, int64_t ldb,
+                       float* __restrict__ out, int R, int C) {
+  __shared__ float part[8][256 + 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c0 = blockIdx.x * 256 + lane * 8;
+  const int r0 = blockIdx.y * 256, r1 = min(R, r0 + 256);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c0 < C) {
+    for (int r = r0 + warp; r < r1; r += 16) {
+      float4 x0[2], x1[2];
+      uint4 v[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int rr = r + u * 8;
+        const bool ok = rr < r1;
+        const float4* pa = reinterpret_cast<const float4*>(a + static_cast<int64_t>(rr) * lda + c0);
+        x0[u] = ok ? __ldg(pa) : make_float4(0.f, 0.f, 0.f, 0.f);
+        x1[u] = ok ? __ldg(pa + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
+        v[u] = ok ? __ldg(reinterpret_cast<const uint4*>(b + static_cast<int64_t>(rr) * ldb + c0)) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        acc[0] = fmaf(x0[u].x, bf16_lo(v[u].x), acc[0]); acc[1] = fmaf(x0[u].y, bf16_hi(v[u].x), acc[1]);
+        acc[2] = fmaf(x0[u].z, bf16_lo(v[u].y), acc[2]); acc[3] = fmaf(x0[u].w, bf16_hi(v[u].y), acc[3]);
+        acc[4] = fmaf(x1[u].x, bf16_lo(v[u].z), acc[4]); acc[5] = fmaf(x1[u].y, bf16_hi(v[u].z), acc[5]);
+        acc[6] = fmaf(x1[u].z, bf16_lo(v[u].w), acc[6]); acc[7] = fmaf(x1[u].w, bf16_hi(v[u].w), acc[7]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) part[warp][lane * 8 + i] = acc[i];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < C) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += part[w][threadIdx.x];
+    atomicAdd(out + c, s);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ elementwise
 __global__ void __launch_bounds__(256)
 scale_cast_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ gamma, __nv_bfloat16* __restrict__ out,
@@ -581,6 +625,11 @@ extern "C" int sr_colsum(const void* a, int a_bf16, int64_t lda, const void* b, 
   if (a_bf16 && b == nullptr && C % 8 == 0 && lda % 8 == 0 && (reinterpret_cast<uintptr_t>(a) & 15) == 0) {
     dim3 g2(static_cast<unsigned>((C + 255) / 256), static_cast<unsigned>((R + 255) / 256));
     colsum_bf16_kernel<<<g2, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(a), lda, out, static_cast<int>(R), static_cast<int>(C));
+  } else if (!a_bf16 && b != nullptr && C % 8 == 0 && lda % 4 == 0 && ldb % 8 == 0 &&
+             ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) == 0) {
+    dim3 g2(static_cast<unsigned>((C + 255) / 256), static_cast<unsigned>((R + 255) / 256));
+    colsum_f32xbf16_kernel<<<g2, 256, 0, st>>>(reinterpret_cast<const float*>(a), lda, reinterpret_cast<const __nv_bfloat16*>(b), ldb, out,
+                                               static_cast<int>(R), static_cast<int>(C));
   } else if (a_bf16)
     colsum_kernel<true><<<grid, 128, 0, st>>>(a, lda, reinterpret_cast<const __nv_bfloat16*>(b), ldb, out, static_cast<int>(R),
                                               static_cast<int>(C));
