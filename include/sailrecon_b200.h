@@ -319,6 +319,76 @@ int sr_dpt_out_head_f32(const float* h, int64_t ldh, const float* w, const float
                         int32_t hid, int32_t out_dim, int32_t act, int32_t conf_act, int32_t map_h, int32_t map_w, int32_t pad,
                         void* stream);   /* pad = 1: h is a zero-bordered map [S, map_h + 2, map_w + 2, ldh] */
 
+/* ---- self-supervised training loss (train/train_imc.py:141-256) ----------------------------------
+ * All fp32, contiguous.  P = correspondence pairs, K = sampled points per pair, N = frames ("nodes").
+ * `rows` = 3 for [.., 3, 4] poses (pad_poses appends (0, 0, 0, 1), train/utils/geometry.py:36-57) or 4 for [.., 4, 4].     */
+
+/* compute_relative_pose (train/utils/geometry.py:252-287): relative [P, 4, 4] = dst @ inverse(src), and its backward.    */
+int sr_relative_pose_f32(const float* src_extrinsic, const float* dst_extrinsic, int32_t rows, float* relative, int64_t num_pairs,
+                         void* stream);
+int sr_relative_pose_bwd_f32(const float* src_extrinsic, const float* dst_extrinsic, int32_t rows, const float* d_relative,
+                             float* d_src, float* d_dst, int64_t num_pairs, void* stream);
+/* backproject_and_reproject (train/utils/geometry.py:89-158; dst_depth == NULL: perspective division by the projected
+ * depth + 1e-6) and backproject_and_reproject_with_approximation (:160-250; dst_depth [P, K]: division by dst_depth *
+ * dst_scale + 1e-6).  src_coords [P, K, 2], src_depth [P, K], src_k / dst_k [P, 3, 3], relative [P, rows, 4], src_scale /
+ * dst_scale [P] or NULL (= 1) -> out_coords [P, K, 2].  workspace: sr_reproject_workspace_floats(P, K) floats.
+ * The backward returns d src_k, d dst_k [P, 3, 3] and d relative [P, rows, 4] from d out_coords [P, K, 2].                */
+int64_t sr_reproject_workspace_floats(int64_t num_pairs, int64_t num_points);
+int sr_reproject_f32(const float* src_coords, const float* src_depth, const float* dst_depth, const float* src_k,
+                     const float* dst_k, const float* relative, int32_t rows, const float* src_scale, const float* dst_scale,
+                     float* out_coords, int64_t num_pairs, int64_t num_points, float* workspace, void* stream);
+int sr_reproject_bwd_f32(const float* src_coords, const float* src_depth, const float* dst_depth, const float* src_k,
+                         const float* dst_k, const float* relative, int32_t rows, const float* src_scale, const float* dst_scale,
+                         const float* d_coords, float* d_src_k, float* d_dst_k, float* d_relative, int64_t num_pairs,
+                         int64_t num_points, float* workspace, void* stream);
+/* compute_projective_residual (train/utils/geometry.py:289-303): residual[i] = || predicted[i] - actual[i] ||_2 over n points
+ * of 2 coordinates; backward: d predicted = d residual * (predicted - actual) / residual (0 where the residual is 0).      */
+int sr_projective_residual_f32(const float* predicted, const float* actual, float* residual, int64_t n, void* stream);
+int sr_projective_residual_bwd_f32(const float* predicted, const float* actual, const float* d_residual, float* d_predicted,
+                                   int64_t n, void* stream);
+/* CDFLossIndexPytorch.compute_weighted_pdf_cdf_vectorized (train/losses/cdf_loss.py:122-186): residuals, weights [P, K]
+ * (weights NULL = 1), src_idx / dst_idx int64 [P] -> pmf, cdf, pdf [num_nodes, num_bins].  bin = trunc((r - min_val) *
+ * inv_bin_width), inv_bin_width = fp32(1 / bin_width) — torch's GPU division by a Python scalar IS this multiplication
+ * (profiles/r02_div_probe.txt); sobel_weight = fp32(1 / (2 bin_width));
+ * smooth_kernel: device fp32 [2 * smooth_radius + 1] (reflect padding).  hist_total: scratch, num_nodes * (num_bins + 1).  */
+int sr_cdf_tables_f32(const float* residuals, const float* weights, const int64_t* src_idx, const int64_t* dst_idx,
+                      int64_t num_pairs, int64_t num_points, int64_t num_nodes, float min_val, float inv_bin_width,
+                      int32_t num_bins, float sobel_weight, const float* smooth_kernel, int32_t smooth_radius, float* hist_total,
+                      float* pmf, float* cdf, float* pdf, void* stream);
+/* compute_weighted_cdf_forward_backward_vectorized (train/losses/cdf_loss.py:188-242): bin = trunc((r - min_val) *
+ * inv_bin_width + 0.5); valid = in range and weight > 0; out = cdf[frame, bin] (2.0 when invalid), grad = pdf[frame, bin] *
+ * weight (0 when invalid), for the pair's source and destination frame.                                                  */
+int sr_cdf_lookup_f32(const float* residuals, const float* weights, const int64_t* src_idx, const int64_t* dst_idx,
+                      const float* cdf, const float* pdf, int64_t num_pairs, int64_t num_points, float min_val,
+                      float inv_bin_width, int32_t num_bins, float* out_src, float* grad_src, float* out_dst, float* grad_dst,
+                      void* stream);
+/* compute_loss (train/train_imc.py:141-256) in one call: loss AND its gradient w.r.t. the predicted cameras.             */
+typedef struct {
+  const float* pred_intrinsics;   /* [N, 3, 3]    cat(pred['intrinsic']), train_imc.py:156                              */
+  const float* pred_extrinsics;   /* [N, rows, 4] cat(pred['extrinsic']), :175                                          */
+  const float* kprime_to_k;       /* [N, 3, 3] batch['K_prime_to_K'] (:162-165) or NULL = identity                      */
+  const int64_t* src_idx;         /* [P] */
+  const int64_t* dst_idx;         /* [P] */
+  const float* src_coords;        /* [P, K, 2] */
+  const float* dst_coords;        /* [P, K, 2] */
+  const float* src_depth;         /* [P, K] */
+  const float* dst_depth;         /* [P, K] */
+  int64_t num_frames, num_pairs, num_points;
+  int32_t pose_rows;              /* 3 or 4 */
+  int32_t shared_focal;           /* batch['shared_focal'] (:168-172) */
+  float min_val, inv_bin_width, sobel_weight;
+  int32_t num_bins, smooth_radius;
+  const float* smooth_kernel;     /* device fp32 [2 * smooth_radius + 1] */
+  float* workspace;               /* sr_reproj_loss_workspace_floats(N, P, K, num_bins) floats */
+  int64_t workspace_floats;
+  float* loss;                    /* [1] */
+  float* d_intrinsics;            /* [N, 3, 3] */
+  float* d_extrinsics;            /* [N, rows, 4] */
+  float* tables;                  /* optional [3 (pmf, cdf, pdf)][2 (exact, approximated)][N][num_bins], or NULL */
+} sr_reproj_loss_t;
+int64_t sr_reproj_loss_workspace_floats(int64_t num_frames, int64_t num_pairs, int64_t num_points, int32_t num_bins);
+int sr_reproj_cdf_loss_f32(const sr_reproj_loss_t* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

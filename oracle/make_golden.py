@@ -117,7 +117,36 @@ def run_cache_case():
     print(name, {k: v.shape for k, v in arrays.items() if k != "meta"}, os.path.getsize(path), "bytes")
 
 
+LOSS_CASES = {
+    # name: (synthetic_batch kwargs, CDFLossIndexPytorch kwargs) — the second is train_imc.py:333-347's configuration
+    "loss_imc": (dict(num_frames=4, num_points=300, seed=0), dict(min_val=0.0, max_val=15.0, num_bins=250, gradient_smooth=0.05)),
+    # ragged K, shared focal length, residuals beyond max_val (the 2.0 / zero-gradient branch), a 9-tap smoothing filter
+    "loss_shared": (dict(num_frames=3, num_points=257, seed=1, shared_focal=True, cam_sigma=0.01),
+                    dict(min_val=0.0, max_val=4.0, num_bins=64, gradient_smooth=0.2)),
+}
+
+
+def run_loss_case(name):
+    """N4: the reference's own compute_loss (train/train_imc.py:141-270) + torch autograd on the CPU."""
+    import ref_train_import
+    sys.path.insert(0, os.path.dirname(HERE))
+    from sailrecon_b200.losses.synthetic import synthetic_batch
+    batch_kw, cdf_kw = LOSS_CASES[name]
+    train_imc = ref_train_import.import_train_imc("/root/reference")
+    batch = synthetic_batch(**batch_kw)
+    out = ref_train_import.run_reference_loss(train_imc, batch, "cpu", cdf_kw)
+    arrays = {"ref_" + k: v for k, v in out.items()}
+    arrays.update({k: np.asarray(v) for k, v in batch.items()})
+    arrays["meta"] = np.frombuffer(json.dumps({"batch": batch_kw, "cdf": cdf_kw}).encode(), dtype=np.uint8)
+    path = os.path.join(os.path.dirname(HERE), "tests", "golden", name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(name, "loss", out["loss"], os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
+    for n in LOSS_CASES:
+        if len(sys.argv) == 1 or n in sys.argv[1:]:
+            run_loss_case(n)
     for n, c in GOLDEN_CASES.items():
         if len(sys.argv) > 1 and n not in sys.argv[1:]:
             continue

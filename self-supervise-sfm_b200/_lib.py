@@ -67,6 +67,24 @@ class SrAttnBwd(C.Structure):
     ]
 
 
+class SrReprojLoss(C.Structure):
+    """struct sr_reproj_loss_t (include/sailrecon_b200.h)."""
+
+    _fields_ = [
+        ("pred_intrinsics", _vp), ("pred_extrinsics", _vp), ("kprime_to_k", _vp),
+        ("src_idx", _vp), ("dst_idx", _vp),
+        ("src_coords", _vp), ("dst_coords", _vp), ("src_depth", _vp), ("dst_depth", _vp),
+        ("num_frames", _i64), ("num_pairs", _i64), ("num_points", _i64),
+        ("pose_rows", _i32), ("shared_focal", _i32),
+        ("min_val", _f32), ("inv_bin_width", _f32), ("sobel_weight", _f32),
+        ("num_bins", _i32), ("smooth_radius", _i32),
+        ("smooth_kernel", _vp),
+        ("workspace", _vp), ("workspace_floats", _i64),
+        ("loss", _vp), ("d_intrinsics", _vp), ("d_extrinsics", _vp),
+        ("tables", _vp),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/sailrecon_b200.h declares
 SIGNATURES = {
     "sr_version": (C.c_int, []),
@@ -116,6 +134,17 @@ SIGNATURES = {
     "sr_uv_posembed_table": (C.c_int, [_vp, _i64, _i64, _i64, C.c_double, C.c_double, _vp]),
     "sr_dpt_out_head_f32": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _vp]),
     "sr_modulate_f32": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _i64, _vp]),
+    "sr_relative_pose_f32": (C.c_int, [_vp, _vp, _i32, _vp, _i64, _vp]),
+    "sr_relative_pose_bwd_f32": (C.c_int, [_vp, _vp, _i32, _vp, _vp, _vp, _i64, _vp]),
+    "sr_reproject_workspace_floats": (_i64, [_i64, _i64]),
+    "sr_reproject_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
+    "sr_reproject_bwd_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
+    "sr_projective_residual_f32": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
+    "sr_projective_residual_bwd_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp]),
+    "sr_cdf_tables_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _f32, _f32, _i32, _f32, _vp, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "sr_cdf_lookup_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _f32, _i32, _vp, _vp, _vp, _vp, _vp]),
+    "sr_reproj_loss_workspace_floats": (_i64, [_i64, _i64, _i64, _i32]),
+    "sr_reproj_cdf_loss_f32": (C.c_int, [C.POINTER(SrReprojLoss), _vp]),
 }
 
 _lib = None

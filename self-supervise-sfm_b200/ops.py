@@ -827,3 +827,175 @@ def dpt_out_head(h: torch.Tensor, hid: int, w: torch.Tensor, bias: torch.Tensor,
                                                conf.data_ptr(), px, hid, out_dim, _DPT_ACT[activation], _DPT_CONF[conf_activation],
                                                mh, mw, pad, _stream()), "dpt_out_head")
     return pred, conf
+
+
+# ------------------------------------------------------------------------------------------------ training loss (N4)
+def _f32c(t: torch.Tensor, name: str, shape=None) -> torch.Tensor:
+    if not (t.is_cuda and t.dtype == torch.float32):
+        raise ValueError(f"sailrecon_b200: {name} must be a fp32 CUDA tensor (no CPU fallback)")
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise ValueError(f"sailrecon_b200: {name} must have shape {tuple(shape)}, got {tuple(t.shape)}")
+    return t.contiguous()
+
+
+def _idx64(t: torch.Tensor, name: str, n: int) -> torch.Tensor:
+    if not (t.is_cuda and t.dtype == torch.int64 and tuple(t.shape) == (n,)):
+        raise ValueError(f"sailrecon_b200: {name} must be an int64 CUDA tensor [{n}]")
+    return t.contiguous()
+
+
+def _pose_rows(t: torch.Tensor, name: str) -> int:
+    if t.dim() != 3 or tuple(t.shape[-2:]) not in ((3, 4), (4, 4)):
+        raise ValueError(f"sailrecon_b200: {name} must be [P, 3, 4] or [P, 4, 4], got {tuple(t.shape)}")
+    return t.shape[-2]
+
+
+def relative_pose(src_extrinsic: torch.Tensor, dst_extrinsic: torch.Tensor) -> torch.Tensor:
+    """dst @ inverse(src) -> [P, 4, 4] (train/utils/geometry.py:252-287)."""
+    rows = _pose_rows(src_extrinsic, "src_extrinsic")
+    s = _f32c(src_extrinsic, "src_extrinsic")
+    d = _f32c(dst_extrinsic, "dst_extrinsic", s.shape)
+    P = s.shape[0]
+    rel = torch.empty(P, 4, 4, dtype=torch.float32, device=s.device)
+    _lib.check(_lib.load().sr_relative_pose_f32(s.data_ptr(), d.data_ptr(), rows, rel.data_ptr(), P, _stream()), "relative_pose")
+    return rel
+
+
+def relative_pose_bwd(src_extrinsic: torch.Tensor, dst_extrinsic: torch.Tensor, d_rel: torch.Tensor):
+    rows = _pose_rows(src_extrinsic, "src_extrinsic")
+    s = _f32c(src_extrinsic, "src_extrinsic")
+    d = _f32c(dst_extrinsic, "dst_extrinsic", s.shape)
+    P = s.shape[0]
+    g = _f32c(d_rel, "d_rel", (P, 4, 4))
+    ds, dd = torch.empty_like(s), torch.empty_like(d)
+    _lib.check(_lib.load().sr_relative_pose_bwd_f32(s.data_ptr(), d.data_ptr(), rows, g.data_ptr(), ds.data_ptr(), dd.data_ptr(), P,
+                                                    _stream()), "relative_pose_bwd")
+    return ds, dd
+
+
+def _reproject_args(src_coords, src_depth, dst_depth, src_k, dst_k, rel, src_scale, dst_scale):
+    if src_coords.dim() != 3 or src_coords.shape[-1] != 2:
+        raise ValueError("sailrecon_b200: src_coords must be [P, K, 2]")
+    P, K = src_coords.shape[:2]
+    rows = _pose_rows(rel, "relative_pose")
+    c = _f32c(src_coords, "src_coords")
+    z = _f32c(src_depth, "src_depth", (P, K))
+    zd = None if dst_depth is None else _f32c(dst_depth, "dst_depth", (P, K))
+    ks, kd = _f32c(src_k, "src_intrinsic", (P, 3, 3)), _f32c(dst_k, "dst_intrinsic", (P, 3, 3))
+    r = _f32c(rel, "relative_pose", (P, rows, 4))
+    ss = None if src_scale is None else _f32c(src_scale.reshape(-1), "src_depth_scale", (P,))
+    sd = None if dst_scale is None else _f32c(dst_scale.reshape(-1), "dst_depth_scale", (P,))
+    ws = torch.empty(max(1, _lib.load().sr_reproject_workspace_floats(P, K)), dtype=torch.float32, device=c.device)
+    return P, K, rows, c, z, zd, ks, kd, r, ss, sd, ws
+
+
+def reproject(src_coords, src_depth, src_k, dst_k, rel, src_scale=None, dst_depth=None, dst_scale=None) -> torch.Tensor:
+    """backproject_and_reproject (dst_depth None) / ..._with_approximation: predicted destination pixels [P, K, 2]
+    (train/utils/geometry.py:89-250)."""
+    P, K, rows, c, z, zd, ks, kd, r, ss, sd, ws = _reproject_args(src_coords, src_depth, dst_depth, src_k, dst_k, rel, src_scale, dst_scale)
+    out = torch.empty(P, K, 2, dtype=torch.float32, device=c.device)
+    _lib.check(_lib.load().sr_reproject_f32(c.data_ptr(), z.data_ptr(), _ptr(zd), ks.data_ptr(), kd.data_ptr(), r.data_ptr(), rows,
+                                            _ptr(ss), _ptr(sd), out.data_ptr(), P, K, ws.data_ptr(), _stream()), "reproject")
+    return out
+
+
+def reproject_bwd(src_coords, src_depth, src_k, dst_k, rel, d_coords, src_scale=None, dst_depth=None, dst_scale=None):
+    """-> (d src_k [P, 3, 3], d dst_k [P, 3, 3], d relative_pose [P, rows, 4])."""
+    P, K, rows, c, z, zd, ks, kd, r, ss, sd, ws = _reproject_args(src_coords, src_depth, dst_depth, src_k, dst_k, rel, src_scale, dst_scale)
+    g = _f32c(d_coords, "d_coords", (P, K, 2))
+    dks, dkd, dr = torch.zeros_like(ks), torch.zeros_like(kd), torch.zeros_like(r)
+    if P and K:
+        _lib.check(_lib.load().sr_reproject_bwd_f32(c.data_ptr(), z.data_ptr(), _ptr(zd), ks.data_ptr(), kd.data_ptr(), r.data_ptr(),
+                                                    rows, _ptr(ss), _ptr(sd), g.data_ptr(), dks.data_ptr(), dkd.data_ptr(),
+                                                    dr.data_ptr(), P, K, ws.data_ptr(), _stream()), "reproject_bwd")
+    return dks, dkd, dr
+
+
+def projective_residual(predicted: torch.Tensor, actual: torch.Tensor) -> torch.Tensor:
+    """|| predicted - actual ||_2 over the last (size 2) dimension (train/utils/geometry.py:289-303)."""
+    if predicted.shape[-1] != 2 or predicted.shape != actual.shape:
+        raise ValueError("sailrecon_b200: projective_residual needs two [..., 2] tensors of the same shape")
+    a, b = _f32c(predicted, "predicted_dst_coords"), _f32c(actual, "actual_dst_coords")
+    out = torch.empty(a.shape[:-1], dtype=torch.float32, device=a.device)
+    _lib.check(_lib.load().sr_projective_residual_f32(a.data_ptr(), b.data_ptr(), out.data_ptr(), out.numel(), _stream()),
+               "projective_residual")
+    return out
+
+
+def projective_residual_bwd(predicted: torch.Tensor, actual: torch.Tensor, d_res: torch.Tensor) -> torch.Tensor:
+    a, b = _f32c(predicted, "predicted_dst_coords"), _f32c(actual, "actual_dst_coords")
+    g = _f32c(d_res, "d_residual", a.shape[:-1])
+    out = torch.empty_like(a)
+    _lib.check(_lib.load().sr_projective_residual_bwd_f32(a.data_ptr(), b.data_ptr(), g.data_ptr(), out.data_ptr(), g.numel(),
+                                                          _stream()), "projective_residual_bwd")
+    return out
+
+
+def cdf_tables(residuals, weights, src_idx, dst_idx, num_nodes: int, min_val: float, inv_bin_width: float, num_bins: int,
+               sobel_weight: float, smooth_kernel: torch.Tensor):
+    """Per-frame weighted PMF / CDF / PDF tables [num_nodes, num_bins] (train/losses/cdf_loss.py:122-186)."""
+    if residuals.dim() != 2:
+        raise ValueError("sailrecon_b200: residuals must be [N_pairs, K_points]")
+    P, K = residuals.shape
+    r = _f32c(residuals, "residuals")
+    w = None if weights is None else _f32c(weights, "weights", (P, K))
+    s, d = _idx64(src_idx, "src_indices", P), _idx64(dst_idx, "dst_indices", P)
+    sk = _f32c(smooth_kernel.reshape(-1), "smooth_kernel")
+    if sk.numel() % 2 != 1:
+        raise ValueError("sailrecon_b200: the smoothing kernel must have an odd number of taps")
+    scratch = torch.empty(num_nodes * (num_bins + 1), dtype=torch.float32, device=r.device)
+    pmf, cdf, pdf = (torch.empty(num_nodes, num_bins, dtype=torch.float32, device=r.device) for _ in range(3))
+    _lib.check(_lib.load().sr_cdf_tables_f32(r.data_ptr(), _ptr(w), s.data_ptr(), d.data_ptr(), P, K, num_nodes, min_val,
+                                             inv_bin_width, num_bins, sobel_weight, sk.data_ptr(), sk.numel() // 2,
+                                             scratch.data_ptr(), pmf.data_ptr(), cdf.data_ptr(), pdf.data_ptr(), _stream()),
+               "cdf_tables")
+    return pmf, cdf, pdf
+
+
+def cdf_lookup(residuals, weights, src_idx, dst_idx, cdf, pdf, min_val: float, inv_bin_width: float):
+    """-> (cdf_src, grad_src, cdf_dst, grad_dst), each [N_pairs, K_points] (train/losses/cdf_loss.py:188-242)."""
+    P, K = residuals.shape
+    num_bins = cdf.shape[1]
+    r = _f32c(residuals, "residuals")
+    w = None if weights is None else _f32c(weights, "weights", (P, K))
+    s, d = _idx64(src_idx, "src_indices", P), _idx64(dst_idx, "dst_indices", P)
+    c, q = _f32c(cdf, "cdf"), _f32c(pdf, "pdf", cdf.shape)
+    outs = [torch.empty(P, K, dtype=torch.float32, device=r.device) for _ in range(4)]
+    _lib.check(_lib.load().sr_cdf_lookup_f32(r.data_ptr(), _ptr(w), s.data_ptr(), d.data_ptr(), c.data_ptr(), q.data_ptr(), P, K,
+                                             min_val, inv_bin_width, num_bins, *(o.data_ptr() for o in outs), _stream()),
+               "cdf_lookup")
+    return tuple(outs)
+
+
+def reproj_cdf_loss(pred_intrinsics, pred_extrinsics, kprime_to_k, shared_focal: bool, src_idx, dst_idx, src_coords, dst_coords,
+                    src_depth, dst_depth, min_val: float, inv_bin_width: float, num_bins: int, sobel_weight: float,
+                    smooth_kernel: torch.Tensor, want_tables: bool = False):
+    """compute_loss (train/train_imc.py:141-256) fused: -> (loss [1], d intrinsics [N, 3, 3], d extrinsics [N, rows, 4], tables)."""
+    from ._lib import SrReprojLoss
+    if pred_intrinsics.dim() != 3:
+        raise ValueError("sailrecon_b200: predicted intrinsics must be [N, 3, 3]")
+    N = pred_intrinsics.shape[0]
+    rows = _pose_rows(pred_extrinsics, "predicted extrinsics")
+    ki = _f32c(pred_intrinsics, "predicted intrinsics", (N, 3, 3))
+    ex = _f32c(pred_extrinsics, "predicted extrinsics", (N, rows, 4))
+    k2k = None if kprime_to_k is None else _f32c(kprime_to_k, "K_prime_to_K", (N, 3, 3))
+    if src_coords.dim() != 3 or src_coords.shape[-1] != 2:
+        raise ValueError("sailrecon_b200: src_coords must be [num_pairs, K, 2]")
+    P, K = src_coords.shape[:2]
+    sc, dc = _f32c(src_coords, "src_coords"), _f32c(dst_coords, "dst_coords", (P, K, 2))
+    sz, dz = _f32c(src_depth, "src_depth", (P, K)), _f32c(dst_depth, "dst_depth", (P, K))
+    s, d = _idx64(src_idx, "src_idx", P), _idx64(dst_idx, "dst_idx", P)
+    sk = _f32c(smooth_kernel.reshape(-1), "smooth_kernel")
+    lib = _lib.load()
+    n_ws = lib.sr_reproj_loss_workspace_floats(N, P, K, num_bins)
+    ws = torch.empty(n_ws, dtype=torch.float32, device=ki.device)
+    loss = torch.empty(1, dtype=torch.float32, device=ki.device)
+    dki, dex = torch.empty_like(ki), torch.empty_like(ex)
+    tables = torch.empty(3, 2, N, num_bins, dtype=torch.float32, device=ki.device) if want_tables else None
+    a = SrReprojLoss(ki.data_ptr(), ex.data_ptr(), _ptr(k2k), s.data_ptr(), d.data_ptr(), sc.data_ptr(), dc.data_ptr(), sz.data_ptr(),
+                     dz.data_ptr(), N, P, K, rows, int(bool(shared_focal)), min_val, inv_bin_width, sobel_weight, num_bins,
+                     sk.numel() // 2, sk.data_ptr(), ws.data_ptr(), n_ws, loss.data_ptr(), dki.data_ptr(), dex.data_ptr(), _ptr(tables))
+    t = _Timed("reproj_cdf_loss", 0.0, 64.0 * P * K)
+    _lib.check(lib.sr_reproj_cdf_loss_f32(C.byref(a), _stream()), "reproj_cdf_loss")
+    t.done()
+    return loss, dki, dex, tables

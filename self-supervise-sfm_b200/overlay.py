@@ -43,3 +43,17 @@ def install(geometry: bool = True, dpt: bool = True, camera_head: bool = True, l
         ours = importlib.import_module(pkg + ".utils")
         rp.pose_encoding_to_extri_intri = ours.pose_encoding_to_extri_intri
         rg.unproject_depth_map_to_point_map = ours.unproject_depth_map_to_point_map
+
+
+def install_training_loss() -> None:
+    """N4: make train/train_imc.py (imported AFTER this call, with the reference's `train/` directory on sys.path) take
+    `utils.geometry` (train/utils/geometry.py: compute_relative_pose, backproject_and_reproject[_with_approximation],
+    compute_projective_residual) and `losses.cdf_loss` (train/losses/cdf_loss.py: CDFLossIndexPytorch) from this package.
+    The script's own `compute_loss` then runs unchanged on the kernels of csrc/loss.cu; `sailrecon_b200.losses.compute_loss`
+    is the fused replacement for that function itself."""
+    for name in ("train_imc", "utils.geometry", "losses.cdf_loss"):
+        if name in sys.modules:
+            raise RuntimeError(f"sailrecon_b200.overlay.install_training_loss() must run before `{name}` is imported")
+    pkg = __name__.rsplit(".", 1)[0]
+    sys.modules["utils.geometry"] = importlib.import_module(pkg + ".losses.geometry")
+    sys.modules["losses.cdf_loss"] = importlib.import_module(pkg + ".losses.cdf_loss")

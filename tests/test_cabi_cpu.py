@@ -36,15 +36,17 @@ def test_struct_layouts_match_header(tmp_path):
     src = tmp_path / "layout.c"
     src.write_text(
         '#include <stdio.h>\n#include <stddef.h>\n#include "%s"\n'
-        'int main(void) { printf("%%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu\\n", sizeof(sr_epilogue_t), offsetof(sr_epilogue_t, pos), '
+        'int main(void) { printf("%%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu %%zu\\n", sizeof(sr_epilogue_t), offsetof(sr_epilogue_t, pos), '
         'sizeof(sr_attn_t), offsetof(sr_attn_t, carry_in), offsetof(sr_attn_t, lse_pad), sizeof(sr_attn_bwd_t), '
-        'offsetof(sr_attn_bwd_t, num_heads), offsetof(sr_attn_bwd_t, scale)); return 0; }\n' % hdr)
+        'offsetof(sr_attn_bwd_t, num_heads), offsetof(sr_attn_bwd_t, scale), sizeof(sr_reproj_loss_t), '
+        'offsetof(sr_reproj_loss_t, min_val), offsetof(sr_reproj_loss_t, tables)); return 0; }\n' % hdr)
     exe = tmp_path / "layout"
     subprocess.run(["gcc", "-o", str(exe), str(src)], check=True)
     got = [int(x) for x in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()]
     assert got == [ctypes.sizeof(_lib.SrEpilogue), _lib.SrEpilogue.pos.offset, ctypes.sizeof(_lib.SrAttn), _lib.SrAttn.carry_in.offset,
                    _lib.SrAttn.lse_pad.offset, ctypes.sizeof(_lib.SrAttnBwd), _lib.SrAttnBwd.num_heads.offset,
-                   _lib.SrAttnBwd.scale.offset]
+                   _lib.SrAttnBwd.scale.offset, ctypes.sizeof(_lib.SrReprojLoss), _lib.SrReprojLoss.min_val.offset,
+                   _lib.SrReprojLoss.tables.offset]
     assert ctypes.sizeof(_lib.SrEpilogue) == 160 and _lib.SrAttn.carry_in.offset == 168
 
 
