@@ -269,6 +269,10 @@ int sr_pose_update(float* pred, const float* delta, float* activated, int64_t ro
  * principal point (W/2, H/2).  Called at sail_recon.py:122-124, :235-237.                                      */
 int sr_pose_to_extri_intri(const float* pose, float* extrinsics, float* intrinsics, int64_t n, int32_t image_h,
                            int32_t image_w, void* stream);
+/* its backward (the training loss differentiates the predicted cameras, train_imc.py:156,175): d pose [n, 9] from
+ * d extrinsics [n, 3, 4] and d intrinsics [n, 3, 3] (NULL = none; only the two focal entries carry gradient).   */
+int sr_pose_to_extri_intri_bwd(const float* pose, const float* d_extrinsics, const float* d_intrinsics, float* d_pose, int64_t n,
+                               int32_t image_h, int32_t image_w, void* stream);
 /* unproject_depth_map_to_point_map (utils/geometry.py:19-128; numpy on the host in the reference, sail_recon.py:139-141):
  * depth fp32 [S, H, W], extrinsics [S, 3, 4] (camera from world), intrinsics [S, 3, 3] (zero skew) -> world points
  * fp32 [S, H, W, 3] = R^T ((u - cu) d / fu, (v - cv) d / fv, d) - R^T t.  Everything stays in HBM.              */
@@ -388,6 +392,35 @@ typedef struct {
 } sr_reproj_loss_t;
 int64_t sr_reproj_loss_workspace_floats(int64_t num_frames, int64_t num_pairs, int64_t num_points, int32_t num_bins);
 int sr_reproj_cdf_loss_f32(const sr_reproj_loss_t* args, void* stream);
+
+/* ---- camera-head backward, fp32 (sailrecon/heads/camera_head.py:85-186 under autograd; csrc/head_train.cu) -------------
+ * The Linear gradients reuse sr_gemm_f32: dX = dY W on a transposed copy of W, dW = dY^T X with the contraction over the T
+ * camera-token rows (both operands transposed copies).                                                                    */
+int sr_transpose_f32(const float* src, int64_t lds, float* dst, int64_t ldd, int64_t R, int64_t C, void* stream);
+/* out[c] (+)= sum_r a[r, c] * b[r, c] (b NULL = 1): bias gradients and d LayerScale gamma = sum_r dy * z (layer_scale.py:22) */
+int sr_colsum_f32(const float* a, int64_t lda, const float* b, int64_t ldb, float* out, int64_t R, int64_t C, int32_t accumulate,
+                  void* stream);
+/* kind 0: nn.GELU (erf form, mlp.py:23,36); kind 1: nn.SiLU (camera_head.py:72).  out = act(u);  du = dg * act'(u)         */
+int sr_act_f32(const float* u, float* out, int64_t n, int32_t kind, void* stream);
+int sr_act_bwd_f32(const float* u, const float* dg, float* du, int64_t n, int32_t kind, void* stream);
+/* out = resid + gamma[c] * z (gamma NULL = 1), all fp32 contiguous [rows, C] (block.py:110-111 un-fused: z is kept)         */
+int sr_ls_residual_f32f32(const float* resid, const float* z, const float* gamma, float* out, int64_t rows, int64_t C, void* stream);
+/* nn.LayerNorm gradient with an fp32 incoming gradient: dx = (dres ? dres : 0) + dLN(dy); dweight / dbias [C] are ADDED to
+ * (NULL = skip; weight NULL = no affine).  x, dy, dres, dx contiguous [rows, C].                                            */
+int sr_layernorm_bwd_f32(const float* x, const float* weight, const float* dy, const float* dres, float* dx, float* dweight,
+                         float* dbias, int64_t rows, int64_t C, float eps, void* stream);
+/* backward of sr_adaln_modulate_f32 (camera_head.py:151-161): d mod [rows, 3C] = [d shift | d scale | d gate] and dx
+ * (accumulate_dx = 1: dx += ...).                                                                                          */
+int sr_adaln_modulate_bwd_f32(const float* x, const float* mod, const float* dy, float* dx, float* dmod, int64_t rows, int64_t C,
+                              float eps, int32_t accumulate_dx, void* stream);
+/* attention backward over T <= 128 rows with the build_lr_mask structure (camera_head.py:197-228): row r sees column c iff
+ * c < n_anchor or c == r.  q, k, v row views (ld ldqkv), dout (lddo) -> dq, dk, dv (ldd); head h at columns [h * D, +D).     */
+int sr_attn_small_bwd_f32(const float* q, const float* k, const float* v, int64_t ldqkv, const float* dout, int64_t lddo, float* dq,
+                          float* dk, float* dv, int64_t ldd, int64_t T, int32_t num_heads, int32_t head_dim, int64_t n_anchor,
+                          float scale, void* stream);
+/* activate_pose backward (head_act.py:12-37 as SAIL-Recon configures it): d pred = d activated, zero where a FoV entry
+ * (columns 7, 8 of the 9) was clipped by the relu.  pred is the PRE-activation encoding [rows, 9].                           */
+int sr_pose_act_bwd_f32(const float* pred, const float* d_activated, float* d_pred, int64_t rows, void* stream);
 
 #ifdef __cplusplus
 }

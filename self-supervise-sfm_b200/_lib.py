@@ -123,6 +123,7 @@ SIGNATURES = {
     "sr_patchify": (C.c_int, [_vp, _vp, C.c_int, _i64, _i64, _i64, _i64, _i32, C.POINTER(_f32), C.POINTER(_f32), _vp]),
     "sr_pose_update": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
     "sr_pose_to_extri_intri": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp]),
+    "sr_pose_to_extri_intri_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i32, _i32, _vp]),
     "sr_unproject_depth": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _vp]),
     "sr_im2col_split_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _vp]),
     "sr_bilinear_nhwc_f32": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _i64, _i32, _vp]),
@@ -145,6 +146,15 @@ SIGNATURES = {
     "sr_cdf_lookup_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _f32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "sr_reproj_loss_workspace_floats": (_i64, [_i64, _i64, _i64, _i32]),
     "sr_reproj_cdf_loss_f32": (C.c_int, [C.POINTER(SrReprojLoss), _vp]),
+    "sr_transpose_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _vp]),
+    "sr_colsum_f32": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _i64, _i32, _vp]),
+    "sr_act_f32": (C.c_int, [_vp, _vp, _i64, _i32, _vp]),
+    "sr_act_bwd_f32": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
+    "sr_ls_residual_f32f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _vp]),
+    "sr_layernorm_bwd_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _vp]),
+    "sr_adaln_modulate_bwd_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _i32, _vp]),
+    "sr_attn_small_bwd_f32": (C.c_int, [_vp, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i64, _i32, _i32, _i64, _f32, _vp]),
+    "sr_pose_act_bwd_f32": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
 }
 
 _lib = None

@@ -30,7 +30,7 @@ SOURCES = [
     "gemm_tc.cu",
     "attn_tc.cu",
     "attn_tc4.cu",
-    "attn_tc3.cu", "attn_bwd.cu", "train_rows.cu", "pose.cu", "dpt.cu", "loss.cu",
+    "attn_tc3.cu", "attn_bwd.cu", "train_rows.cu", "pose.cu", "dpt.cu", "loss.cu", "head_train.cu",
 ]
 
 NVCC_FLAGS = [

@@ -48,6 +48,42 @@ __global__ void pose_to_extri_intri_kernel(const float* __restrict__ pose, float
   }
 }
 
+// Backward of pose_to_extri_intri_kernel.  R = I + s M(q), s = 2 / |q|^2:  dL/dq_m = s <G, dM/dq_m> - s^2 q_m <G, M>;
+// d fov = d f * -(size / 4) / sin^2(fov / 2)  (f = (size / 2) / tan(fov / 2)).
+__global__ void pose_to_extri_intri_bwd_kernel(const float* __restrict__ pose, const float* __restrict__ d_extri,
+                                               const float* __restrict__ d_intri, float* __restrict__ d_pose, int64_t n, float H,
+                                               float W) {
+  const int64_t r = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+  if (r >= n) return;
+  const float* p = pose + r * 9;
+  const float* g = d_extri + r * 12;
+  const float i = p[3], j = p[4], k = p[5], w = p[6];
+  const float s = 2.0f / (i * i + j * j + k * k + w * w);
+  const float g00 = g[0], g01 = g[1], g02 = g[2], g10 = g[4], g11 = g[5], g12 = g[6], g20 = g[8], g21 = g[9], g22 = g[10];
+  const float gm = g00 * -(j * j + k * k) + g01 * (i * j - k * w) + g02 * (i * k + j * w) + g10 * (i * j + k * w) +
+                   g11 * -(i * i + k * k) + g12 * (j * k - i * w) + g20 * (i * k - j * w) + g21 * (j * k + i * w) +
+                   g22 * -(i * i + j * j);
+  const float di = g01 * j + g02 * k + g10 * j - 2.0f * g11 * i - g12 * w + g20 * k + g21 * w - 2.0f * g22 * i;
+  const float dj = -2.0f * g00 * j + g01 * i + g02 * w + g10 * i + g12 * k - g20 * w + g21 * k - 2.0f * g22 * j;
+  const float dk = -2.0f * g00 * k - g01 * w + g02 * i + g10 * w - 2.0f * g11 * k + g12 * j + g20 * i + g21 * j;
+  const float dw = -g01 * k + g02 * j + g10 * k - g12 * i - g20 * j + g21 * i;
+  float* o = d_pose + r * 9;
+  o[0] = g[3];
+  o[1] = g[7];
+  o[2] = g[11];
+  o[3] = s * di - s * s * i * gm;
+  o[4] = s * dj - s * s * j * gm;
+  o[5] = s * dk - s * s * k * gm;
+  o[6] = s * dw - s * s * w * gm;
+  o[7] = 0.f;
+  o[8] = 0.f;
+  if (d_intri != nullptr) {
+    const float sh = sinf(p[7] / 2.0f), sw = sinf(p[8] / 2.0f);
+    o[7] = d_intri[r * 9 + 4] * (-(H / 4.0f) / (sh * sh));
+    o[8] = d_intri[r * 9 + 0] * (-(W / 4.0f) / (sw * sw));
+  }
+}
+
 // world = R^T (cam - t)  with cam = ((u - cu) d / fu, (v - cv) d / fv, d); (R | t) is camera-from-world, so the inverse of
 // geometry.py:closed_form_inverse_se3 is R^T and -R^T t.  Arithmetic order follows the reference: cam @ R_inv^T + t_inv.
 __global__ void unproject_depth_kernel(const float* __restrict__ depth, const float* __restrict__ extri,
@@ -94,6 +130,20 @@ extern "C" int sr_pose_to_extri_intri(const float* pose, float* extrinsics, floa
   if (n == 0) return SR_OK;
   pose_to_extri_intri_kernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       pose, extrinsics, intrinsics, n, static_cast<float>(image_h), static_cast<float>(image_w));
+  ++g_launch_count;
+  SR_CHECK_CUDA(cudaGetLastError());
+  return SR_OK;
+}
+
+extern "C" int sr_pose_to_extri_intri_bwd(const float* pose, const float* d_extrinsics, const float* d_intrinsics, float* d_pose,
+                                          int64_t n, int32_t image_h, int32_t image_w, void* stream) {
+  using namespace sr;
+  if (int rc = require_sm100()) return rc;
+  if (n == 0) return SR_OK;
+  SR_REQUIRE(pose && d_extrinsics && d_pose && n > 0, "sr_pose_to_extri_intri_bwd: null pointer");
+  SR_REQUIRE(d_intrinsics == nullptr || (image_h > 0 && image_w > 0), "sr_pose_to_extri_intri_bwd: image size required for intrinsics");
+  pose_to_extri_intri_bwd_kernel<<<static_cast<unsigned>((n + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      pose, d_extrinsics, d_intrinsics, d_pose, n, static_cast<float>(image_h), static_cast<float>(image_w));
   ++g_launch_count;
   SR_CHECK_CUDA(cudaGetLastError());
   return SR_OK;

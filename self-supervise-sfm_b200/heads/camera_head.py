@@ -7,6 +7,7 @@ to the anchors and to itself — two launches of the structured attention kernel
 Per refinement iteration: embed_pose+SiLU (one GEMM epilogue), the 2048->6144 modulation GEMM, one fused
 adaLN-modulate-gate-residual kernel, 4 trunk blocks (7 launches each), trunk_norm, pose_branch (2 GEMMs) and one
 accumulate+activate kernel.
+In train() mode with autograd enabled `forward` is one autograd node with an fp32 kernel backward (camera_head_train.py).
 """
 from __future__ import annotations
 
@@ -44,7 +45,9 @@ class CameraHead(nn.Module):
         self.pose_branch = Mlp(in_features=dim_in, hidden_features=dim_in // 2, out_features=self.target_dim, drop=0)
 
     def forward(self, aggregated_tokens_list, cam_token_last_layer: torch.Tensor, num_iterations: int = 4) -> list:
-        engine.forbid_autograd(self, "CameraHead.forward")
+        if self.training and torch.is_grad_enabled():          # train_imc.py:361-381: one autograd node, fp32 backward kernels
+            from .camera_head_train import forward_autograd
+            return forward_autograd(self, aggregated_tokens_list, cam_token_last_layer, num_iterations)
         tokens = aggregated_tokens_list[-1]                                                # camera_head.py:103-109
         pose_q = tokens[:, :, 0]
         if pose_q.shape[0] != 1:

@@ -626,6 +626,21 @@ def pose_to_extri_intri(pose: torch.Tensor, image_hw=None, build_intrinsics: boo
     return ext, intr
 
 
+def pose_to_extri_intri_bwd(pose: torch.Tensor, d_ext: torch.Tensor, d_intr: Optional[torch.Tensor], image_hw=None) -> torch.Tensor:
+    """-> d pose [..., 9] (the gradient of pose_to_extri_intri)."""
+    p = pose.contiguous()
+    n = p.numel() // 9
+    ge = d_ext.contiguous().float()
+    gi = None if d_intr is None else d_intr.contiguous().float()
+    if ge.numel() != n * 12 or (gi is not None and gi.numel() != n * 9):
+        raise ValueError("sailrecon_b200: pose_to_extri_intri_bwd shape mismatch")
+    H, W = (0, 0) if gi is None else (int(image_hw[0]), int(image_hw[1]))
+    out = torch.empty_like(p)
+    _lib.check(_lib.load().sr_pose_to_extri_intri_bwd(p.data_ptr(), ge.data_ptr(), _ptr(gi), out.data_ptr(), n, H, W, _stream()),
+               "pose_to_extri_intri_bwd")
+    return out
+
+
 def unproject_depth(depth: torch.Tensor, extrinsics: torch.Tensor, intrinsics: torch.Tensor) -> torch.Tensor:
     """depth fp32 [S, H, W], extrinsics [S, 3, 4], intrinsics [S, 3, 3] -> world points [S, H, W, 3]; utils/geometry.py:19-128."""
     for t, name in ((depth, "depth"), (extrinsics, "extrinsics"), (intrinsics, "intrinsics")):
@@ -999,3 +1014,117 @@ def reproj_cdf_loss(pred_intrinsics, pred_extrinsics, kprime_to_k, shared_focal:
     _lib.check(lib.sr_reproj_cdf_loss_f32(C.byref(a), _stream()), "reproj_cdf_loss")
     t.done()
     return loss, dki, dex, tables
+
+
+# ------------------------------------------------------------------------------------------------ camera-head backward (fp32)
+def _f32_rows(t: torch.Tensor, name: str) -> torch.Tensor:
+    _rows2d(t, torch.float32, name)
+    if not t.is_contiguous():
+        raise ValueError(f"sailrecon_b200: {name} must be contiguous")
+    return t
+
+
+def transpose_f32(src: torch.Tensor) -> torch.Tensor:
+    """[R, C] fp32 (row stride >= C) -> contiguous [C, R]."""
+    _rows2d(src, torch.float32, "src")
+    R, C_ = src.shape
+    dst = torch.empty(C_, R, dtype=torch.float32, device=src.device)
+    _lib.check(_lib.load().sr_transpose_f32(src.data_ptr(), src.stride(0), dst.data_ptr(), R, R, C_, _stream()), "transpose_f32")
+    return dst
+
+
+def colsum_f32(a: torch.Tensor, b: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+               accumulate: bool = False) -> torch.Tensor:
+    """out[c] (+)= sum_r a[r, c] * b[r, c]."""
+    _rows2d(a, torch.float32, "a")
+    R, C_ = a.shape
+    if b is not None:
+        _rows2d(b, torch.float32, "b")
+        if b.shape != a.shape:
+            raise ValueError("sailrecon_b200: colsum_f32 shape mismatch")
+    if out is None:
+        out, accumulate = torch.empty(C_, dtype=torch.float32, device=a.device), False
+    _vec(out, C_, "out")
+    _lib.check(_lib.load().sr_colsum_f32(a.data_ptr(), a.stride(0), _ptr(b), b.stride(0) if b is not None else 0, out.data_ptr(), R, C_,
+                                         int(accumulate), _stream()), "colsum_f32")
+    return out
+
+
+_ACT_KIND = {"gelu": 0, "silu": 1}
+
+
+def act_f32(u: torch.Tensor, kind: str) -> torch.Tensor:
+    u = _f32_rows(u, "u")
+    out = torch.empty_like(u)
+    _lib.check(_lib.load().sr_act_f32(u.data_ptr(), out.data_ptr(), u.numel(), _ACT_KIND[kind], _stream()), "act_f32")
+    return out
+
+
+def act_bwd_f32(u: torch.Tensor, dg: torch.Tensor, kind: str) -> torch.Tensor:
+    u, dg = _f32_rows(u, "u"), _f32_rows(dg, "dg")
+    if u.shape != dg.shape:
+        raise ValueError("sailrecon_b200: act_bwd_f32 shape mismatch")
+    du = torch.empty_like(u)
+    _lib.check(_lib.load().sr_act_bwd_f32(u.data_ptr(), dg.data_ptr(), du.data_ptr(), u.numel(), _ACT_KIND[kind], _stream()), "act_bwd_f32")
+    return du
+
+
+def ls_residual_f32(resid: torch.Tensor, z: torch.Tensor, gamma: Optional[torch.Tensor]) -> torch.Tensor:
+    resid, z = _f32_rows(resid, "resid"), _f32_rows(z, "z")
+    if resid.shape != z.shape:
+        raise ValueError("sailrecon_b200: ls_residual_f32 shape mismatch")
+    _vec(gamma, z.shape[1], "gamma")
+    out = torch.empty_like(resid)
+    _lib.check(_lib.load().sr_ls_residual_f32f32(resid.data_ptr(), z.data_ptr(), _ptr(gamma), out.data_ptr(), z.shape[0], z.shape[1],
+                                                 _stream()), "ls_residual_f32")
+    return out
+
+
+def layernorm_bwd_f32(x: torch.Tensor, weight: Optional[torch.Tensor], dy: torch.Tensor, eps: float,
+                      dres: Optional[torch.Tensor] = None, dweight: Optional[torch.Tensor] = None,
+                      dbias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dx = (dres or 0) + dLN(dy); dweight / dbias (fp32 [C]) are added to in place."""
+    x, dy = _f32_rows(x, "x"), _f32_rows(dy, "dy")
+    if x.shape != dy.shape or (dres is not None and _f32_rows(dres, "dres").shape != x.shape):
+        raise ValueError("sailrecon_b200: layernorm_bwd_f32 shape mismatch")
+    for t, n in ((weight, "weight"), (dweight, "dweight"), (dbias, "dbias")):
+        _vec(t, x.shape[1], n)
+    dx = torch.empty_like(x)
+    _lib.check(_lib.load().sr_layernorm_bwd_f32(x.data_ptr(), _ptr(weight), dy.data_ptr(), _ptr(dres), dx.data_ptr(), _ptr(dweight),
+                                                _ptr(dbias), x.shape[0], x.shape[1], eps, _stream()), "layernorm_bwd_f32")
+    return dx
+
+
+def adaln_modulate_bwd(x: torch.Tensor, mod: torch.Tensor, dy: torch.Tensor, eps: float, dx: torch.Tensor, accumulate_dx: bool):
+    """-> d mod [T, 3C]; dx (=|+=) gradient w.r.t. x."""
+    x, mod, dy, dx = _f32_rows(x, "x"), _f32_rows(mod, "mod"), _f32_rows(dy, "dy"), _f32_rows(dx, "dx")
+    T, C_ = x.shape
+    if mod.shape != (T, 3 * C_) or dy.shape != x.shape or dx.shape != x.shape:
+        raise ValueError("sailrecon_b200: adaln_modulate_bwd shape mismatch")
+    dmod = torch.empty_like(mod)
+    _lib.check(_lib.load().sr_adaln_modulate_bwd_f32(x.data_ptr(), mod.data_ptr(), dy.data_ptr(), dx.data_ptr(), dmod.data_ptr(), T, C_,
+                                                     eps, int(accumulate_dx), _stream()), "adaln_modulate_bwd")
+    return dmod
+
+
+def attn_small_bwd_f32(qkv: torch.Tensor, dout: torch.Tensor, num_heads: int, n_anchor: int, scale: float) -> torch.Tensor:
+    """qkv fp32 [T, 3C] (q | k | v), dout [T, C] -> d qkv [T, 3C]; visibility: column < n_anchor or the row itself."""
+    qkv, dout = _f32_rows(qkv, "qkv"), _f32_rows(dout, "dout")
+    T, C3 = qkv.shape
+    C_ = C3 // 3
+    if dout.shape != (T, C_) or C_ % num_heads:
+        raise ValueError("sailrecon_b200: attn_small_bwd_f32 shape mismatch")
+    d = torch.empty_like(qkv)
+    _lib.check(_lib.load().sr_attn_small_bwd_f32(qkv.data_ptr(), qkv[:, C_:].data_ptr(), qkv[:, 2 * C_:].data_ptr(), C3, dout.data_ptr(),
+                                                 C_, d.data_ptr(), d[:, C_:].data_ptr(), d[:, 2 * C_:].data_ptr(), C3, T, num_heads,
+                                                 C_ // num_heads, n_anchor, scale, _stream()), "attn_small_bwd_f32")
+    return d
+
+
+def pose_act_bwd(pred: torch.Tensor, d_act: torch.Tensor) -> torch.Tensor:
+    pred, d_act = _f32_rows(pred, "pred"), _f32_rows(d_act, "d_activated")
+    if pred.shape != d_act.shape or pred.shape[1] != 9:
+        raise ValueError("sailrecon_b200: pose_act_bwd needs two [T, 9] tensors")
+    out = torch.empty_like(pred)
+    _lib.check(_lib.load().sr_pose_act_bwd_f32(pred.data_ptr(), d_act.data_ptr(), out.data_ptr(), pred.shape[0], _stream()), "pose_act_bwd")
+    return out

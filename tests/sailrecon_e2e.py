@@ -53,6 +53,9 @@ def train_main(mode, out_path, Na, Nq, size):
     if mode == "overlay_train":
         import sailrecon_b200.overlay as overlay
         overlay.install(geometry=False, dpt=False, camera_head=False, layers=False)
+    if mode == "overlay_train_full":        # aggregator + camera head + pose -> cameras on this package; the reference's DPT heads
+        import sailrecon_b200.overlay as overlay
+        overlay.install(dpt=False)
     from sailrecon.models.sail_recon import SailRecon
     dev = "cuda"
     torch.manual_seed(0)
@@ -63,6 +66,11 @@ def train_main(mode, out_path, Na, Nq, size):
     if mode == "overlay_train":
         import sailrecon_b200.models.aggregator as A
         assert type(model.aggregator) is A.Aggregator and type(model.camera_head).__module__ == "sailrecon.heads.camera_head"
+    if mode == "overlay_train_full":
+        import sailrecon_b200.heads.camera_head as H
+        import sailrecon_b200.models.aggregator as A
+        assert type(model.aggregator) is A.Aggregator and type(model.camera_head) is H.CameraHead
+        assert type(model.depth_head).__module__ == "sailrecon.heads.dpt_head"
     g = torch.Generator().manual_seed(6)
     images = torch.rand(Na + Nq, 3, size, size, generator=g).to(dev)
     model.aggregator.generator.manual_seed(1234)

@@ -99,9 +99,12 @@ def test_inference_forwards_refuse_training_mode_with_autograd():
         agg(torch.zeros(1, 2, 3, 56, 56), [0], [1])
     for call in (lambda: blk(x), lambda: att(x),
                  lambda: agg.forward_with_cache(torch.zeros(1, 1, 3, 56, 56)),
-                 lambda: head({-1: torch.zeros(1, 1, 5, 256)}, torch.zeros(1, 1, 256))):
+                 lambda: head.trunk_fn(torch.zeros(1, 2, 256), None, 1)):
         with pytest.raises(RuntimeError, match="inference path"):
             call()
+    # CameraHead.forward dispatches to its autograd node (heads/camera_head_train.py) in train() mode; no CPU path there either
+    with pytest.raises(RuntimeError, match="CUDA"):
+        head({-1: torch.zeros(1, 1, 5, 256)}, torch.zeros(1, 1, 256))
     # eval() or no_grad(): the guard is silent (the call then fails on the CPU tensor instead — no CPU fallback)
     blk.eval()
     with pytest.raises(RuntimeError, match="CUDA"):

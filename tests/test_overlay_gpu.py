@@ -83,3 +83,20 @@ def test_training_step_through_overlay(tmp_path):
         assert np.isfinite(ours["grad." + k]).all(), k
         tol = 2.5e-1 if k.startswith(("depth_head", "point_head")) else (5e-2 if k.startswith("camera_head") else 3e-2)
         assert e < tol, (k, e)
+
+
+def test_training_step_through_overlay_with_our_camera_head(tmp_path):
+    """As above with `overlay.install(dpt=False)`: the Aggregator, the CameraHead (one fp32 autograd node,
+    heads/camera_head_train.py) and pose_encoding_to_extri_intri (utils/pose_enc.py, kernel backward) all come from this
+    package; only the two DPT heads are the reference's.  Same probes, same tolerances; the camera-head parameters now
+    compare this package's fp32 backward kernels with torch autograd (upstream noise: the bf16 aggregator tokens)."""
+    ref = _run("ref_train", str(tmp_path / "ref_t.npz"), 2, 2, 518)
+    ours = _run("overlay_train_full", str(tmp_path / "ours_f.npz"), 2, 2, 518)
+    assert int(ours["params_with_grad"]) == int(ref["params_with_grad"])
+    assert abs(float(ours["loss"]) - float(ref["loss"])) <= 2e-2 * max(1.0, abs(float(ref["loss"])))
+    errs = {k[5:]: _rel(ours[k], ref[k]) for k in ref if k.startswith("grad.")}
+    print("full-overlay training parity", {k: f"{v:.2e}" for k, v in sorted(errs.items())})
+    for k, e in errs.items():
+        assert np.isfinite(ours["grad." + k]).all(), k
+        tol = 2.5e-1 if k.startswith(("depth_head", "point_head")) else (5e-2 if k.startswith("camera_head") else 3e-2)
+        assert e < tol, (k, e)
