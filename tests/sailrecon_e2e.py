@@ -98,7 +98,7 @@ def train_main(mode, out_path, Na, Nq, size):
 
 def main():
     mode, out_path = sys.argv[1], sys.argv[2]
-    if mode.endswith("train"):
+    if "train" in mode:
         return train_main(mode, out_path, int(sys.argv[3]), int(sys.argv[4]), int(sys.argv[5]))
     Na = int(sys.argv[3]) if len(sys.argv) > 3 else 3
     Nq = int(sys.argv[4]) if len(sys.argv) > 4 else 2
