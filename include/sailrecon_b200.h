@@ -197,6 +197,14 @@ int sr_ls_residual_f32(const float* resid, const void* z, const float* gamma, fl
 /* mlp.py:36 on the saved pre-activation u (bf16): g = gelu_erf(u);  du = dg * gelu'(u)                         */
 int sr_gelu_fwd_bf16(const void* u, void* out, int64_t n, void* stream);
 int sr_gelu_bwd_bf16(const void* u, const void* dg, void* du, int64_t n, void* stream);
+/* Fused forms (one pass over the rows, column sums by shared-memory partials + one atomic per column and block):
+ * sr_ls_bwd_bf16: LayerScale backward — dz = bf16(dy * gamma) (the gradient entering the Linear under the LayerScale),
+ *   dgamma[c] += sum_r dy * z, dbias[c] += sum_r float(dz) (the Linear's bias gradient; NULL = skip).  dy fp32, z / dz bf16.
+ * sr_gelu_bwd_colsum_bf16: du = bf16(dg * gelu'(u)) (du may alias dg) and dbias[c] += sum_r float(du) (fc1's bias gradient). */
+int sr_ls_bwd_bf16(const float* dy, int64_t lddy, const void* z, int64_t ldz, const float* gamma, void* dz, int64_t lddz,
+                   float* dgamma, float* dbias, int64_t rows, int64_t C, void* stream);
+int sr_gelu_bwd_colsum_bf16(const void* u, int64_t ldu, const void* dg, int64_t lddg, void* du, int64_t lddu, float* dbias,
+                            int64_t rows, int64_t C, void* stream);
 /* LayerNorm gradient (block.py norm1 / norm2, C = 1024): dx = dres + dLN(dy), where dres (fp32) is the gradient arriving
  * over the residual connection (NULL = dx itself, i.e. dx += dLN(dy); dres may alias dx); dweight / dbias (fp32 [C],
  * accumulated with atomics; NULL = skip).  x fp32, dy bf16.                                                         */

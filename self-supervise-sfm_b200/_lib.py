@@ -146,6 +146,8 @@ SIGNATURES = {
     "sr_cdf_lookup_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _f32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "sr_reproj_loss_workspace_floats": (_i64, [_i64, _i64, _i64, _i32]),
     "sr_reproj_cdf_loss_f32": (C.c_int, [C.POINTER(SrReprojLoss), _vp]),
+    "sr_ls_bwd_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _vp, _i64, _vp, _vp, _i64, _i64, _vp]),
+    "sr_gelu_bwd_colsum_bf16": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i64, _vp]),
     "sr_transpose_f32": (C.c_int, [_vp, _i64, _vp, _i64, _i64, _i64, _vp]),
     "sr_colsum_f32": (C.c_int, [_vp, _i64, _vp, _i64, _vp, _i64, _i64, _i32, _vp]),
     "sr_act_f32": (C.c_int, [_vp, _vp, _i64, _i32, _vp]),

@@ -274,6 +274,128 @@ gelu_kernel(const __nv_bfloat16* __restrict__ u, const __nv_bfloat16* __restrict
   *reinterpret_cast<uint4*>(out + e) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
 }
 
+// LayerScale backward in ONE pass (round 2, late): reads the incoming gradient dy (fp32) and the saved Linear output z (bf16)
+// once and produces everything block.py:110-111 needs from them —
+//   dz[r, c]    = bf16(dy * gamma[c])          (the gradient entering the Linear under the LayerScale)
+//   dgamma[c]  += sum_r dy * z                 (layer_scale.py:22)
+//   dbias[c]   += sum_r float(dz)              (the Linear's bias gradient: column sums of the ROUNDED dz, as colsum(dz) gives)
+// 8 B per element instead of the 14 B of colsum(dy, z) + scale_cast + colsum(dz).  Same 256 x 256 block shape as
+// colsum_f32xbf16_kernel; two atomics per column and block.
+__global__ void __launch_bounds__(256)
+ls_bwd_kernel(const float* __restrict__ dy, int64_t lddy, const __nv_bfloat16* __restrict__ z, int64_t ldz,
+              const float* __restrict__ gamma, __nv_bfloat16* __restrict__ dz, int64_t lddz, float* __restrict__ dgamma,
+              float* __restrict__ dbias, int R, int C) {
+  __shared__ float part[2][8][256 + 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c0 = blockIdx.x * 256 + lane * 8;
+  const int r0 = blockIdx.y * 256, r1 = min(R, r0 + 256);
+  float ag[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, ab[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c0 < C) {
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c0)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c0) + 1);
+    const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    for (int r = r0 + warp; r < r1; r += 16) {
+      float4 x0[2], x1[2];
+      uint4 v[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int rr = r + u * 8;
+        const bool ok = rr < r1;
+        const float4* pa = reinterpret_cast<const float4*>(dy + static_cast<int64_t>(rr) * lddy + c0);
+        x0[u] = ok ? __ldg(pa) : make_float4(0.f, 0.f, 0.f, 0.f);
+        x1[u] = ok ? __ldg(pa + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
+        v[u] = ok ? __ldg(reinterpret_cast<const uint4*>(z + static_cast<int64_t>(rr) * ldz + c0)) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int rr = r + u * 8;
+        if (rr >= r1) continue;
+        const float d[8] = {x0[u].x, x0[u].y, x0[u].z, x0[u].w, x1[u].x, x1[u].y, x1[u].z, x1[u].w};
+        const float zz[8] = {bf16_lo(v[u].x), bf16_hi(v[u].x), bf16_lo(v[u].y), bf16_hi(v[u].y),
+                             bf16_lo(v[u].z), bf16_hi(v[u].z), bf16_lo(v[u].w), bf16_hi(v[u].w)};
+        uint32_t o[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          ag[2 * i] = fmaf(d[2 * i], zz[2 * i], ag[2 * i]);
+          ag[2 * i + 1] = fmaf(d[2 * i + 1], zz[2 * i + 1], ag[2 * i + 1]);
+          o[i] = pack_bf16x2(d[2 * i] * gm[2 * i], d[2 * i + 1] * gm[2 * i + 1]);
+          ab[2 * i] += bf16_lo(o[i]);
+          ab[2 * i + 1] += bf16_hi(o[i]);
+        }
+        *reinterpret_cast<uint4*>(dz + static_cast<int64_t>(rr) * lddz + c0) = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { part[0][warp][lane * 8 + i] = ag[i]; part[1][warp][lane * 8 + i] = ab[i]; }
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < C) {
+    float sg = 0.f, sb = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { sg += part[0][w][threadIdx.x]; sb += part[1][w][threadIdx.x]; }
+    atomicAdd(dgamma + c, sg);
+    if (dbias) atomicAdd(dbias + c, sb);
+  }
+}
+
+// GELU backward with the fc1 bias gradient in the same pass: du = bf16(dg * gelu'(u)) (in place over dg allowed) and
+// dbias[c] += sum_r float(du) — saves the separate colsum(du) read of the [T, 4096] gradient.
+__global__ void __launch_bounds__(256)
+gelu_bwd_colsum_kernel(const __nv_bfloat16* __restrict__ u, int64_t ldu, const __nv_bfloat16* dg, int64_t lddg, __nv_bfloat16* du,
+                       int64_t lddu, float* __restrict__ dbias, int R, int C) {
+  __shared__ float part[8][256 + 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c0 = blockIdx.x * 256 + lane * 8;
+  const int r0 = blockIdx.y * 256, r1 = min(R, r0 + 256);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c0 < C) {
+    for (int r = r0 + warp; r < r1; r += 16) {
+      uint4 uu[2], gg[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int rr = r + k * 8;
+        const bool ok = rr < r1;
+        uu[k] = ok ? __ldg(reinterpret_cast<const uint4*>(u + static_cast<int64_t>(rr) * ldu + c0)) : make_uint4(0u, 0u, 0u, 0u);
+        gg[k] = ok ? *reinterpret_cast<const uint4*>(dg + static_cast<int64_t>(rr) * lddg + c0) : make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const int rr = r + k * 8;
+        if (rr >= r1) continue;
+        const uint32_t uw[4] = {uu[k].x, uu[k].y, uu[k].z, uu[k].w}, gw[4] = {gg[k].x, gg[k].y, gg[k].z, gg[k].w};
+        uint32_t ow[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float rv[2];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const float x = h ? bf16_hi(uw[i]) : bf16_lo(uw[i]);
+            float erf_abs, e;
+            erf_gauss(x, erf_abs, e);
+            const float cdf = 0.5f + copysignf(0.5f * erf_abs, x);
+            rv[h] = (h ? bf16_hi(gw[i]) : bf16_lo(gw[i])) * fmaf(x, 0.39894228040143267794f * e, cdf);
+          }
+          ow[i] = pack_bf16x2(rv[0], rv[1]);
+          acc[2 * i] += bf16_lo(ow[i]);
+          acc[2 * i + 1] += bf16_hi(ow[i]);
+        }
+        *reinterpret_cast<uint4*>(du + static_cast<int64_t>(rr) * lddu + c0) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) part[warp][lane * 8 + i] = acc[i];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < C) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += part[w][threadIdx.x];
+    atomicAdd(dbias + c, s);
+  }
+}
+
+
 // ------------------------------------------------------------------------------------------------ LayerNorm backward
 // One warp per row, lane holds columns {128 i + 4 lane .. +3}, i < NCH (C = 128 NCH).  dx = dres + rstd * (g - mean(g) -
 // xhat * mean(g * xhat)) with g = dy * w.  The per-column dw / db partials live in shared memory (each lane owns its own
@@ -676,6 +798,39 @@ extern "C" int sr_gelu_bwd_bf16(const void* u, const void* dg, void* du, int64_t
   SR_REQUIRE(u && dg && du && n > 0 && n % 8 == 0, "sr_gelu_bwd_bf16: n must be a positive multiple of 8");
   gelu_kernel<1><<<static_cast<unsigned>((n / 8 + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<const __nv_bfloat16*>(u), reinterpret_cast<const __nv_bfloat16*>(dg), reinterpret_cast<__nv_bfloat16*>(du), n);
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_ls_bwd_bf16(const float* dy, int64_t lddy, const void* z, int64_t ldz, const float* gamma, void* dz, int64_t lddz,
+                              float* dgamma, float* dbias, int64_t rows, int64_t C, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(dy && z && gamma && dz && dgamma && rows > 0 && C > 0, "sr_ls_bwd_bf16: bad arguments");
+  SR_REQUIRE(C % 8 == 0 && lddy % 4 == 0 && ldz % 8 == 0 && lddz % 8 == 0 && lddy >= C && ldz >= C && lddz >= C &&
+                 ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(dz) |
+                   reinterpret_cast<uintptr_t>(gamma)) & 15) == 0,
+             "sr_ls_bwd_bf16: needs C % 8 == 0 and 16-byte aligned rows");
+  SR_REQUIRE(rows < (1ll << 31) && (rows + 255) / 256 <= 65535, "sr_ls_bwd_bf16: too many rows");
+  dim3 grid(static_cast<unsigned>((C + 255) / 256), static_cast<unsigned>((rows + 255) / 256));
+  ls_bwd_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      dy, lddy, reinterpret_cast<const __nv_bfloat16*>(z), ldz, gamma, reinterpret_cast<__nv_bfloat16*>(dz), lddz, dgamma, dbias,
+      static_cast<int>(rows), static_cast<int>(C));
+  SR_LAUNCHED();
+  return SR_OK;
+}
+
+extern "C" int sr_gelu_bwd_colsum_bf16(const void* u, int64_t ldu, const void* dg, int64_t lddg, void* du, int64_t lddu, float* dbias,
+                                       int64_t rows, int64_t C, void* stream) {
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(u && dg && du && dbias && rows > 0 && C > 0, "sr_gelu_bwd_colsum_bf16: bad arguments");
+  SR_REQUIRE(C % 8 == 0 && ldu % 8 == 0 && lddg % 8 == 0 && lddu % 8 == 0 && ldu >= C && lddg >= C && lddu >= C &&
+                 ((reinterpret_cast<uintptr_t>(u) | reinterpret_cast<uintptr_t>(dg) | reinterpret_cast<uintptr_t>(du)) & 15) == 0,
+             "sr_gelu_bwd_colsum_bf16: needs C % 8 == 0 and 16-byte aligned rows");
+  SR_REQUIRE(rows < (1ll << 31) && (rows + 255) / 256 <= 65535, "sr_gelu_bwd_colsum_bf16: too many rows");
+  dim3 grid(static_cast<unsigned>((C + 255) / 256), static_cast<unsigned>((rows + 255) / 256));
+  gelu_bwd_colsum_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(u), ldu, reinterpret_cast<const __nv_bfloat16*>(dg), lddg,
+      reinterpret_cast<__nv_bfloat16*>(du), lddu, dbias, static_cast<int>(rows), static_cast<int>(C));
   SR_LAUNCHED();
   return SR_OK;
 }

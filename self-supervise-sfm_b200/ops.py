@@ -397,6 +397,37 @@ def scale_cast_bf16(x: torch.Tensor, gamma: Optional[torch.Tensor], out: torch.T
     return out
 
 
+def ls_bwd(dy: torch.Tensor, z: torch.Tensor, gamma: torch.Tensor, dz: torch.Tensor, dgamma: torch.Tensor,
+           dbias: Optional[torch.Tensor]) -> torch.Tensor:
+    """LayerScale backward in one pass: dz = bf16(dy * gamma); dgamma += colsum(dy * z); dbias += colsum(dz) (None = skip)."""
+    _rows2d(dy, torch.float32, "dy")
+    _rows2d(z, torch.bfloat16, "z")
+    _rows2d(dz, torch.bfloat16, "dz")
+    if not (dy.shape == z.shape == dz.shape):
+        raise ValueError("sailrecon_b200: ls_bwd shape mismatch")
+    for t_, n_ in ((gamma, "gamma"), (dgamma, "dgamma"), (dbias, "dbias")):
+        _vec(t_, dy.shape[1], n_)
+    tm = _Timed("ls_bwd", 0.0, 8.0 * dy.numel())
+    _lib.check(_lib.load().sr_ls_bwd_bf16(dy.data_ptr(), dy.stride(0), z.data_ptr(), z.stride(0), gamma.data_ptr(), dz.data_ptr(),
+                                          dz.stride(0), dgamma.data_ptr(), _ptr(dbias), dy.shape[0], dy.shape[1], _stream()), "ls_bwd")
+    tm.done()
+    return dz
+
+
+def gelu_bwd_colsum(u: torch.Tensor, dg: torch.Tensor, du: torch.Tensor, dbias: torch.Tensor) -> torch.Tensor:
+    """du = bf16(dg * gelu'(u)) (du may be dg) and dbias += colsum(du)."""
+    for t_, n_ in ((u, "u"), (dg, "dg"), (du, "du")):
+        _rows2d(t_, torch.bfloat16, n_)
+    if not (u.shape == dg.shape == du.shape):
+        raise ValueError("sailrecon_b200: gelu_bwd_colsum shape mismatch")
+    _vec(dbias, u.shape[1], "dbias")
+    tm = _Timed("gelu_bwd", 0.0, 6.0 * u.numel())
+    _lib.check(_lib.load().sr_gelu_bwd_colsum_bf16(u.data_ptr(), u.stride(0), dg.data_ptr(), dg.stride(0), du.data_ptr(), du.stride(0),
+                                                   dbias.data_ptr(), u.shape[0], u.shape[1], _stream()), "gelu_bwd_colsum")
+    tm.done()
+    return du
+
+
 def ls_residual(resid: torch.Tensor, z: torch.Tensor, gamma: Optional[torch.Tensor], out: torch.Tensor) -> torch.Tensor:
     _rows2d(resid, torch.float32, "resid")
     _rows2d(z, torch.bfloat16, "z")

@@ -138,17 +138,23 @@ def _acc(grads: Dict[nn.Parameter, torch.Tensor], p: Optional[nn.Parameter]) -> 
     return grads[p]
 
 
+# One-pass LayerScale / GELU backward kernels that also produce the bias gradients (sr_ls_bwd_bf16, sr_gelu_bwd_colsum_bf16).
+# False = the separate colsum / scale_cast / gelu_bwd launches they replace (kept as the A/B reference of the tests).
+FUSED_ROW_BACKWARD = True
+
+
 def linear_backward(lin: nn.Module, a_in: torch.Tensor, dz: torch.Tensor, grads: Dict[nn.Parameter, torch.Tensor],
-                    need_input_grad: bool = True, use_transposes: bool = False) -> Optional[torch.Tensor]:
+                    need_input_grad: bool = True, use_transposes: bool = False, bias_done: bool = False) -> Optional[torch.Tensor]:
     """Gradients of z = a_in W^T + b (nn.Linear): dW += dz^T a_in, db += colsum(dz) (fp32 accumulators in `grads`), returns
     d a_in = dz W (bf16).  a_in [T, K] bf16, dz [T, N] bf16 — both GEMMs on the tcgen05 kernel, reading dz, a_in and W AS THEY
     LIE in memory (MN-major operand descriptors, sr_gemm_bf16_t): no transposed copies, and dW accumulates in fp32 straight
     into the gradient bucket.  use_transposes=True is the round-1 path (explicit bf16 transposes + the K-major kernel), kept
-    as the A/B reference of tests/test_train_gpu.py."""
+    as the A/B reference of tests/test_train_gpu.py.  bias_done: the kernel that produced dz already added its column sums to
+    the bias gradient (ops.ls_bwd / ops.gelu_bwd_colsum)."""
     T, K = a_in.shape
     N = dz.shape[1]
     dev = a_in.device
-    gb = _acc(grads, lin.bias) if lin.bias is not None else None
+    gb = _acc(grads, lin.bias) if (lin.bias is not None and not bias_done) else None
     gw = _acc(grads, lin.weight)
     if N % 128 or K % 128:
         raise NotImplementedError("sailrecon_b200: Linear gradients need in / out features that are multiples of 128")
@@ -193,21 +199,34 @@ def block_backward(blk: nn.Module, s: BlockSaved, dy: torch.Tensor, grads: Dict[
     dx1 = torch.empty_like(dy)                                     # = dy (residual path of x2 = x1 + g2 z2) + MLP branch
     # ---- MLP branch
     g2 = engine.gamma_of(blk.ls2)
-    if g2 is not None:
-        ops.colsum(dy, s.z2, _acc(grads, blk.ls2.gamma), accumulate=True)
-    dz2 = ops.scale_cast_bf16(dy, g2, torch.empty(T, C, dtype=BF, device=dev))
-    dg = linear_backward(mlp.fc2, s.g, dz2, grads)
-    du = ops.gelu_bwd(s.u, dg, dg)                                 # in place over dg
-    dh2 = linear_backward(mlp.fc1, s.h2, du, grads)
+    dz2 = torch.empty(T, C, dtype=BF, device=dev)
+    fused2 = FUSED_ROW_BACKWARD and g2 is not None and mlp.fc2.bias is not None
+    if fused2:                                                     # d gamma2, dz2 and fc2's bias gradient in one pass
+        ops.ls_bwd(dy, s.z2, g2, dz2, _acc(grads, blk.ls2.gamma), _acc(grads, mlp.fc2.bias))
+    else:
+        if g2 is not None:
+            ops.colsum(dy, s.z2, _acc(grads, blk.ls2.gamma), accumulate=True)
+        ops.scale_cast_bf16(dy, g2, dz2)
+    dg = linear_backward(mlp.fc2, s.g, dz2, grads, bias_done=fused2)
+    fused_u = FUSED_ROW_BACKWARD and mlp.fc1.bias is not None
+    if fused_u:                                                    # in place over dg, fc1's bias gradient in the same pass
+        du = ops.gelu_bwd_colsum(s.u, dg, dg, _acc(grads, mlp.fc1.bias))
+    else:
+        du = ops.gelu_bwd(s.u, dg, dg)
+    dh2 = linear_backward(mlp.fc1, s.h2, du, grads, bias_done=fused_u)
     w2, _, eps2 = engine.ln_params(blk.norm2)
     ops.layernorm_bwd(s.x1, w2, dh2, dx1, _acc(grads, blk.norm2.weight), _acc(grads, blk.norm2.bias), eps2, dres=dy)
     # ---- attention branch
     dx = out if out is not None else torch.empty_like(dy)          # = dx1 (residual path of x1 = x + g1 z1) + attention branch
     g1 = engine.gamma_of(blk.ls1)
-    if g1 is not None:
-        ops.colsum(dx1, s.z1, _acc(grads, blk.ls1.gamma), accumulate=True)
-    dz1 = ops.scale_cast_bf16(dx1, g1, dz2)                        # dz2 is free again
-    do = linear_backward(attn.proj, s.o, dz1, grads)
+    fused1 = FUSED_ROW_BACKWARD and g1 is not None and attn.proj.bias is not None
+    if fused1:
+        dz1 = ops.ls_bwd(dx1, s.z1, g1, dz2, _acc(grads, blk.ls1.gamma), _acc(grads, attn.proj.bias))   # dz2 is free again
+    else:
+        if g1 is not None:
+            ops.colsum(dx1, s.z1, _acc(grads, blk.ls1.gamma), accumulate=True)
+        dz1 = ops.scale_cast_bf16(dx1, g1, dz2)
+    do = linear_backward(attn.proj, s.o, dz1, grads, bias_done=fused1)
     dqkv = torch.empty(T, 3 * C, dtype=BF, device=dev)
     q, k, v = s.qkv[:, :C], s.qkv[:, C:2 * C], s.qkv[:, 2 * C:]
     dq, dk, dv = dqkv[:, :C], dqkv[:, C:2 * C], dqkv[:, 2 * C:]

@@ -73,6 +73,58 @@ def test_gelu_fwd_bwd():
     assert rel_l2(du.float().cpu(), uf.grad.cpu()) < 4e-3
 
 
+def test_fused_ls_bwd_and_gelu_bwd_colsum_equal_the_separate_launches():
+    """sr_ls_bwd_bf16 == colsum(dy, z) + scale_cast(dy, gamma) + colsum(dz); sr_gelu_bwd_colsum_bf16 == gelu_bwd + colsum(du):
+    the bf16 outputs bit-identical, the column sums to fp32 summation order.  Ragged row counts, strided inputs, in place."""
+    from sailrecon_b200 import ops
+    for R in (1, 255, 333, 1374 * 3):
+        dy, gam = _randn(R, 1024, seed=R), _randn(1024, seed=7)
+        zwide = _randn(R, 2048, seed=R + 1).to(BF)
+        z = zwide[:, 512:1536]                                               # strided view
+        dg0, db0 = torch.full((1024,), 0.5, device=DEV), torch.full((1024,), -0.25, device=DEV)
+        dz = ops.ls_bwd(dy, z, gam, torch.empty(R, 1024, dtype=BF, device=DEV), dg0, db0)
+        ref_dz = ops.scale_cast_bf16(dy, gam, torch.empty(R, 1024, dtype=BF, device=DEV))
+        assert torch.equal(dz, ref_dz)
+        rg, rb = torch.full((1024,), 0.5, device=DEV), torch.full((1024,), -0.25, device=DEV)
+        ops.colsum(dy, z.contiguous(), rg, accumulate=True)
+        ops.colsum(ref_dz, None, rb, accumulate=True)
+        assert rel_l2(dg0.cpu(), rg.cpu()) < 1e-5 and rel_l2(db0.cpu(), rb.cpu()) < 1e-5
+        assert rel_l2(dg0.cpu(), (0.5 + (dy.double() * z.double()).sum(0)).float().cpu()) < 1e-5
+        dg1 = torch.zeros(1024, device=DEV)
+        ops.ls_bwd(dy, z, gam, dz, dg1, None)                                # no bias: skipped
+        u, dgr = _randn(R, 4096, seed=R + 2, scale=2.0).to(BF), _randn(R, 4096, seed=R + 3).to(BF)
+        ref_du = ops.gelu_bwd(u, dgr, torch.empty_like(u))
+        rb4 = torch.zeros(4096, device=DEV)
+        ops.colsum(ref_du, None, rb4, accumulate=True)
+        b4 = torch.zeros(4096, device=DEV)
+        work = dgr.clone()
+        du = ops.gelu_bwd_colsum(u, work, work, b4)                          # in place over the incoming gradient
+        assert du.data_ptr() == work.data_ptr() and torch.equal(du, ref_du)
+        assert rel_l2(b4.cpu(), rb4.cpu()) < 1e-5
+
+
+def test_block_backward_fused_row_kernels_equal_the_separate_ones():
+    from sailrecon_b200 import engine, train
+    blk = _rand_block(9)
+    T = 450
+    x, dy = _randn(T, 1024, seed=30), _randn(T, 1024, seed=31)
+    pos = _positions(3, 150)
+    rp = engine.RowPositions(pos.to(torch.int32).contiguous(), int(pos.max()) + 1)
+    res = []
+    for fused in (True, False):
+        train.FUSED_ROW_BACKWARD = fused
+        try:
+            saved = train.block_forward_saving(blk, x, engine.full_segments(3, 150), rp)
+            grads = {}
+            dx = train.block_backward(blk, saved, dy, grads)
+        finally:
+            train.FUSED_ROW_BACKWARD = True
+        res.append((dx, grads))
+    assert torch.equal(res[0][0], res[1][0])
+    for p_, g_ in res[0][1].items():
+        assert rel_l2(g_.cpu(), res[1][1][p_].cpu()) < 1e-5
+
+
 def test_layernorm_bwd():
     from sailrecon_b200 import ops
     T, C = 203, 1024
