@@ -353,6 +353,19 @@ int sr_reproject_bwd_f32(const float* src_coords, const float* src_depth, const 
                          const float* dst_k, const float* relative, int32_t rows, const float* src_scale, const float* dst_scale,
                          const float* d_coords, float* d_src_k, float* d_dst_k, float* d_relative, int64_t num_pairs,
                          int64_t num_points, float* workspace, void* stream);
+/* No counterpart in the reference (PyTorch allocates whatever it needs).  sr_reproject_f32 for callers that cannot hand
+ * over a workspace because they are not allowed to allocate device memory: a plugin inside another engine's closed memory
+ * pool, a localisation loop that must not touch cudaMalloc once it is running, a worker that owns nothing but the buffers
+ * passed to it.  Same arguments minus `workspace`, same kernels, same result bit for bit.  The per-pair camera records go
+ * into a fixed 512 KiB array built into the library (held on every GPU the library is loaded on, until the process ends),
+ * so num_pairs <= sr_reproject_static_max_pairs() (4096); more is SR_ERR_SHAPE with a message, never a partial result.
+ * The call itself allocates nothing, on either side.  Its first use on a GPU looks the array's address up (do it once at
+ * start-up with that GPU current, before capturing any stream).  All calls on one GPU share the array: calls that may run
+ * concurrently there corrupt each other, so serialise them on a stream.  Nothing has to be cleared between calls.          */
+int64_t sr_reproject_static_max_pairs(void);
+int sr_reproject_static_f32(const float* src_coords, const float* src_depth, const float* dst_depth, const float* src_k,
+                            const float* dst_k, const float* relative, int32_t rows, const float* src_scale,
+                            const float* dst_scale, float* out_coords, int64_t num_pairs, int64_t num_points, void* stream);
 /* compute_projective_residual (train/utils/geometry.py:289-303): residual[i] = || predicted[i] - actual[i] ||_2 over n points
  * of 2 coordinates; backward: d predicted = d residual * (predicted - actual) / residual (0 where the residual is 0).      */
 int sr_projective_residual_f32(const float* predicted, const float* actual, float* residual, int64_t n, void* stream);

@@ -139,6 +139,8 @@ SIGNATURES = {
     "sr_relative_pose_bwd_f32": (C.c_int, [_vp, _vp, _i32, _vp, _vp, _vp, _i64, _vp]),
     "sr_reproject_workspace_floats": (_i64, [_i64, _i64]),
     "sr_reproject_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
+    "sr_reproject_static_max_pairs": (_i64, []),
+    "sr_reproject_static_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _i64, _i64, _vp]),
     "sr_reproject_bwd_f32": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "sr_projective_residual_f32": (C.c_int, [_vp, _vp, _vp, _i64, _vp]),
     "sr_projective_residual_bwd_f32": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _vp]),

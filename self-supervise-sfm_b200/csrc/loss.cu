@@ -23,6 +23,8 @@
 // pivoting — same value up to fp32 rounding.  Histogram sums are fp32 atomics: exact and order-independent for the unit
 // weights compute_loss uses (train_imc.py:238-240), order-dependent in the last bit for general weights exactly like
 // torch's scatter_add_.
+#include <mutex>
+
 #include "common.cuh"
 #include "sr_internal.h"
 
@@ -980,6 +982,75 @@ extern "C" int sr_reproj_cdf_loss_f32(const sr_reproj_loss_t* a, void* stream) {
   g_launch_count += 7;
   if (a->tables != nullptr)
     SR_CHECK_CUDA(cudaMemcpyAsync(a->tables, tables, sizeof(float) * 6 * N * bins, cudaMemcpyDeviceToDevice, st));
+  SR_CHECK_CUDA(cudaGetLastError());
+  return SR_OK;
+}
+
+// ---- sr_reproject_static_f32: the forward reprojection for callers that may not allocate device memory ----------------------
+// sr_reproject_f32 needs kPairStride floats of scratch per pair (the per-pair camera record the set-up kernel writes and the
+// point kernel reads) and expects the caller to bring it.  Some hosts can't: a plugin running inside somebody else's
+// engine whose memory pool is closed to it, a real-time localisation loop that promised "no cudaMalloc after start-up", a
+// process that only borrows the buffers its parent hands over.  For them the scratch lives here, inside the loaded library:
+// one fixed array per GPU, resident from the moment the module is loaded on that GPU until the process exits.
+//
+// The first call on each GPU (made with that GPU current) asks the runtime where the array sits on it and remembers the
+// answer; make that first call during start-up, ahead of any stream capture.  There is one array per GPU and every call
+// writes it from record 0, so two calls that can be in flight on the same GPU at once (different streams, different threads)
+// overwrite each other's records: keep them on one stream or order them with events.
+//
+// kStaticMaxPairs is the price/limit trade: 4096 pairs * 32 floats = 512 KiB per GPU.  Larger batches are refused, not split.
+constexpr int64_t kStaticMaxPairs = 4096;
+constexpr int kStaticMaxDevices = 64;
+static __device__ __align__(256) float g_static_pair_records[kStaticMaxPairs * sr::kPairStride];
+
+namespace {
+// In host code `g_static_pair_records` is only a handle for the runtime to look the symbol up with; the address the
+// kernels must be given is whatever cudaGetSymbolAddress reports for the device that is current, and each device has its own.
+float* g_static_pair_ptr[kStaticMaxDevices];   // written once per device, under g_static_mutex
+std::mutex g_static_mutex;
+
+int static_pair_records(float** out) {
+  int dev = -1;
+  SR_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kStaticMaxDevices) return sr::fail(SR_ERR_SHAPE, "sr_reproject_static_f32: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (g_static_pair_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    SR_CHECK_CUDA(cudaGetSymbolAddress(&p, g_static_pair_records));
+    if (p == nullptr) return sr::fail(SR_ERR_CUDA, "sr_reproject_static_f32: cudaGetSymbolAddress returned a null address");
+    g_static_pair_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_static_pair_ptr[dev];
+  return SR_OK;
+}
+}  // namespace
+
+extern "C" int64_t sr_reproject_static_max_pairs(void) { return kStaticMaxPairs; }
+
+extern "C" int sr_reproject_static_f32(const float* src_coords, const float* src_depth, const float* dst_depth, const float* src_k,
+                                       const float* dst_k, const float* relative, int32_t rows, const float* src_scale,
+                                       const float* dst_scale, float* out_coords, int64_t num_pairs, int64_t num_points,
+                                       void* stream) {
+  using namespace sr;
+  if (int rc = require_sm100()) return rc;
+  SR_REQUIRE(rows == 3 || rows == 4, "sr_reproject_static_f32: relative pose must be [P, 3, 4] or [P, 4, 4]");
+  SR_REQUIRE(num_pairs >= 0 && num_points >= 0 && num_points < (1 << 30), "sr_reproject_static_f32: bad shape");
+  SR_REQUIRE(num_pairs <= kStaticMaxPairs,
+             "sr_reproject_static_f32: %lld pairs exceed the built-in scratch (%lld pairs); split the batch or call "
+             "sr_reproject_f32 with a caller-owned workspace",
+             static_cast<long long>(num_pairs), static_cast<long long>(kStaticMaxPairs));
+  if (num_pairs == 0 || num_points == 0) return SR_OK;
+  SR_REQUIRE(src_coords && src_depth && src_k && dst_k && relative && out_coords, "sr_reproject_static_f32: null pointer");
+  float* records = nullptr;
+  if (int rc = static_pair_records(&records)) return rc;
+  cudaStream_t st = as_stream(stream);
+  // Nothing to clear: the set-up kernel rewrites all kPairStride floats of every record [0, num_pairs) and the point kernel
+  // reads only those, so what an earlier call left behind is never seen.
+  pair_setup_pairs_kernel<<<blocks_for(num_pairs, 64), 64, 0, st>>>(src_k, dst_k, relative, rows, records, num_pairs);
+  dim3 grid(blocks_for(num_points, kPointThreads), static_cast<unsigned>(num_pairs));
+  reproject_kernel<<<grid, kPointThreads, 0, st>>>(src_coords, src_depth, dst_depth, src_scale, dst_scale, records, out_coords,
+                                                   static_cast<int>(num_points));
+  g_launch_count += 2;
   SR_CHECK_CUDA(cudaGetLastError());
   return SR_OK;
 }
