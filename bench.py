@@ -1044,6 +1044,8 @@ def main():
     ap.add_argument("--ring-frames", type=int, default=512)
     ap.add_argument("--ring-depth", type=int, default=None, help="global blocks of the ring workload (24) / the sharded record (4)")
     args = ap.parse_args()
+    import faulthandler
+    faulthandler.enable(all_threads=False)          # SIGABRT / SIGSEGV: say on stderr which Python call the rank was in
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -1151,33 +1153,7 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(tt[0]), float(tt[1])
 
-    extras = {}
-    if headline and not args.no_extras:
-        # parity against / timing of the live reference on the same GPU (rank 0 at N = 1: one model pair per box)
-        if world == 1:
-            try:
-                extras.update(parity_and_library_baseline(agg, head, images, Na, Nq))
-            except Exception as e:                                   # the checker failing must not hide the measurement
-                extras["parity"] = {"error": f"{type(e).__name__}: {e}"}
-        del images, poses
-        from sailrecon_b200 import engine, parallel
-        engine.WS.clear()
-        torch.cuda.empty_cache()
-        # configs[3] at reduced depth, sharded over the N ranks (strong scaling) + parity of the ring across N
-        rec = parallel.ring_measure(args.ring_frames, args.ring_depth or 4, 3, 1, rank, world, dev)
-        rec["ring_parity_rel_l2_vs_unsharded"] = parallel.ring_parity(rank, world, dev) if world > 1 else None
-        extras["sharded"] = rec
-        torch.cuda.empty_cache()
-        # configs[4]: the training step, one scene per rank, gradients all-reduced (DDP) + Adam
-        tr = train_measure(args, rank, world, dev, agg, 24, 3, 2, True, profile=True, e2e=False)
-        extras["train24"] = {k: tr[k] for k in ("ms_per_step", "frames_per_s", "steps", "warmup", "gpu_launches",
-                                                "algorithmic_tflop_per_step", "tensor_frac_whole_step", "outputs_finite",
-                                                "hbm_peak_gb", "trainable_params")}
-        extras["train24"]["workload"] = ("train24: 12 anchors + 12 queries, 518 px, forward + backward + per-layer NCCL gradient "
-                                         "all-reduce + Adam of the 3 x 24 aggregator blocks, one scene per GPU (weak scaling)")
-        extras["train24"]["roofline"] = tr.get("roofline")
-        extras["train24"]["kernels_ms"] = {k: round(v["ms_per_step"], 3) for k, v in (tr.get("kernels") or {}).items()}
-
+    line = None
     if rank == 0:
         peak_tf, peak_src = load_peak_tf()
         prof = summarize_profile(records)
@@ -1210,6 +1186,53 @@ def main():
             "tensor_frac_whole_step": fl["total"] / step_s / 1e12 / peak_tf,
             "outputs_finite": finite,
         }
+
+    extras = {}
+    if headline and not args.no_extras:
+        if rank == 0 and world > 1:
+            # (Multi-GPU runs only: the single-GPU line stays the one line it always was.)  The measurement is complete at this point; the records below are additions to it.  If one of them brings the
+            # process down (a device fault ends in NCCL's watchdog calling abort(), which no Python handler survives), this
+            # line is what remains on stdout; otherwise the full line printed at the end repeats it and is the last one.
+            print(json.dumps({**line, "partial": "headline only - the complete line (same numbers + parity / sharded / "
+                                                 "train24 / cpu_baseline records) follows unless an extra killed the process"}),
+                  flush=True)
+        # parity against / timing of the live reference on the same GPU (rank 0 at N = 1: one model pair per box)
+        if world == 1:
+            try:
+                extras.update(parity_and_library_baseline(agg, head, images, Na, Nq))
+            except Exception as e:                                   # the checker failing must not hide the measurement
+                extras["parity"] = {"error": f"{type(e).__name__}: {e}"}
+        del images, poses
+        from sailrecon_b200 import engine, parallel
+        engine.WS.clear()
+        torch.cuda.empty_cache()
+        # configs[3] at reduced depth, sharded over the N ranks (strong scaling) + parity of the ring across N
+        # An extra that raises (out of memory on a smaller board, a shape it does not support) is recorded as an error and must
+        # not take the headline measurement above with it.  (A device-side fault is different: the CUDA context is gone and
+        # NCCL's watchdog aborts the process; faulthandler, enabled in main(), then says on stderr which call it was in.)
+        try:
+            rec = parallel.ring_measure(args.ring_frames, args.ring_depth or 4, 3, 1, rank, world, dev)
+            rec["ring_parity_rel_l2_vs_unsharded"] = parallel.ring_parity(rank, world, dev) if world > 1 else None
+            extras["sharded"] = rec
+        except Exception as e:
+            extras["sharded"] = {"error": f"{type(e).__name__}: {e}"}
+            print(f"[bench rank {rank}] sharded extra failed: {type(e).__name__}: {e}", file=sys.stderr, flush=True)
+        torch.cuda.empty_cache()
+        # configs[4]: the training step, one scene per rank, gradients all-reduced (DDP) + Adam
+        try:
+            tr = train_measure(args, rank, world, dev, agg, 24, 3, 2, True, profile=True, e2e=False)
+            extras["train24"] = {k: tr[k] for k in ("ms_per_step", "frames_per_s", "steps", "warmup", "gpu_launches",
+                                                    "algorithmic_tflop_per_step", "tensor_frac_whole_step", "outputs_finite",
+                                                    "hbm_peak_gb", "trainable_params")}
+            extras["train24"]["workload"] = ("train24: 12 anchors + 12 queries, 518 px, forward + backward + per-layer NCCL gradient "
+                                             "all-reduce + Adam of the 3 x 24 aggregator blocks, one scene per GPU (weak scaling)")
+            extras["train24"]["roofline"] = tr.get("roofline")
+            extras["train24"]["kernels_ms"] = {k: round(v["ms_per_step"], 3) for k, v in (tr.get("kernels") or {}).items()}
+        except Exception as e:
+            extras["train24"] = {"error": f"{type(e).__name__}: {e}"}
+            print(f"[bench rank {rank}] train24 extra failed: {type(e).__name__}: {e}", file=sys.stderr, flush=True)
+
+    if rank == 0:
         line.update(extras)
         if world == 1 and not args.no_cpu_baseline and headline:
             try:

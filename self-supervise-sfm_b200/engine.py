@@ -87,6 +87,17 @@ class Workspace:
     def clear(self):
         self._buf.clear()
 
+    def detach(self, stream: int, device=None) -> list:
+        """Forget (and hand back) every buffer of the raw stream handle `stream`: nothing is evicted otherwise, so each
+        stream that ever ran a forward keeps its own scratch set (multi-GB at 32 frames of 518 px) for the life of the
+        process, and torch recycles raw handles from a 32-entry pool — a later owner of the same handle would otherwise
+        grow / replace buffers somebody else still uses.  The caller either drops the returned list (memory goes back
+        to the allocator once the stream's work is done) or keeps it alive (localize.Localizer: a captured CUDA graph
+        holds the addresses)."""
+        dev = None if device is None else torch.device(device)
+        keys = [k for k in self._buf if k[2] == stream and (dev is None or k[1] == dev)]
+        return [self._buf.pop(k) for k in keys]
+
 
 WS = Workspace()
 

@@ -38,6 +38,9 @@ class Localizer:
         self.cam_token_last_layer: Optional[torch.Tensor] = None
         self._graph = None
         self._key = None
+        self._keep: list = []
+        self._params: list = []
+        self._stamp = None
         self._stream: Optional[torch.cuda.Stream] = None
 
     # ---------------------------------------------------------------------------------------------- phase 1
@@ -49,6 +52,10 @@ class Localizer:
         self.head._anchor_kv = None
         self._graph = None
         self._key = None
+        self._keep = []                   # the graph's scratch (owned here since _capture) goes back to the allocator
+        if self._stream is not None:      # and whatever the eager warm-up of a half-finished capture left under this stream
+            engine.WS.detach(self._stream.cuda_stream)
+            ops.detach_attn_workspace(self._stream.cuda_stream)
 
     def build(self, anchor_images: torch.Tensor) -> torch.Tensor:
         """SailRecon.tmp_forward (sail_recon.py:176-199): anchor_images [Na, 3, H, W] (or [1, Na, 3, H, W]) in [0, 1]."""
@@ -83,11 +90,21 @@ class Localizer:
         if not self.use_graph:
             return self._pipeline(imgs)
         key = (tuple(imgs.shape), imgs.device)
-        if self._graph is None or self._key != key:
+        if self._graph is None or self._key != key or self._weights_stamp() != self._stamp:
             self._capture(imgs, key)
         self._static_in.copy_(imgs, non_blocking=True)
         self._graph.replay()
         return self._static_out
+
+    def _weights_stamp(self):
+        """The graph bakes in the addresses of the bf16 weight copies engine._cached made at capture time; an optimizer step,
+        load_state_dict or .to() after that would leave it replaying stale weights.  Sum of the parameters' in-place
+        version counters + their addresses' xor: ~0.1 ms of Python per call, checked before every replay."""
+        v, a = 0, 0
+        for p in self._params:
+            v += p._version
+            a ^= p.data_ptr()
+        return v, a
 
     def _capture(self, imgs: torch.Tensor, key) -> None:
         """Warm up on a side stream (lazy per-kernel attributes, bf16 weight copies, position / RoPE tables), then record
@@ -95,6 +112,9 @@ class Localizer:
         dev = imgs.device
         if self._stream is None:
             self._stream = torch.cuda.Stream(device=dev)
+        self._graph, self._keep = None, []
+        self._params = list(self.agg.parameters()) + list(self.head.parameters())
+        self._stamp = self._weights_stamp()
         self._static_in = imgs.clone()
         self._stream.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(self._stream):
@@ -106,9 +126,12 @@ class Localizer:
         with torch.cuda.graph(g, stream=self._stream):
             self._static_out = self._pipeline(self._static_in)
         self._graph, self._key = g, key
-        # the graph holds raw addresses of the per-stream scratch buffers: keep them alive even if engine.WS is cleared
+        # The graph holds raw addresses of the scratch the warm-up allocated under this stream's handle (engine.WS and the
+        # split-KV workspace a single under-filled query launch uses).  Take them OUT of the shared tables and own them:
+        # torch hands stream handles out of a 32-entry pool, so another Localizer / user stream with the same handle could
+        # otherwise grow or replace a buffer this graph still writes; now it simply gets buffers of its own.
         sid = self._stream.cuda_stream
-        self._keep = [buf for k, buf in engine.WS._buf.items() if k[2] == sid]
+        self._keep = engine.WS.detach(sid, dev) + ops.detach_attn_workspace(sid, dev)
 
 
 # ------------------------------------------------------------------------------------------------ bench.py --workload reloc

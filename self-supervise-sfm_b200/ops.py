@@ -296,6 +296,13 @@ def _attn_workspace(nbytes: int, device) -> torch.Tensor:
     return buf
 
 
+def detach_attn_workspace(stream: int, device=None) -> list:
+    """Forget (and return) the split-KV scratch of the raw stream handle `stream` — see engine.Workspace.detach."""
+    dev = None if device is None else torch.device(device)
+    keys = [k for k in _ATTN_WS if k[1] == stream and (dev is None or k[0] == dev)]
+    return [_ATTN_WS.pop(k) for k in keys]
+
+
 def new_lse(num_heads: int, batch: int, q_len: int, device) -> torch.Tensor:
     """Row log-sum-exp buffer of attention(..., lse=) / attention_bwd: [num_heads, batch, q_len rounded up to 64], +inf."""
     return torch.full((num_heads, batch, (q_len + 63) // 64 * 64), float("inf"), dtype=torch.float32, device=device)
@@ -890,6 +897,20 @@ def _idx64(t: torch.Tensor, name: str, n: int) -> torch.Tensor:
     return t.contiguous()
 
 
+def _check_pair_indices(src_idx: torch.Tensor, dst_idx: torch.Tensor, n: int, what: str) -> None:
+    """Every pair index must name one of the n frames: the loss kernels index histograms, totals, cameras and CDF tables with
+    them unchecked (csrc/loss.cu), where the reference's scatter_add_ / gather raise a device-side assert (cdf_loss.py:150-160,
+    :219-226).  One reduction + one host read per index tensor; the verdict is remembered ON the tensor object (with its
+    in-place version counter and n), so a pair list that is reused step after step costs nothing after its first use."""
+    for t in (src_idx, dst_idx):
+        if t.numel() == 0 or getattr(t, "_sr_range_ok", None) == (t._version, n):
+            continue
+        lo, hi = (int(v) for v in torch.stack(torch.aminmax(t)).tolist())
+        if lo < 0 or hi >= n:
+            raise IndexError(f"sailrecon_b200 {what}: pair indices span [{lo}, {hi}] but there are only {n} frames")
+        t._sr_range_ok = (t._version, n)
+
+
 def _pose_rows(t: torch.Tensor, name: str) -> int:
     if t.dim() != 3 or tuple(t.shape[-2:]) not in ((3, 4), (4, 4)):
         raise ValueError(f"sailrecon_b200: {name} must be [P, 3, 4] or [P, 4, 4], got {tuple(t.shape)}")
@@ -986,6 +1007,7 @@ def cdf_tables(residuals, weights, src_idx, dst_idx, num_nodes: int, min_val: fl
     r = _f32c(residuals, "residuals")
     w = None if weights is None else _f32c(weights, "weights", (P, K))
     s, d = _idx64(src_idx, "src_indices", P), _idx64(dst_idx, "dst_indices", P)
+    _check_pair_indices(s, d, num_nodes, "cdf_tables")
     sk = _f32c(smooth_kernel.reshape(-1), "smooth_kernel")
     if sk.numel() % 2 != 1:
         raise ValueError("sailrecon_b200: the smoothing kernel must have an odd number of taps")
@@ -1006,6 +1028,9 @@ def cdf_lookup(residuals, weights, src_idx, dst_idx, cdf, pdf, min_val: float, i
     w = None if weights is None else _f32c(weights, "weights", (P, K))
     s, d = _idx64(src_idx, "src_indices", P), _idx64(dst_idx, "dst_indices", P)
     c, q = _f32c(cdf, "cdf"), _f32c(pdf, "pdf", cdf.shape)
+    if c.dim() != 2:
+        raise ValueError(f"sailrecon_b200: cdf / pdf must be [num_nodes, num_bins], got {tuple(c.shape)}")
+    _check_pair_indices(s, d, c.shape[0], "cdf_lookup")
     outs = [torch.empty(P, K, dtype=torch.float32, device=r.device) for _ in range(4)]
     _lib.check(_lib.load().sr_cdf_lookup_f32(r.data_ptr(), _ptr(w), s.data_ptr(), d.data_ptr(), c.data_ptr(), q.data_ptr(), P, K,
                                              min_val, inv_bin_width, num_bins, *(o.data_ptr() for o in outs), _stream()),
@@ -1031,6 +1056,7 @@ def reproj_cdf_loss(pred_intrinsics, pred_extrinsics, kprime_to_k, shared_focal:
     sc, dc = _f32c(src_coords, "src_coords"), _f32c(dst_coords, "dst_coords", (P, K, 2))
     sz, dz = _f32c(src_depth, "src_depth", (P, K)), _f32c(dst_depth, "dst_depth", (P, K))
     s, d = _idx64(src_idx, "src_idx", P), _idx64(dst_idx, "dst_idx", P)
+    _check_pair_indices(s, d, N, "reproj_cdf_loss")
     sk = _f32c(smooth_kernel.reshape(-1), "smooth_kernel")
     lib = _lib.load()
     n_ws = lib.sr_reproj_loss_workspace_floats(N, P, K, num_bins)

@@ -49,8 +49,12 @@ def install_training_loss() -> None:
     """N4: make train/train_imc.py (imported AFTER this call, with the reference's `train/` directory on sys.path) take
     `utils.geometry` (train/utils/geometry.py: compute_relative_pose, backproject_and_reproject[_with_approximation],
     compute_projective_residual) and `losses.cdf_loss` (train/losses/cdf_loss.py: CDFLossIndexPytorch) from this package.
-    The script's own `compute_loss` then runs unchanged on the kernels of csrc/loss.cu; `sailrecon_b200.losses.compute_loss`
-    is the fused replacement for that function itself."""
+    The script's own `compute_loss` function then runs on the kernels of csrc/loss.cu (tests/test_loss_gpu.py runs the live
+    reference's compute_loss on these same mirrors) — with ONE required change in the training loop around it: the trainer builds
+    CDFLossIndexPytorch with placeholder pair indices `[0]` (train_imc.py:338-346) and the reference's forward then indexes
+    that length-1 buffer with every pair number; the mirror does not reproduce that and raises IndexError for any batch with
+    more than one pair until the loop calls `cdf_loss.set_pairs(batch['src_idx'], batch['dst_idx'], num_nodes)` per batch.
+    `sailrecon_b200.losses.compute_loss` (the fused replacement for the function itself) takes the pairs from the batch."""
     for name in ("train_imc", "utils.geometry", "losses.cdf_loss"):
         if name in sys.modules:
             raise RuntimeError(f"sailrecon_b200.overlay.install_training_loss() must run before `{name}` is imported")

@@ -593,6 +593,16 @@ class EmbedSaved:
     HW: tuple
 
 
+# The im2col rows are the K operand of the projection GEMM (K % 64) AND the N operand of its weight gradient dW = dz^T a
+# (sr_gemm_bf16_t: N % 128), so the training path pads them to 128 columns: 588 -> 640 for patch 14 (what ceil-to-64 gives
+# too, i.e. unchanged), 192 -> 256 for patch 8, where ceil-to-64 used to fail with a shape error in the middle of backward.
+_IM2COL_PAD = 128
+
+
+def _im2col_width(K: int) -> int:
+    return (K + _IM2COL_PAD - 1) // _IM2COL_PAD * _IM2COL_PAD
+
+
 def embed_forward_saving(agg: nn.Module, imgs: torch.Tensor, X0: torch.Tensor, S: int, P: int, C: int):
     """aggregator.py:267-274 + vision_transformer.py:242-307 in the bf16 autocast arithmetic, keeping what the backward reads.
     Writes the patch-token rows of X0 [S*P, C] (rows psi.. of every frame) and returns EmbedSaved.  Same arithmetic as
@@ -607,11 +617,11 @@ def embed_forward_saving(agg: nn.Module, imgs: torch.Tensor, X0: torch.Tensor, S
         ph = pe_mod.patch_size[0]
         hw = (H // ph) * (W // ph)
         K = 3 * ph * ph
-        Kp = (K + 63) // 64 * 64
+        Kp = _im2col_width(K)
         a = torch.empty(S * hw, Kp, dtype=BF, device=dev)
         ops.patchify(imgs.contiguous(), a, ph, _RESNET_MEAN, _RESNET_STD)
         y = torch.empty(S * hw, C, dtype=BF, device=dev)
-        ops.gemm(a, engine.weight_bf16(pe_mod.proj, pad_k=64), engine.bias_for(pe_mod.proj, "bf16"), y, kind=SR_EPI_BIAS)
+        ops.gemm(a, engine.weight_bf16(pe_mod.proj, pad_k=_IM2COL_PAD), engine.bias_for(pe_mod.proj, "bf16"), y, kind=SR_EPI_BIAS)
         X0.view(S, P, C)[:, psi:] = y.view(S, hw, C)
         return EmbedSaved(a, [], None, S, P, hw, (H, W))
     vit = pe_mod
@@ -623,14 +633,14 @@ def embed_forward_saving(agg: nn.Module, imgs: torch.Tensor, X0: torch.Tensor, S
         raise NotImplementedError("sailrecon_b200: the ViT patch embed must have the aggregator's width and register count")
     pe = vit.interpolated_pos_embed(H, W)
     K = 3 * ph * ph
-    Kp = (K + 63) // 64 * 64
+    Kp = _im2col_width(K)
     a = torch.empty(S * hw, Kp, dtype=BF, device=dev)
     ops.patchify(imgs.contiguous(), a, ph, _RESNET_MEAN, _RESNET_STD)
     x = torch.empty(S * Pd, D, dtype=torch.float32, device=dev)
     proj = vit.patch_embed.proj
     from ._lib import SR_EPI_LS_RESIDUAL
     for s_ in range(S):                                                  # x[s, 1+R:] = pos_embed[1:] + proj(patches)
-        ops.gemm(a[s_ * hw:(s_ + 1) * hw], engine.weight_bf16(proj, pad_k=64), engine.bias_for(proj, "bf16"),
+        ops.gemm(a[s_ * hw:(s_ + 1) * hw], engine.weight_bf16(proj, pad_k=_IM2COL_PAD), engine.bias_for(proj, "bf16"),
                  x[s_ * Pd + 1 + R:(s_ + 1) * Pd], kind=SR_EPI_LS_RESIDUAL, gamma=None, resid=pe[1:])
     xv = x.view(S, Pd, D)
     xv[:, 0] = vit.cls_token.detach()[0, 0] + pe[0]
@@ -655,6 +665,8 @@ def _proj_wgrad(proj: nn.Module, a: torch.Tensor, dz: torch.Tensor, grads: Dict[
     K = proj.weight[0].numel()
     if proj.bias is not None:
         ops.colsum(dz, None, _acc(grads, proj.bias), accumulate=True)
+    if a.shape[1] % _IM2COL_PAD or a.shape[1] < K:
+        raise ValueError(f"sailrecon_b200: im2col rows must be padded to a multiple of {_IM2COL_PAD} columns >= {K}, got {a.shape[1]}")
     tmp = torch.empty(D, a.shape[1], dtype=torch.float32, device=dz.device)
     ops.gemm_t(dz, a, tmp, a_mn_major=True)                              # [D, Kp] = dz[T, D]^T a[T, Kp], operands in place
     _acc(grads, proj.weight).view(D, K).add_(tmp[:, :K])

@@ -203,3 +203,37 @@ def test_edge_shapes():
     with pytest.raises(NotImplementedError):
         losses.backproject_and_reproject(t["src_coords"].clone().requires_grad_(True), t["src_depth"], t["pred_intrinsics"][:2],
                                          t["pred_intrinsics"][:2], E44[:2].detach(), torch.ones(2, 1, device=DEV))
+
+
+def test_pair_index_outside_the_frames_raises_instead_of_corrupting_memory():
+    """A pair list that names a frame the predictions do not have (batch / model mismatch): the reference dies on a device-side
+    assert inside scatter_add_ / gather (cdf_loss.py:150-160); here it is an IndexError BEFORE any kernel runs."""
+    from sailrecon_b200 import ops
+    g, meta = load_loss_golden("loss_imc")
+    t = _t(g)
+    N = t["pred_intrinsics"].shape[0]
+    bad = dict(t)
+    bad["dst_idx"] = t["dst_idx"].clone()
+    bad["dst_idx"][-1] = N
+    with pytest.raises(IndexError, match="pair indices"):
+        _ours_fused(bad, meta["cdf"])
+    neg = dict(t)
+    neg["src_idx"] = t["src_idx"].clone()
+    neg["src_idx"][0] = -1
+    with pytest.raises(IndexError, match="pair indices"):
+        _ours_fused(neg, meta["cdf"])
+    P, K = t["src_depth"].shape
+    r = torch.rand(P, K, device=DEV)
+    sk = torch.ones(1, device=DEV)
+    with pytest.raises(IndexError):                                       # num_nodes smaller than max index + 1
+        ops.cdf_tables(r, None, t["src_idx"], t["dst_idx"], N - 1, 0.0, 50.0, 50, 25.0, sk)
+    pmf, cdf, pdf = ops.cdf_tables(r, None, t["src_idx"], t["dst_idx"], N, 0.0, 50.0, 50, 25.0, sk)
+    with pytest.raises(IndexError):
+        ops.cdf_lookup(r, None, t["src_idx"], t["dst_idx"], cdf[:N - 1].contiguous(), pdf[:N - 1].contiguous(), 0.0, 50.0)
+    ops.cdf_lookup(r, None, t["src_idx"], t["dst_idx"], cdf, pdf, 0.0, 50.0)    # the same (cached-OK) lists at the right N still run
+    # an in-place edit of a list that passed before is seen (version counter)
+    idx = t["src_idx"].clone()
+    ops.cdf_lookup(r, None, idx, t["dst_idx"], cdf, pdf, 0.0, 50.0)
+    idx[0] = N + 3
+    with pytest.raises(IndexError):
+        ops.cdf_lookup(r, None, idx, t["dst_idx"], cdf, pdf, 0.0, 50.0)

@@ -379,6 +379,21 @@ def test_localizer_camera_only_matches_full_reloc_path(bf16):
         pg, eg, ig = graph.localize(queries[i:i + 1])
         torch.cuda.synchronize()
         assert torch.equal(pg, pe) and torch.equal(eg, ee), i            # same kernels, same inputs: bit-identical
+    # the graph owns the scratch it captured: nothing is left in the shared per-stream tables under its stream handle
+    from sailrecon_b200 import engine, ops
+    sid = graph._stream.cuda_stream
+    assert graph._keep and not [k for k in engine.WS._buf if k[2] == sid] and not [k for k in ops._ATTN_WS if k[1] == sid]
+    # weights changed after the capture (optimizer step / load_state_dict): the replay must not serve the stale bf16 copies
+    before = eg.clone()
+    with torch.no_grad():
+        for prm in list(head.parameters())[-2:] + list(agg.global_reloc_blocks[-1].mlp.parameters()):
+            prm.mul_(1.25)
+    pe, ee, ie = eager.localize(queries[2:3])
+    pe, ee = pe.clone(), ee.clone()
+    pg, eg, ig = graph.localize(queries[2:3])
+    torch.cuda.synchronize()
+    assert not torch.equal(ee, before)
+    assert torch.equal(pg, pe) and torch.equal(eg, ee)
     eager.clear()
     with pytest.raises(RuntimeError):
         eager.localize(queries[:1])

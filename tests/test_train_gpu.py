@@ -201,6 +201,33 @@ def test_qknorm_rope_fwd_equals_fused_epilogue_and_bwd_matches_autograd():
         assert rel_l2(got.cpu(), want.grad.cpu()) < 2e-3
 
 
+
+@pytest.mark.parametrize("ph,Kp", [(14, 640), (8, 256)])
+def test_patch_projection_weight_gradient_at_im2col_widths_that_are_not_multiples_of_128(ph, Kp):
+    """train._proj_wgrad: dW of Conv2d(3, D, ph, stride ph) as dz^T im2col on the transposed-operand GEMM, which needs the
+    im2col width % 128 == 0 — patch 14 gets 640 from ceil-to-64 by luck, patch 8 (192 -> 256) needs the explicit padding."""
+    from sailrecon_b200 import ops, train
+    from sailrecon_b200.models.aggregator import _RESNET_MEAN, _RESNET_STD
+    torch.manual_seed(ph)
+    D, S, H, W = 128, 2, 8 * ph, 12 * ph
+    proj = torch.nn.Conv2d(3, D, ph, ph).to(DEV)
+    imgs = torch.rand(S, 3, H, W, device=DEV)
+    T, K = S * 8 * 12, 3 * ph * ph
+    assert train._im2col_width(K) == Kp
+    a = torch.empty(T, Kp, dtype=BF, device=DEV)
+    ops.patchify(imgs, a, ph, _RESNET_MEAN, _RESNET_STD)
+    dz = _randn(T, D, seed=3).to(BF)
+    grads = {}
+    train._proj_wgrad(proj, a, dz, grads)
+    mean = torch.tensor(_RESNET_MEAN, device=DEV).view(1, 3, 1, 1)
+    std = torch.tensor(_RESNET_STD, device=DEV).view(1, 3, 1, 1)
+    x = ((imgs - mean) / std).to(BF).float()                              # the kernel's operand rounding
+    z = F.conv2d(x, proj.weight, proj.bias, stride=ph).permute(0, 2, 3, 1).reshape(T, D)
+    (z * dz.float()).sum().backward()
+    assert rel_l2(grads[proj.weight], proj.weight.grad) < 1e-3 and rel_l2(grads[proj.bias], proj.bias.grad) < 1e-3
+    with pytest.raises(ValueError, match="padded"):
+        train._proj_wgrad(proj, a[:, :Kp - 64].contiguous(), dz, grads)
+
 @pytest.mark.parametrize("T,K,N", [(333, 1024, 3072), (2748, 1024, 4096), (1374, 4096, 1024), (70, 1024, 1024)])
 def test_linear_backward_on_tensor_cores(T, K, N):
     """dW = dz^T a and da = dz W on the tensor-core GEMM reading its operands in place (MN-major descriptors, sr_gemm_bf16_t)
