@@ -39,9 +39,10 @@ query image against the HBM-resident scene K/V cache); ms per localised image.
 
 --impl reference: the UNMODIFIED reference (oracle/_ref, a byte-identical copy of /root/reference/sailrecon made by
 oracle/make_ref.py) run on the host cores, fp32, all threads: each step is a WHOLE forward (24 DINOv2 blocks + 24 x 3
-aggregator blocks + 4 camera-head iterations, nothing scaled or extrapolated) of a bounded sample scene (2 anchors + 2
-queries at 518x518); the requested warm-up and timed steps are run as far as they fit a wall-clock budget (270 s; 20 + 5 forwards of 8.3 s on the
-round-2 box fit) and `steps` / `warmup` report the counts actually run.
+aggregator blocks + 4 camera-head iterations, nothing scaled or extrapolated).  One 4-frame forward calibrates the host; if
+one warm-up + two timed forwards of the GPU arm's own 16 + 16-frame scene are predicted to fit the wall-clock budget
+(--cpu-budget-s, 270 s) the arm runs that scene, else a bounded sample scene (2 anchors + 2 queries at 518x518); the
+requested warm-up and timed steps are run as far as they fit the budget and `steps` / `warmup` report the counts actually run.
 """
 from __future__ import annotations
 
@@ -53,6 +54,7 @@ import subprocess
 import sys
 import threading
 import time
+from typing import Optional
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -148,68 +150,107 @@ def load_peak_tf():
         return 1400.0, "fallback (B200_PROFILING.md sustained ~1.4 PF)"
 
 
-CPU_SAMPLE = (2, 2, 518)            # anchors, queries, pixels of the bounded CPU sample scene
+CPU_SAMPLE = (2, 2, 518)            # anchors, queries, pixels of the bounded CPU sample scene (cpu_baseline leg; fallback of the arm)
+CPU_FULL = (16, 16, 518)            # the GPU arm's own scene (agg32): what --impl reference runs when the host is fast enough
+
+
+class _CpuReference:
+    """The unmodified reference's Aggregator + CameraHead on the host cores (fp32, no autocast — the arithmetic of
+    BASELINE.json configs[0]), WHOLE depth, built once and run on scenes of any size."""
+
+    def __init__(self):
+        cls = reference_classes()
+        if cls is None:
+            raise RuntimeError("oracle/_ref is absent: run `python oracle/make_ref.py` (or __graft_entry__.build()) in the build container")
+        Aggregator, CameraHead = cls
+        self.threads = os.cpu_count() or 1
+        torch.set_num_threads(self.threads)
+        torch.manual_seed(0)
+        self.agg, self.head = Aggregator().eval(), CameraHead(dim_in=2 * C).eval()
+
+    def run(self, sample, steps: int, warmup: int, deadline: float, give_up_s: Optional[float] = None) -> Optional[dict]:
+        """`warmup` untimed and up to `steps` timed forwards on `sample`, stopping early when the next one would pass
+        `deadline` (time.perf_counter() clock).  Nothing is scaled."""
+        Na, Nq, size = sample
+        images = torch.rand(1, Na + Nq, 3, size, size, generator=torch.Generator().manual_seed(1))
+
+        def fwd():
+            self.agg.generator.manual_seed(1234)
+            t0 = time.perf_counter()
+            with torch.no_grad():
+                out, _, cam = self.agg(images, list(range(Na)), list(range(Na, Na + Nq)), fix_rank=300)
+                poses = self.head(out, cam)
+            return time.perf_counter() - t0, poses
+
+        done_w, ts, last = 0, [], None
+        for _ in range(warmup):
+            # the first warm-up always runs; further ones only while ALL requested timed steps still fit behind them
+            if done_w and time.perf_counter() + (warmup - done_w + steps) * 1.05 * last > deadline:
+                break
+            last, _ = fwd()
+            done_w += 1
+        if give_up_s is not None and last is not None and time.perf_counter() + 1.05 * last > deadline + give_up_s:
+            return None                                   # a timed forward of this scene would overrun by more than give_up_s
+        for _ in range(steps):
+            if ts and time.perf_counter() + 1.1 * max(ts) > deadline:
+                break
+            dt, poses = fwd()
+            ts.append(dt)
+        t = sum(ts) / len(ts)
+        return {"s_per_step": t, "frames_per_s": (Na + Nq) / t, "steps": len(ts), "warmup": done_w, "threads": self.threads,
+                "finite": bool(torch.isfinite(poses[-1]).all()), "scene": sample,
+                "sample": f"unmodified reference (oracle/_ref) Aggregator + CameraHead forward, whole depth (24 DINOv2 blocks + 24 x "
+                          f"(frame, global, reloc) blocks + 4 camera-head iterations), {Na} anchors + {Nq} queries at {size}x{size}, "
+                          f"fp32, {self.threads} host threads; {len(ts)} timed forward(s) of {t:.1f} s after {done_w} warm-up; "
+                          f"frames/s = {Na + Nq} / step time, nothing scaled"}
 
 
 def cpu_reference_forward(steps: int, warmup: int, budget_s: float) -> dict:
-    """The unmodified reference's Aggregator + CameraHead forward on the host cores (fp32, no autocast — the arithmetic
-    of BASELINE.json configs[0]), WHOLE depth, on the bounded sample scene.  Runs `warmup` untimed and up to `steps`
-    timed forwards, stopping early when the next one would overrun `budget_s`.  Nothing is scaled."""
-    cls = reference_classes()
-    if cls is None:
-        raise RuntimeError("oracle/_ref is absent: run `python oracle/make_ref.py` (or __graft_entry__.build()) in the build container")
-    Aggregator, CameraHead = cls
-    threads = os.cpu_count() or 1
-    torch.set_num_threads(threads)
-    Na, Nq, size = CPU_SAMPLE
+    """The cpu_baseline leg: the bounded sample scene CPU_SAMPLE within `budget_s` seconds."""
     t_start = time.perf_counter()
-    torch.manual_seed(0)
-    agg, head = Aggregator().eval(), CameraHead(dim_in=2 * C).eval()
-    images = torch.rand(1, Na + Nq, 3, size, size, generator=torch.Generator().manual_seed(1))
-
-    def fwd():
-        agg.generator.manual_seed(1234)
-        t0 = time.perf_counter()
-        with torch.no_grad():
-            out, _, cam = agg(images, list(range(Na)), list(range(Na, Na + Nq)), fix_rank=300)
-            poses = head(out, cam)
-        return time.perf_counter() - t0, poses
-
-    done_w, ts, last = 0, [], None
-    for _ in range(warmup):
-        # the first warm-up always runs; further ones only while ALL requested timed steps still fit the budget behind them
-        if done_w and time.perf_counter() - t_start + (warmup - done_w + steps) * 1.05 * last > budget_s:
-            break
-        last, _ = fwd()
-        done_w += 1
-    for _ in range(steps):
-        if ts and time.perf_counter() - t_start + 1.1 * max(ts) > budget_s:
-            break
-        dt, poses = fwd()
-        ts.append(dt)
-    t = sum(ts) / len(ts)
-    return {"s_per_step": t, "frames_per_s": (Na + Nq) / t, "steps": len(ts), "warmup": done_w, "threads": threads,
-            "finite": bool(torch.isfinite(poses[-1]).all()),
-            "sample": f"unmodified reference (oracle/_ref) Aggregator + CameraHead forward, whole depth (24 DINOv2 blocks + 24 x "
-                      f"(frame, global, reloc) blocks + 4 camera-head iterations), {Na} anchors + {Nq} queries at {size}x{size}, "
-                      f"fp32, {threads} host threads; {len(ts)} timed forward(s) of {t:.1f} s after {done_w} warm-up; frames/s = "
-                      f"{Na + Nq} / step time, nothing scaled"}
+    return _CpuReference().run(CPU_SAMPLE, steps, warmup, t_start + budget_s)
 
 
 def run_reference_arm(args, rank: int, world: int) -> None:
+    """--impl reference: the reference's own CPU implementation of the path, on the GPU arm's configuration.  One forward
+    of the 4-frame sample calibrates the host; if one warm-up + two timed forwards of the FULL agg32 scene (16 + 16 frames,
+    the scene the GPU arm times) are predicted to fit the budget, the arm runs that — same workload on both sides of the
+    driver's ratio.  Otherwise (slow or few host cores) it stays on the 4-frame sample and says so: frames/s is then a
+    per-frame throughput across two scene sizes, which flatters the reference (its global attention and its dense
+    (S*P)^2 masks grow faster than the frame count)."""
     if rank != 0:
         return
-    Na, Nq, size = CPU_SAMPLE
-    r = cpu_reference_forward(args.steps, max(args.warmup, 1), args.cpu_budget_s)
+    t_start = time.perf_counter()
+    deadline = t_start + args.cpu_budget_s
+    ref = _CpuReference()
+    cal = ref.run(CPU_SAMPLE, 1, 1, deadline)
+    frames_ratio = (CPU_FULL[0] + CPU_FULL[1]) / (CPU_SAMPLE[0] + CPU_SAMPLE[1])
+    predicted = cal["s_per_step"] * frames_ratio * 1.5             # linear part x 8, + the quadratic global attention / masks
+    full = not args.cpu_sample_only and time.perf_counter() + 3.0 * predicted <= deadline
+    r = None
+    if full:
+        r = ref.run(CPU_FULL, max(args.steps, 2), 1, deadline, give_up_s=60.0)
+        if r is None:                                              # badly mis-predicted: the warm-up alone ate the budget
+            full = False
+            predicted = float("nan")
+        elif r["steps"] < 2:
+            r["sample"] += "; ONE timed forward only (the host was slower than the calibration predicted)"
+    if r is None:
+        r = ref.run(CPU_SAMPLE, args.steps, max(args.warmup, 1), deadline)
+    Na, Nq, size = r["scene"]
     v = r["frames_per_s"]
+    what = (f"agg32: {Na} anchors + {Nq} queries at {size}x{size} per step - the GPU arm's own scene" if full else
+            f"bounded sample scene of {Na} anchors + {Nq} queries at {size}x{size} per step (the full 16 + 16 scene was predicted at "
+            f"{predicted:.0f} s per forward on this host: 1 + 2 of them do not fit the {args.cpu_budget_s:.0f} s budget; frames/s is "
+            "per-frame throughput)")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": r["steps"],
             "warmup": r["warmup"], "steps_requested": args.steps, "warmup_requested": args.warmup,
             "ms_per_step": r["s_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"agg32 hot path (DINOv2 ViT-L patch embed + 24x(frame, global, reloc) blocks + camera head, "
-                                   f"fix_rank 300, random-init weights) on the reference's CPU path; bounded sample scene of "
-                                   f"{Na} anchors + {Nq} queries at {size}x{size} per step (frames/s is per-frame throughput; the "
-                                   "CPU cost is linear in the frame count at this size)"},
+            "config": {"workload": "agg32 hot path (DINOv2 ViT-L patch embed + 24x(frame, global, reloc) blocks + camera head, "
+                                   "fix_rank 300, random-init weights) on the reference's CPU path; " + what,
+                       "same_scene_as_gpu_arm": bool(full),
+                       "calibration": f"{cal['s_per_step']:.1f} s per 4-frame forward -> {predicted:.0f} s predicted per 32-frame forward"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": r["threads"], "kind": "reference", "sample": r["sample"]},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "outputs_finite": r["finite"]}
@@ -1036,6 +1077,8 @@ def main():
     ap.add_argument("--no-extras", action="store_true",
                     help="agg32: headline only (skip parity / library baseline / sharded / train24 records; ncu runs)")
     ap.add_argument("--cpu-budget-s", type=float, default=270.0, help="--impl reference: wall-clock budget of the CPU arm")
+    ap.add_argument("--cpu-sample-only", action="store_true",
+                    help="--impl reference: stay on the 4-frame sample scene even if the full 32-frame scene would fit the budget")
     ap.add_argument("--checkpoint", action="store_true",
                     help="workload train: the reference's torch.utils.checkpoint schedule (re-run every block inside the backward) "
                          "instead of keeping the activations in HBM")

@@ -56,7 +56,8 @@ __device__ __forceinline__ bool mbar_test_wait(uint64_t* bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded spin: a protocol bug traps (-> CUDA error surfaced through the C-ABI status)
-// instead of hanging the GPU.  ~2^31 polls is minutes; normal waits are microseconds.
+// instead of hanging the GPU.  2^26 polls of the tight loop are seconds, 2^24 polls of the sleeping loop below (each a
+// __nanosleep of 96 ns nominal, microseconds in practice) up to about a minute; normal waits are microseconds.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 #ifdef SR_DEBUG_HANG_TRAP
   uint32_t spins = 0;
