@@ -146,7 +146,7 @@ def _gather_worker(rank, world, port, counts, errs):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("counts", [[2, 1], [3, 0, 2]])
+@pytest.mark.parametrize("counts", [[2, 1], [3, 0, 2], [2, 2]])       # broadcast fallback (gloo, uneven / empty) and the one-collective path
 def test_allgather_rows_uneven_counts(counts):
     errs = mp.Manager().dict()
     mp.spawn(_gather_worker, args=(len(counts), _free_port(), counts, errs), nprocs=len(counts), join=True)
