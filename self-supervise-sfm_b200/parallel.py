@@ -365,14 +365,25 @@ class ScenePlan:
 
 
 def _allgather_rows(dst: torch.Tensor, local: torch.Tensor, counts: Sequence[int], rank: int, group=None) -> torch.Tensor:
-    """dst[sum(counts), ...] <- concatenation of every rank's `local` rows (uneven counts: one broadcast per rank)."""
+    """dst[sum(counts), ...] <- concatenation of every rank's `local` rows.  Equal counts (the usual case: anchors divide
+    evenly over the ranks) -> ONE all_gather_into_tensor; uneven or empty shards keep one broadcast per rank."""
+    R = len(counts)
+    if not (dist.is_initialized() and R > 1):
+        if counts[rank]:
+            off = sum(counts[:rank])
+            dst[off:off + counts[rank]].copy_(local)
+        return dst
+    if local.shape[0] != counts[rank]:
+        raise ValueError(f"_allgather_rows: rank {rank} holds {local.shape[0]} rows, the plan says {counts[rank]}")
+    if min(counts) > 0 and len(set(counts)) == 1 and dst.is_contiguous() and local.is_contiguous():
+        dist.all_gather_into_tensor(dst, local, group=group)
+        return dst
     off = 0
     for r, c in enumerate(counts):
         if c:
             if r == rank:
                 dst[off:off + c].copy_(local)
-            if dist.is_initialized() and len(counts) > 1:
-                dist.broadcast(dst[off:off + c], src=_global_rank(group, r), group=group)
+            dist.broadcast(dst[off:off + c], src=_global_rank(group, r), group=group)
         off += c
     return dst
 
