@@ -41,7 +41,7 @@ query image against the HBM-resident scene K/V cache); ms per localised image.
 oracle/make_ref.py) run on the host cores, fp32, all threads: each step is a WHOLE forward (24 DINOv2 blocks + 24 x 3
 aggregator blocks + 4 camera-head iterations, nothing scaled or extrapolated).  One 4-frame forward calibrates the host; if
 one warm-up + two timed forwards of the GPU arm's own 16 + 16-frame scene are predicted to fit the wall-clock budget
-(--cpu-budget-s, 270 s) the arm runs that scene, else a bounded sample scene (2 anchors + 2 queries at 518x518); the
+(--cpu-budget-s, 300 s) the arm runs that scene, else a bounded sample scene (2 anchors + 2 queries at 518x518); the
 requested warm-up and timed steps are run as far as they fit the budget and `steps` / `warmup` report the counts actually run.
 """
 from __future__ import annotations
@@ -225,9 +225,11 @@ def run_reference_arm(args, rank: int, world: int) -> None:
     ref = _CpuReference()
     cal = ref.run(CPU_SAMPLE, 1, 1, deadline)
     frames_ratio = (CPU_FULL[0] + CPU_FULL[1]) / (CPU_SAMPLE[0] + CPU_SAMPLE[1])
-    predicted = cal["s_per_step"] * frames_ratio * 1.5             # linear part x 8, + the quadratic global attention / masks
-    # 2.2 x: the warm-up and ONE timed forward must fit with a margin; a second / third timed one runs if the budget still allows
-    full = not args.cpu_sample_only and time.perf_counter() + 2.2 * predicted <= deadline
+    # linear part x 8, + the quadratic global attention / dense masks: measured 124.3 s against 7.3 s per 4-frame forward on the
+    # 16-thread round-3 box (profiles/r03_ref_arm_full.json) = 2.1 x the linear extrapolation
+    predicted = cal["s_per_step"] * frames_ratio * 2.1
+    # the warm-up and ONE timed forward must fit; a second / third timed one runs if the budget still allows
+    full = not args.cpu_sample_only and time.perf_counter() + 2.05 * predicted <= deadline
     r = None
     if full:
         r = ref.run(CPU_FULL, max(args.steps, 2), 1, deadline, give_up_s=60.0)
@@ -1077,7 +1079,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true",
                     help="agg32: headline only (skip parity / library baseline / sharded / train24 records; ncu runs)")
-    ap.add_argument("--cpu-budget-s", type=float, default=270.0, help="--impl reference: wall-clock budget of the CPU arm")
+    ap.add_argument("--cpu-budget-s", type=float, default=300.0, help="--impl reference: wall-clock budget of the CPU arm")
     ap.add_argument("--cpu-sample-only", action="store_true",
                     help="--impl reference: stay on the 4-frame sample scene even if the full 32-frame scene would fit the budget")
     ap.add_argument("--checkpoint", action="store_true",
